@@ -1,0 +1,140 @@
+/*
+ * b200p.h -- C-ABI of libb200parallm.so: the sm_100a kernels under the batched decode step.
+ *
+ * The reference (misanthropic-ai/mlx_parallm) has no FFI of its own: its arithmetic is reached
+ * through mlx.core (nanobind).  Each entry point below therefore cites the *MLX call site in the
+ * reference* that it replaces (paths relative to the reference root).  A maintainer binds these
+ * with ctypes; mlx_parallm_b200/_lib.py is that binding.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative B200P_ERR_*; b200p_last_error() gives a
+ *     thread-local message.
+ *   - all pointers are CALLER-OWNED DEVICE pointers unless named host_*; nothing is allocated,
+ *     freed or synchronised inside; every launch is ordered on `stream` (a cudaStream_t passed as
+ *     void*) and is CUDA-graph capturable.
+ *   - `dtype` is the storage type of activations, scales, biases and KV (MLX unifies them through
+ *     result_type before quantized_matmul): B200P_F32 / F16 / BF16.
+ *   - quantized weights are in MLX layout: w uint32 [N, K*bits/32] (element j of a word in bits
+ *     [j*bits,(j+1)*bits)), scales/biases [N, K/group_size]; group_size 64 or 128... (any multiple
+ *     of 32 dividing K for the generic path; the tensor path requires 64), bits in {4, 8}.
+ *   - there is NO CPU fallback: without an sm_100 device b200p_arch_check() fails and every
+ *     launch returns B200P_ERR_ARCH / B200P_ERR_CUDA.
+ */
+#ifndef B200P_H
+#define B200P_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200P_OK          0
+#define B200P_ERR_ARG    -1   /* bad shape / null pointer / unsupported combination */
+#define B200P_ERR_ALIGN  -2   /* pointer or leading dimension not aligned as required */
+#define B200P_ERR_ARCH   -3   /* device is not sm_100 */
+#define B200P_ERR_CUDA   -4   /* CUDA runtime error (message in b200p_last_error) */
+
+enum { B200P_F32 = 0, B200P_F16 = 1, B200P_BF16 = 2 };
+
+/* dequantize rounding (oracle/mlx_ops.py MODE_*) */
+enum { B200P_DQ_F32_MULADD = 0, B200P_DQ_FMA = 1, B200P_DQ_T_MULADD = 2 };
+
+/* b200p_qmm epilogues */
+enum {
+  B200P_EPI_STORE = 0,        /* y[M,N] (dtype) = acc                                   */
+  B200P_EPI_STORE_F32 = 1,    /* y[M,N] (float) = acc                (lm_head logits)    */
+  B200P_EPI_ADD_RESIDUAL = 2, /* y[M,N] (float) += acc               (o_proj, down_proj) */
+  B200P_EPI_SILU_MUL = 3      /* y[M,N/2] (dtype) = silu(acc[:, :N/2]) * acc[:, N/2:]
+                                 rows [0,N/2) of w are gate_proj, rows [N/2,N) up_proj   */
+};
+
+const char* b200p_version(void);
+const char* b200p_last_error(void);
+/* 0 iff the current device is compute capability 10.x */
+int b200p_arch_check(void);
+int b200p_sm_count(void);
+
+/* mx.dequantize(w, scales, biases, group_size, bits)            [nn.QuantizedEmbedding.__call__,
+ * models/llama.py:212, models/qwen3.py:166; bit-exactness target of the north star]
+ * out[N,K] in `dtype`. */
+int b200p_dequantize(const uint32_t* w, const void* scales, const void* biases, void* out,
+                     int64_t N, int64_t K, int group_size, int bits, int dtype, int mode,
+                     void* stream);
+
+/* embed_tokens(ids): gather rows + dequantize                    [models/llama.py:212]
+ * ids int32 [M]; out float [M,K] if out_f32 else `dtype` [M,K] (values are the dtype-rounded
+ * dequantised weights either way). */
+int b200p_embed(const int32_t* ids, const uint32_t* w, const void* scales, const void* biases,
+                void* out, int64_t M, int64_t V, int64_t K, int group_size, int bits, int dtype,
+                int mode, int out_f32, void* stream);
+
+/* mx.quantized_matmul(x, w, scales, biases, transpose=True)       [nn.QuantizedLinear.__call__:
+ * models/llama.py:93,143,165,250-252; models/qwen3.py:63,115]
+ * x `dtype` [M,K] row-major (ldx elements between rows), y per `epilogue` (ldy elements between
+ * rows).  fp32 accumulation.  Internally: CUDA-core GEMV (any dtype) or the tcgen05 tile path
+ * (F16/BF16, group 64, M >= tile threshold).  `workspace` (>= b200p_qmm_workspace_bytes) is
+ * required by the split-K tensor path; may be NULL for the GEMV path. */
+int b200p_qmm(const void* x, const uint32_t* w, const void* scales, const void* biases, void* y,
+              int64_t M, int64_t N, int64_t K, int64_t ldx, int64_t ldy, int group_size, int bits,
+              int dtype, int epilogue, void* workspace, size_t workspace_bytes, void* stream);
+size_t b200p_qmm_workspace_bytes(int64_t M, int64_t N, int64_t K);
+/* 1 if the tcgen05 tile path can run this call, else 0 */
+int b200p_qmm_tensor_supported(int64_t M, int64_t N, int64_t K, int group_size, int bits, int dtype,
+                               int epilogue);
+/* force a path for tests/benchmarks: 0 = auto, 1 = GEMV only, 2 = tensor only (error if unsupported) */
+int b200p_qmm_set_path(int path);
+
+/* mx.fast.rms_norm(x, w, eps)                                      [nn.RMSNorm: models/llama.py:187,
+ * 189,231]  x float [M,H] (the fp32 residual stream) -> y `dtype` [M,H]; w `dtype` [H]. */
+int b200p_rmsnorm(const float* x, const void* w, void* y, int64_t M, int64_t H, float eps,
+                  int dtype, void* stream);
+
+/* per-head q/k RMSNorm (qwen3 only) + mx.fast.rope at per-row offsets + cache append
+ *                      [models/qwen3.py:65-70; models/llama.py:107-117; models/base.py:119-140]
+ * qkv `dtype` [B*L, (Hq+2*Hkv)*D] (q heads, then k heads, then v heads);
+ * q_out `dtype` [B, L, Hq, D]; kcache/vcache `dtype` [B, Hkv, Tcap, D];
+ * lengths int32 [B] = tokens already in the cache per row (position of token l is lengths[b]+l);
+ * q_norm_w / k_norm_w `dtype` [D] or NULL.  Does NOT advance lengths. */
+int b200p_rope_kv_append(const void* qkv, void* q_out, void* kcache, void* vcache,
+                         const int32_t* lengths, const void* q_norm_w, const void* k_norm_w,
+                         int64_t B, int64_t L, int Hq, int Hkv, int D, int64_t Tcap,
+                         float rope_base, float rope_scale, float norm_eps, int dtype,
+                         void* stream);
+/* lengths[b] += delta (device side, keeps the decode graph replayable) */
+int b200p_advance_lengths(int32_t* lengths, int64_t B, int32_t delta, void* stream);
+
+/* mx.fast.scaled_dot_product_attention for cached decode / chunked prefill
+ *                      [models/llama.py:139-141, models/qwen3.py:111-113; causal rule of
+ *                       models/base.py:17-40 applied by bound, not by an additive -1e9 mask]
+ * q `dtype` [B, L, Hq, D]; caches as above; query (b,l) attends to keys [0, lengths[b]+l+1)
+ * (lengths = tokens in cache BEFORE this call's L tokens were appended).
+ * out `dtype` [B, L, Hq*D].  workspace: float, >= b200p_attn_workspace_bytes. */
+int b200p_attn(const void* q, const void* kcache, const void* vcache, const int32_t* lengths,
+               void* out, int64_t B, int64_t L, int Hq, int Hkv, int D, int64_t Tcap,
+               float scale, int dtype, void* workspace, size_t workspace_bytes, void* stream);
+size_t b200p_attn_workspace_bytes(int64_t B, int64_t L, int Hq, int D);
+/* 0 = auto, 1 = generic CUDA-core kernel only, 2 = tensor (mma) split-K kernel only */
+int b200p_attn_set_path(int path);
+
+/* mx.argmax(logits, axis=-1, keepdims=True)                         [utils.py:350-352,363]
+ * logits float [B, V] (ldl floats between rows) -> tokens int32 [B]; lowest index among ties.
+ * probs_out (optional, float [B]) receives softmax(logits)[b, token] computed in the same pass. */
+int b200p_argmax(const float* logits, int32_t* tokens, float* probs_out, int64_t B, int64_t V,
+                 int64_t ldl, void* stream);
+
+/* top_p_sampling(logits, top_p, temperature) / mx.random.categorical(logits/temp)
+ *                                                        [sample_utils.py:3-39; utils.py:354-361]
+ * Draws from the renormalised nucleus {tokens whose inclusive sorted cumulative mass <= top_p}
+ * (top_p >= 1 -> plain categorical).  Philox counter RNG keyed by (seed, offset, row).
+ * If the nucleus is empty (p_max > top_p; the reference divides 0/0) the argmax is returned.
+ * probs_out (optional, float [B]) receives softmax(logits)[b, token] (untempered, utils.py:363). */
+int b200p_sample_top_p(const float* logits, int32_t* tokens, float* probs_out, int64_t B,
+                       int64_t V, int64_t ldl, float temperature, float top_p, uint64_t seed,
+                       uint64_t offset, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200P_H */

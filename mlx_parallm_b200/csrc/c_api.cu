@@ -1,0 +1,157 @@
+// C-ABI glue: error plumbing, device checks and the path dispatchers of b200p_qmm / b200p_attn.
+#include <stdarg.h>
+
+#include "common.cuh"
+
+namespace b200p {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+  set_error("%s: %s", what, cudaGetErrorString(e));
+  return B200P_ERR_CUDA;
+}
+
+// implemented in the kernel translation units
+int qmv_launch(const void* x, const uint32_t* w, const void* s, const void* b, void* y, int64_t M, int64_t N,
+               int64_t K, int64_t ldx, int64_t ldy, int gs, int bits, int dtype, int epi, cudaStream_t st);
+bool qmm_tc_supported(int64_t M, int64_t N, int64_t K, int gs, int bits, int dtype, int epi);
+int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b, void* y, int64_t M, int64_t N,
+                  int64_t K, int64_t ldx, int64_t ldy, int bits, int dtype, int epi, void* ws, size_t ws_bytes,
+                  cudaStream_t st);
+size_t qmm_tc_workspace_bytes(int64_t M, int64_t N, int64_t K);
+int attn_generic_launch(const void* q, const void* kc, const void* vc, const int32_t* lengths, void* out,
+                        int64_t B, int64_t L, int Hq, int Hkv, int D, int64_t Tcap, float scale, int dtype,
+                        cudaStream_t st);
+bool attn_decode_supported(int64_t L, int Hq, int Hkv, int D, int dtype);
+int attn_decode_launch(const void* q, const void* kc, const void* vc, const int32_t* lengths, void* out,
+                       int64_t B, int64_t L, int Hq, int Hkv, int D, int64_t Tcap, float scale, int dtype,
+                       void* ws, size_t ws_bytes, cudaStream_t st);
+size_t attn_decode_workspace_bytes(int64_t B, int64_t L, int Hq, int D);
+
+static int g_qmm_path = 0;   // 0 auto, 1 gemv, 2 tensor
+static int g_attn_path = 0;  // 0 auto, 1 generic, 2 tensor
+static int g_sm_count = -1;
+static int g_cc_major = -1;
+
+static int query_device() {
+  if (g_cc_major >= 0) return B200P_OK;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+  cudaDeviceProp p;
+  e = cudaGetDeviceProperties(&p, dev);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceProperties");
+  g_cc_major = p.major;
+  g_sm_count = p.multiProcessorCount;
+  return B200P_OK;
+}
+
+int sm_count() {
+  query_device();
+  return g_sm_count > 0 ? g_sm_count : 148;
+}
+
+}  // namespace b200p
+
+using namespace b200p;
+
+extern "C" const char* b200p_version(void) { return "b200parallm 0.1 (sm_100a)"; }
+extern "C" const char* b200p_last_error(void) { return g_err; }
+
+extern "C" int b200p_arch_check(void) {
+  int rc = query_device();
+  if (rc) return rc;
+  B200P_REQUIRE(g_cc_major == 10, B200P_ERR_ARCH, "device compute capability %d.x is not sm_100", g_cc_major);
+  return B200P_OK;
+}
+
+extern "C" int b200p_sm_count(void) {
+  int rc = query_device();
+  if (rc) return rc;
+  return g_sm_count;
+}
+
+extern "C" int b200p_qmm_set_path(int path) {
+  B200P_REQUIRE(path >= 0 && path <= 2, B200P_ERR_ARG, "path must be 0..2");
+  g_qmm_path = path;
+  return B200P_OK;
+}
+
+extern "C" int b200p_attn_set_path(int path) {
+  B200P_REQUIRE(path >= 0 && path <= 2, B200P_ERR_ARG, "path must be 0..2");
+  g_attn_path = path;
+  return B200P_OK;
+}
+
+extern "C" size_t b200p_qmm_workspace_bytes(int64_t M, int64_t N, int64_t K) {
+  return qmm_tc_workspace_bytes(M, N, K);
+}
+
+extern "C" int b200p_qmm_tensor_supported(int64_t M, int64_t N, int64_t K, int group_size, int bits, int dtype,
+                                          int epilogue) {
+  return qmm_tc_supported(M, N, K, group_size, bits, dtype, epilogue) ? 1 : 0;
+}
+
+extern "C" int b200p_qmm(const void* x, const uint32_t* w, const void* scales, const void* biases, void* y,
+                         int64_t M, int64_t N, int64_t K, int64_t ldx, int64_t ldy, int group_size, int bits,
+                         int dtype, int epilogue, void* workspace, size_t workspace_bytes, void* stream) {
+  B200P_REQUIRE(x && w && scales && biases && y, B200P_ERR_ARG, "null pointer");
+  B200P_REQUIRE(bits == 4 || bits == 8, B200P_ERR_ARG, "bits must be 4 or 8, got %d", bits);
+  B200P_REQUIRE(M >= 0 && N > 0 && K > 0 && N % 2 == 0, B200P_ERR_ARG, "bad shape M=%lld N=%lld K=%lld (N must be even)",
+                (long long)M, (long long)N, (long long)K);
+  B200P_REQUIRE(group_size >= 32 && group_size % 32 == 0 && K % group_size == 0, B200P_ERR_ARG,
+                "group_size %d must be a multiple of 32 dividing K=%lld", group_size, (long long)K);
+  B200P_REQUIRE(epilogue >= 0 && epilogue <= 3, B200P_ERR_ARG, "bad epilogue %d", epilogue);
+  B200P_REQUIRE(dtype >= 0 && dtype <= 2, B200P_ERR_ARG, "bad dtype %d", dtype);
+  const size_t xs = dtype == B200P_F32 ? 4 : 2;
+  B200P_REQUIRE(aligned(x, 16) && aligned(w, 16) && (ldx * xs) % 16 == 0 && ldx >= K, B200P_ERR_ALIGN,
+                "x rows and w must be 16-byte aligned (ldx=%lld)", (long long)ldx);
+  B200P_REQUIRE((K * bits / 8) % 16 == 0, B200P_ERR_ALIGN, "packed weight rows must be 16-byte multiples (K=%lld)",
+                (long long)K);
+  B200P_REQUIRE(ldy >= (epilogue == B200P_EPI_SILU_MUL ? N / 2 : N), B200P_ERR_ARG, "ldy too small");
+  if (M == 0) return B200P_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool tc_ok = qmm_tc_supported(M, N, K, group_size, bits, dtype, epilogue);
+  if (g_qmm_path == 2) {
+    B200P_REQUIRE(tc_ok, B200P_ERR_ARG, "tensor path forced but unsupported for this call");
+  }
+  if (tc_ok && g_qmm_path != 1) {
+    B200P_REQUIRE(workspace && workspace_bytes >= qmm_tc_workspace_bytes(M, N, K), B200P_ERR_ARG,
+                  "tensor path needs a workspace of %zu bytes", qmm_tc_workspace_bytes(M, N, K));
+    return qmm_tc_launch(x, w, scales, biases, y, M, N, K, ldx, ldy, bits, dtype, epilogue, workspace,
+                         workspace_bytes, st);
+  }
+  return qmv_launch(x, w, scales, biases, y, M, N, K, ldx, ldy, group_size, bits, dtype, epilogue, st);
+}
+
+extern "C" size_t b200p_attn_workspace_bytes(int64_t B, int64_t L, int Hq, int D) {
+  return attn_decode_workspace_bytes(B, L, Hq, D);
+}
+
+extern "C" int b200p_attn(const void* q, const void* kcache, const void* vcache, const int32_t* lengths, void* out,
+                          int64_t B, int64_t L, int Hq, int Hkv, int D, int64_t Tcap, float scale, int dtype,
+                          void* workspace, size_t workspace_bytes, void* stream) {
+  B200P_REQUIRE(q && kcache && vcache && lengths && out, B200P_ERR_ARG, "null pointer");
+  B200P_REQUIRE(Hq > 0 && Hkv > 0 && Hq % Hkv == 0, B200P_ERR_ARG, "bad head counts %d/%d", Hq, Hkv);
+  B200P_REQUIRE(B >= 0 && L >= 0 && Tcap > 0, B200P_ERR_ARG, "bad shape");
+  B200P_REQUIRE(dtype >= 0 && dtype <= 2, B200P_ERR_ARG, "bad dtype %d", dtype);
+  if (B * L == 0) return B200P_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool tc_ok = attn_decode_supported(L, Hq, Hkv, D, dtype);
+  if (g_attn_path == 2) B200P_REQUIRE(tc_ok, B200P_ERR_ARG, "tensor attention forced but unsupported for this call");
+  if (tc_ok && g_attn_path != 1) {
+    B200P_REQUIRE(workspace && workspace_bytes >= attn_decode_workspace_bytes(B, L, Hq, D), B200P_ERR_ARG,
+                  "attention needs a workspace of %zu bytes", attn_decode_workspace_bytes(B, L, Hq, D));
+    return attn_decode_launch(q, kcache, vcache, lengths, out, B, L, Hq, Hkv, D, Tcap, scale, dtype, workspace,
+                              workspace_bytes, st);
+  }
+  return attn_generic_launch(q, kcache, vcache, lengths, out, B, L, Hq, Hkv, D, Tcap, scale, dtype, st);
+}

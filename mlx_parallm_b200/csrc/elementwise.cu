@@ -1,0 +1,286 @@
+// dequantize / embedding gather / RMSNorm / RoPE + KV append / argmax.
+// All HBM- or latency-bound byte work: one pass, 128-bit accesses, no tensor cores.
+#include "common.cuh"
+
+namespace b200p {
+
+// ------------------------------------------------------------------------------------------------
+// dequantize: out[n,k] = q*s + b under one of three rounding recipes (include/b200p.h B200P_DQ_*)
+// ------------------------------------------------------------------------------------------------
+template <typename T, int MODE>
+__device__ __forceinline__ float dq_one(uint32_t q, float s, float b) {
+  float qf = u8_to_float(q);
+  if (MODE == B200P_DQ_F32_MULADD) {
+    return __fadd_rn(__fmul_rn(qf, s), b);
+  } else if (MODE == B200P_DQ_FMA) {
+    return __fmaf_rn(qf, s, b);
+  } else {
+    float p = Tr<T>::to_f(Tr<T>::from_f(__fmul_rn(qf, s)));
+    return __fadd_rn(p, b);
+  }
+}
+
+// one thread per packed uint32 word; row index comes from `rows` (gather) or is the identity.
+template <typename T, int BITS, int MODE, typename OUT>
+__global__ void __launch_bounds__(256)
+dequant_kernel(const uint32_t* __restrict__ w, const T* __restrict__ scales,
+               const T* __restrict__ biases, OUT* __restrict__ out,
+               const int32_t* __restrict__ rows, int64_t n_rows, int64_t V, int64_t K, int gs) {
+  constexpr int PER = 32 / BITS;
+  const int64_t words_per_row = K / PER;
+  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n_rows * words_per_row) return;
+  int64_t r = idx / words_per_row;
+  int64_t wi = idx - r * words_per_row;
+  int64_t src = rows ? (int64_t)rows[r] : r;
+  if (src < 0 || src >= V) src = 0;  // out-of-vocab ids read row 0 (MLX would index modulo/UB)
+  uint32_t word = w[src * words_per_row + wi];
+  int64_t k0 = wi * PER;
+  int64_t g = k0 / gs;
+  float s = Tr<T>::to_f(scales[src * (K / gs) + g]);
+  float b = Tr<T>::to_f(biases[src * (K / gs) + g]);
+  __align__(16) OUT vals[PER];
+#pragma unroll
+  for (int j = 0; j < PER; ++j) {
+    uint32_t q = (word >> (j * BITS)) & ((1u << BITS) - 1u);
+    float v = dq_one<T, MODE>(q, s, b);
+    T vt = Tr<T>::from_f(v);  // storage rounding always happens
+    vals[j] = Tr<OUT>::from_f(Tr<T>::to_f(vt));
+  }
+  OUT* dst = out + r * K + k0;
+  constexpr int BYTES = PER * sizeof(OUT);
+  if (BYTES % 16 == 0) {
+#pragma unroll
+    for (int j = 0; j < BYTES / 16; ++j) reinterpret_cast<uint4*>(dst)[j] = reinterpret_cast<uint4*>(vals)[j];
+  } else {
+#pragma unroll
+    for (int j = 0; j < BYTES / 8; ++j) reinterpret_cast<uint2*>(dst)[j] = reinterpret_cast<uint2*>(vals)[j];
+  }
+}
+
+template <typename T, typename OUT>
+static int launch_dequant(const uint32_t* w, const void* scales, const void* biases, void* out,
+                          const int32_t* rows, int64_t n_rows, int64_t V, int64_t K, int gs, int bits,
+                          int mode, cudaStream_t st) {
+  const int per = 32 / bits;
+  int64_t total = n_rows * (K / per);
+  if (total == 0) return B200P_OK;
+  dim3 grid((unsigned)((total + 255) / 256)), block(256);
+#define L(B_, M_)                                                                                   \
+  dequant_kernel<T, B_, M_, OUT><<<grid, block, 0, st>>>(w, (const T*)scales, (const T*)biases,      \
+                                                         (OUT*)out, rows, n_rows, V, K, gs)
+  if (bits == 4) {
+    if (mode == 0) L(4, 0); else if (mode == 1) L(4, 1); else L(4, 2);
+  } else {
+    if (mode == 0) L(8, 0); else if (mode == 1) L(8, 1); else L(8, 2);
+  }
+#undef L
+  B200P_LAUNCH_CHECK("dequant_kernel");
+  return B200P_OK;
+}
+
+static int check_quant_args(const void* w, const void* s, const void* b, int64_t K, int gs, int bits, int mode) {
+  B200P_REQUIRE(w && s && b, B200P_ERR_ARG, "null quantized-weight pointer");
+  B200P_REQUIRE(bits == 4 || bits == 8, B200P_ERR_ARG, "bits must be 4 or 8, got %d", bits);
+  B200P_REQUIRE(gs >= 32 && gs % 32 == 0 && K % gs == 0, B200P_ERR_ARG,
+                "group_size %d must be a multiple of 32 dividing K=%lld", gs, (long long)K);
+  B200P_REQUIRE(mode >= 0 && mode <= 2, B200P_ERR_ARG, "bad dequantize mode %d", mode);
+  B200P_REQUIRE(aligned(w, 16), B200P_ERR_ALIGN, "w must be 16-byte aligned");
+  return B200P_OK;
+}
+
+}  // namespace b200p
+
+using namespace b200p;
+
+extern "C" int b200p_dequantize(const uint32_t* w, const void* scales, const void* biases, void* out,
+                                int64_t N, int64_t K, int group_size, int bits, int dtype, int mode,
+                                void* stream) {
+  int rc = check_quant_args(w, scales, biases, K, group_size, bits, mode);
+  if (rc) return rc;
+  B200P_REQUIRE(out && aligned(out, 16), B200P_ERR_ALIGN, "out must be non-null and 16-byte aligned");
+  B200P_REQUIRE(N >= 0, B200P_ERR_ARG, "N < 0");
+  B200P_DISPATCH_DTYPE(dtype, T, return (launch_dequant<T, T>(w, scales, biases, out, nullptr, N, N, K,
+                                                              group_size, bits, mode, (cudaStream_t)stream)));
+  return B200P_OK;
+}
+
+extern "C" int b200p_embed(const int32_t* ids, const uint32_t* w, const void* scales, const void* biases,
+                           void* out, int64_t M, int64_t V, int64_t K, int group_size, int bits, int dtype,
+                           int mode, int out_f32, void* stream) {
+  int rc = check_quant_args(w, scales, biases, K, group_size, bits, mode);
+  if (rc) return rc;
+  B200P_REQUIRE(ids && out && aligned(out, 16), B200P_ERR_ALIGN, "ids/out must be non-null, out 16-byte aligned");
+  if (out_f32) {
+    B200P_DISPATCH_DTYPE(dtype, T, return (launch_dequant<T, float>(w, scales, biases, out, ids, M, V, K,
+                                                                    group_size, bits, mode, (cudaStream_t)stream)));
+  } else {
+    B200P_DISPATCH_DTYPE(dtype, T, return (launch_dequant<T, T>(w, scales, biases, out, ids, M, V, K,
+                                                                group_size, bits, mode, (cudaStream_t)stream)));
+  }
+  return B200P_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// RMSNorm: fp32 residual row -> dtype row.  One CTA per row.
+// ------------------------------------------------------------------------------------------------
+namespace b200p {
+
+__device__ __forceinline__ float block_sum(float v, float* sh) {
+  v = warp_sum(v);
+  int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  if (lane == 0) sh[wid] = v;
+  __syncthreads();
+  float t = (threadIdx.x < nw) ? sh[threadIdx.x] : 0.f;
+  if (wid == 0) {
+    t = warp_sum(t);
+    if (lane == 0) sh[32] = t;
+  }
+  __syncthreads();
+  float r = sh[32];
+  __syncthreads();
+  return r;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+rmsnorm_kernel(const float* __restrict__ x, const T* __restrict__ w, T* __restrict__ y, int64_t H, float eps) {
+  __shared__ float sh[33];
+  pdl_wait();
+  const float* xr = x + (int64_t)blockIdx.x * H;
+  T* yr = y + (int64_t)blockIdx.x * H;
+  float ss = 0.f;
+  const int64_t H4 = H / 4;
+  for (int64_t i = threadIdx.x; i < H4; i += blockDim.x) {
+    float4 v = reinterpret_cast<const float4*>(xr)[i];
+    ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+  }
+  for (int64_t i = H4 * 4 + threadIdx.x; i < H; i += blockDim.x) ss += xr[i] * xr[i];
+  ss = block_sum(ss, sh);
+  float inv = 1.0f / sqrtf(ss / (float)H + eps);
+  pdl_launch_dependents();
+  for (int64_t i = threadIdx.x; i < H4; i += blockDim.x) {
+    float4 v = reinterpret_cast<const float4*>(xr)[i];
+    __align__(16) T o[4];
+    o[0] = Tr<T>::from_f(v.x * inv * Tr<T>::to_f(w[4 * i + 0]));
+    o[1] = Tr<T>::from_f(v.y * inv * Tr<T>::to_f(w[4 * i + 1]));
+    o[2] = Tr<T>::from_f(v.z * inv * Tr<T>::to_f(w[4 * i + 2]));
+    o[3] = Tr<T>::from_f(v.w * inv * Tr<T>::to_f(w[4 * i + 3]));
+    if (sizeof(T) == 2) reinterpret_cast<uint2*>(yr)[i] = *reinterpret_cast<uint2*>(o);
+    else reinterpret_cast<uint4*>(yr)[i] = *reinterpret_cast<uint4*>(o);
+  }
+  for (int64_t i = H4 * 4 + threadIdx.x; i < H; i += blockDim.x)
+    yr[i] = Tr<T>::from_f(xr[i] * inv * Tr<T>::to_f(w[i]));
+}
+
+}  // namespace b200p
+
+extern "C" int b200p_rmsnorm(const float* x, const void* w, void* y, int64_t M, int64_t H, float eps,
+                             int dtype, void* stream) {
+  B200P_REQUIRE(x && w && y, B200P_ERR_ARG, "null pointer");
+  B200P_REQUIRE(aligned(x, 16) && aligned(y, 16) && H % 4 == 0, B200P_ERR_ALIGN,
+                "rmsnorm needs 16-byte aligned rows (H %% 4 == 0)");
+  if (M == 0) return B200P_OK;
+  B200P_DISPATCH_DTYPE(dtype, T, (rmsnorm_kernel<T><<<(unsigned)M, 256, 0, (cudaStream_t)stream>>>(
+                                     x, (const T*)w, (T*)y, H, eps)));
+  B200P_LAUNCH_CHECK("rmsnorm_kernel");
+  return B200P_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// (qwen3 q/k head RMSNorm) + RoPE (non-traditional pairing i, i+D/2) + KV-cache append.
+// grid = (B*L, Hq + 2*Hkv); block = D/2 threads, thread i owns the pair (i, i + D/2).
+// ------------------------------------------------------------------------------------------------
+namespace b200p {
+
+template <typename T>
+__global__ void rope_kv_append_kernel(const T* __restrict__ qkv, T* __restrict__ q_out, T* __restrict__ kc,
+                                      T* __restrict__ vc, const int32_t* __restrict__ lengths,
+                                      const T* __restrict__ qn_w, const T* __restrict__ kn_w, int L, int Hq,
+                                      int Hkv, int D, int64_t Tcap, float log2_base, float rope_scale,
+                                      float eps) {
+  __shared__ float sh[33];
+  pdl_wait();
+  const int tok = blockIdx.x;  // b*L + l
+  const int b = tok / L, l = tok - b * L;
+  const int head = blockIdx.y;
+  const int half = D >> 1;
+  const int i = threadIdx.x;
+  const int64_t row_stride = (int64_t)(Hq + 2 * Hkv) * D;
+  const T* src = qkv + (int64_t)tok * row_stride + (int64_t)head * D;
+  const int pos_i = lengths[b] + l;
+  const bool act = i < half;  // block is padded to whole warps
+  float x1 = act ? Tr<T>::to_f(src[i]) : 0.f;
+  float x2 = act ? Tr<T>::to_f(src[i + half]) : 0.f;
+  if (head >= Hq + Hkv) {  // V head: plain append
+    int hv = head - Hq - Hkv;
+    if (pos_i < Tcap && act) {
+      T* dst = vc + (((int64_t)b * Hkv + hv) * Tcap + pos_i) * D;
+      dst[i] = src[i];
+      dst[i + half] = src[i + half];
+    }
+    return;
+  }
+  const bool is_q = head < Hq;
+  const T* nw = is_q ? qn_w : kn_w;
+  if (nw != nullptr) {  // mx.fast.rms_norm over head_dim (qwen3.py:65-70), rounded to storage type
+    float ss = block_sum(x1 * x1 + x2 * x2, sh);
+    float inv = 1.0f / sqrtf(ss / (float)D + eps);
+    if (act) {
+      x1 = Tr<T>::to_f(Tr<T>::from_f(x1 * inv * Tr<T>::to_f(nw[i])));
+      x2 = Tr<T>::to_f(Tr<T>::from_f(x2 * inv * Tr<T>::to_f(nw[i + half])));
+    }
+  }
+  if (!act) return;
+  // theta = pos * scale * base^(-i/half)
+  float inv_freq = exp2f(-(float)i * (log2_base / (float)half));
+  float ang = (float)pos_i * rope_scale * inv_freq;
+  float sn, cs;
+  sincosf(ang, &sn, &cs);
+  float o1 = x1 * cs - x2 * sn;
+  float o2 = x1 * sn + x2 * cs;
+  if (is_q) {
+    T* dst = q_out + ((int64_t)tok * Hq + head) * D;
+    dst[i] = Tr<T>::from_f(o1);
+    dst[i + half] = Tr<T>::from_f(o2);
+  } else if (pos_i < Tcap) {
+    int hk = head - Hq;
+    T* dst = kc + (((int64_t)b * Hkv + hk) * Tcap + pos_i) * D;
+    dst[i] = Tr<T>::from_f(o1);
+    dst[i + half] = Tr<T>::from_f(o2);
+  }
+}
+
+__global__ void advance_lengths_kernel(int32_t* lengths, int64_t B, int32_t delta) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < B) lengths[i] += delta;
+}
+
+}  // namespace b200p
+
+extern "C" int b200p_rope_kv_append(const void* qkv, void* q_out, void* kcache, void* vcache,
+                                    const int32_t* lengths, const void* q_norm_w, const void* k_norm_w,
+                                    int64_t B, int64_t L, int Hq, int Hkv, int D, int64_t Tcap,
+                                    float rope_base, float rope_scale, float norm_eps, int dtype,
+                                    void* stream) {
+  B200P_REQUIRE(qkv && q_out && kcache && vcache && lengths, B200P_ERR_ARG, "null pointer");
+  B200P_REQUIRE(D >= 2 && D % 2 == 0 && D <= 2048, B200P_ERR_ARG, "head_dim %d unsupported", D);
+  B200P_REQUIRE(Hq > 0 && Hkv > 0 && Hq % Hkv == 0, B200P_ERR_ARG, "bad head counts %d/%d", Hq, Hkv);
+  B200P_REQUIRE(B * L < (1ll << 31) && Hq + 2 * Hkv < 65536, B200P_ERR_ARG, "grid too large");
+  if (B * L == 0) return B200P_OK;
+  dim3 grid((unsigned)(B * L), (unsigned)(Hq + 2 * Hkv)), block(((D / 2 + 31) / 32) * 32);
+  B200P_DISPATCH_DTYPE(dtype, T, (rope_kv_append_kernel<T><<<grid, block, 0, (cudaStream_t)stream>>>(
+                                     (const T*)qkv, (T*)q_out, (T*)kcache, (T*)vcache, lengths,
+                                     (const T*)q_norm_w, (const T*)k_norm_w, (int)L, Hq, Hkv, D, Tcap,
+                                     log2f(rope_base), rope_scale, norm_eps)));
+  B200P_LAUNCH_CHECK("rope_kv_append_kernel");
+  return B200P_OK;
+}
+
+extern "C" int b200p_advance_lengths(int32_t* lengths, int64_t B, int32_t delta, void* stream) {
+  B200P_REQUIRE(lengths, B200P_ERR_ARG, "null lengths");
+  if (B == 0) return B200P_OK;
+  advance_lengths_kernel<<<(unsigned)((B + 255) / 256), 256, 0, (cudaStream_t)stream>>>(lengths, B, delta);
+  B200P_LAUNCH_CHECK("advance_lengths_kernel");
+  return B200P_OK;
+}

@@ -1,0 +1,407 @@
+"""Shared decoder implementation behind models/llama.py and models/qwen3.py.
+
+Same module tree, parameter names and call signatures as the reference graphs
+(mlx_parallm/models/llama.py:49-271, mlx_parallm/models/qwen3.py:23-226), re-hosted on the
+sm_100a kernels of libb200parallm.so:
+
+    embed (gather+dequant)                                   b200p_embed
+    per layer:  RMSNorm                                      b200p_rmsnorm
+                fused q|k|v projection                       b200p_qmm (EPI_STORE)
+                (q/k head norm) + RoPE + KV append           b200p_rope_kv_append
+                GQA attention over the cache                 b200p_attn
+                o_proj + residual                            b200p_qmm (EPI_ADD_RESIDUAL)
+                RMSNorm                                      b200p_rmsnorm
+                fused gate|up projection + silu*mul          b200p_qmm (EPI_SILU_MUL)
+                down_proj + residual                         b200p_qmm (EPI_ADD_RESIDUAL)
+    final RMSNorm + lm_head (float32 logits)                 b200p_rmsnorm, b200p_qmm (EPI_STORE_F32)
+
+The residual stream is float32 (the reference's stream is float32 from layer 0 on because
+PagedKVCache promotes); GEMM inputs and the KV cache are the model's 16-bit storage
+type.  Tensor parallelism (column-split q/k/v/gate/up, row-split o/down, vocab-split head) is
+applied at load time by ``tp.shard_*`` and adds one all-reduce after each row-split projection.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional
+
+import torch
+
+from .. import ops
+from .._lib import EPI_ADD_RESIDUAL, EPI_SILU_MUL, EPI_STORE, EPI_STORE_F32
+from .base import BatchedKVCache, PagedKVCache
+
+MAX_TOKENS_PER_FORWARD = 8192     # chunk size (B*L) of one prefill pass through the layers
+
+
+class QuantizedLinear:
+    """nn.QuantizedLinear stand-in: weight uint32 [N, K*bits/32] (held as int32), scales/biases [N, K/gs]."""
+
+    def __init__(self, in_features: int, out_features: int, group_size: int = 64, bits: int = 4):
+        self.in_features, self.out_features = in_features, out_features
+        self.group_size, self.bits = group_size, bits
+        self.weight = self.scales = self.biases = None
+
+    def set(self, weight, scales, biases):
+        self.weight, self.scales, self.biases = weight, scales, biases
+        self.out_features = weight.shape[0]
+        self.in_features = weight.shape[1] * 32 // self.bits
+
+    def __call__(self, x, epilogue=EPI_STORE, out=None, workspace=None):
+        lead = x.shape[:-1]
+        y = ops.qmm(x.reshape(-1, x.shape[-1]), self.weight, self.scales, self.biases, self.group_size,
+                    self.bits, epilogue, out, workspace)
+        return y if out is not None else y.reshape(*lead, -1)
+
+
+class QuantizedEmbedding(QuantizedLinear):
+    """nn.QuantizedEmbedding stand-in (llama.py:212; .as_linear for tied heads, llama.py:250)."""
+
+    def embed(self, ids_i32, out=None):
+        return ops.embed(ids_i32, self.weight, self.scales, self.biases, self.group_size, self.bits, out=out)
+
+    def as_linear(self, x, **kw):
+        return QuantizedLinear.__call__(self, x, **kw)
+
+
+class RMSNorm:
+    def __init__(self, dims: int, eps: float):
+        self.weight = None
+        self.eps = eps
+        self.dims = dims
+
+
+class Attention:
+    def __init__(self, args, head_dim: int, qk_norm: bool):
+        self.n_heads = args.num_attention_heads
+        self.n_kv_heads = args.num_key_value_heads
+        self.head_dim = head_dim
+        self.scale = head_dim ** -0.5
+        gs, bits = args._group_size, args._bits
+        h = args.hidden_size
+        self.q_proj = QuantizedLinear(h, self.n_heads * head_dim, gs, bits)
+        self.k_proj = QuantizedLinear(h, self.n_kv_heads * head_dim, gs, bits)
+        self.v_proj = QuantizedLinear(h, self.n_kv_heads * head_dim, gs, bits)
+        self.o_proj = QuantizedLinear(self.n_heads * head_dim, h, gs, bits)
+        self.qkv_proj = QuantizedLinear(h, (self.n_heads + 2 * self.n_kv_heads) * head_dim, gs, bits)
+        self.q_norm = RMSNorm(head_dim, args.rms_norm_eps) if qk_norm else None
+        self.k_norm = RMSNorm(head_dim, args.rms_norm_eps) if qk_norm else None
+
+
+class MLP:
+    def __init__(self, args):
+        gs, bits = args._group_size, args._bits
+        h, inter = args.hidden_size, args.intermediate_size
+        self.gate_proj = QuantizedLinear(h, inter, gs, bits)
+        self.up_proj = QuantizedLinear(h, inter, gs, bits)
+        self.down_proj = QuantizedLinear(inter, h, gs, bits)
+        self.gate_up_proj = QuantizedLinear(h, 2 * inter, gs, bits)
+
+
+class TransformerBlock:
+    def __init__(self, args, head_dim: int, qk_norm: bool):
+        self.self_attn = Attention(args, head_dim, qk_norm)
+        self.mlp = MLP(args)
+        self.input_layernorm = RMSNorm(args.hidden_size, args.rms_norm_eps)
+        self.post_attention_layernorm = RMSNorm(args.hidden_size, args.rms_norm_eps)
+        self.args = args
+
+
+class DecoderStack:
+    """LlamaModel / Qwen3Model (llama.py:194-231, qwen3.py:146-185)."""
+
+    def __init__(self, args, head_dim: int, qk_norm: bool):
+        self.args = args
+        self.vocab_size = args.vocab_size
+        self.num_hidden_layers = args.num_hidden_layers
+        assert self.vocab_size > 0
+        self.embed_tokens = QuantizedEmbedding(args.hidden_size, args.vocab_size, args._group_size, args._bits)
+        self.layers = [TransformerBlock(args, head_dim, qk_norm) for _ in range(args.num_hidden_layers)]
+        self.norm = RMSNorm(args.hidden_size, args.rms_norm_eps)
+
+
+def _fuse_rows(parts: List[QuantizedLinear], fused: QuantizedLinear):
+    """Concatenate row blocks into one MLX-layout matrix and re-point the parts at views of it."""
+    w = torch.cat([p.weight for p in parts], 0).contiguous()
+    s = torch.cat([p.scales for p in parts], 0).contiguous()
+    b = torch.cat([p.biases for p in parts], 0).contiguous()
+    fused.set(w, s, b)
+    r = 0
+    for p in parts:
+        n = p.weight.shape[0]
+        p.set(w[r:r + n], s[r:r + n], b[r:r + n])
+        r += n
+
+
+class DecoderModel:
+    """``Model`` of the reference: callable(inputs[B,L], cache=None) -> logits [B, L, V] (float32)."""
+
+    qk_norm = False
+
+    def __init__(self, args):
+        self.args = args
+        self.model_type = args.model_type
+        q = getattr(args, "quantization", None) or {}
+        args._group_size = q.get("group_size", 64)
+        args._bits = q.get("bits", 4)
+        hd = self._head_dim(args)
+        self._hd = hd
+        self.model = DecoderStack(args, hd, self.qk_norm)
+        self.lm_head = None
+        if not args.tie_word_embeddings:
+            self.lm_head = QuantizedLinear(args.hidden_size, args.vocab_size, args._group_size, args._bits)
+        self.dtype: Optional[torch.dtype] = None
+        self.device: Optional[torch.device] = None
+        self._arenas: Dict[int, dict] = {}
+        self.tp_rank, self.tp_world, self.tp_group = 0, 1, None
+        self._allreduce = None
+        rs = getattr(args, "rope_scaling", None)
+        self.rope_scale = 1.0
+        if rs and (rs.get("type") == "linear" or rs.get("rope_type") == "linear"):
+            self.rope_scale = 1.0 / rs["factor"]                        # llama.py:69-76
+
+    # -- reference properties ----------------------------------------------------------------
+    @staticmethod
+    def _head_dim(args) -> int:
+        return args.hidden_size // args.num_attention_heads              # llama.py:55
+
+    @property
+    def layers(self):
+        return self.model.layers
+
+    @property
+    def head_dim(self):
+        return self._hd
+
+    @property
+    def n_kv_heads(self):
+        """KV heads held by THIS rank (what a cache for this model instance must be built with)."""
+        return self.model.layers[0].self_attn.n_kv_heads
+
+    def sanitize(self, weights):
+        return {k: v for k, v in weights.items() if "self_attn.rotary_emb.inv_freq" not in k}   # llama.py:254-258
+
+    def eval(self):
+        return self
+
+    # -- parameters ----------------------------------------------------------------------------
+    def parameter_names(self) -> List[str]:
+        names = []
+        for pre in ["model.embed_tokens"] + (["lm_head"] if self.lm_head is not None else []):
+            names += [f"{pre}.{s}" for s in ("weight", "scales", "biases")]
+        names.append("model.norm.weight")
+        for i in range(len(self.model.layers)):
+            p = f"model.layers.{i}."
+            for proj in ("self_attn.q_proj", "self_attn.k_proj", "self_attn.v_proj", "self_attn.o_proj",
+                         "mlp.gate_proj", "mlp.up_proj", "mlp.down_proj"):
+                names += [f"{p}{proj}.{s}" for s in ("weight", "scales", "biases")]
+            names += [p + "input_layernorm.weight", p + "post_attention_layernorm.weight"]
+            if self.qk_norm:
+                names += [p + "self_attn.q_norm.weight", p + "self_attn.k_norm.weight"]
+        return names
+
+    def _module(self, path: str):
+        obj = self
+        for part in path.split("."):
+            obj = obj[int(part)] if part.isdigit() else getattr(obj, part)
+        return obj
+
+    def load_weights(self, weights: Dict[str, torch.Tensor], device="cuda", strict: bool = True):
+        """Take MLX-format tensors (utils.py:654-708 key naming), move them to the device, fuse q|k|v and
+        gate|up row blocks.  Under TP the tensors must already be this rank's shards (tp.shard_weights)."""
+        device = torch.device(device)
+        missing = [n for n in self.parameter_names() if n not in weights]
+        if missing and strict:
+            raise KeyError(f"missing parameters: {missing[:4]}{'...' if len(missing) > 4 else ''}")
+        dts = {weights[n].dtype for n in self.parameter_names() if n in weights and n.endswith(".scales")}
+        if len(dts) != 1:
+            raise TypeError(f"scales must share one dtype, got {dts}")
+        self.dtype = dts.pop()
+        self.device = device
+
+        def put(t):
+            if t.dtype == torch.uint32:
+                t = t.view(torch.int32)
+            return t.to(device).contiguous()
+
+        groups: Dict[str, dict] = {}
+        for name in self.parameter_names():
+            if name not in weights:
+                continue
+            mod, leaf = name.rsplit(".", 1)
+            groups.setdefault(mod, {})[leaf] = put(weights[name])
+        for mod, g in groups.items():
+            m = self._module(mod)
+            if isinstance(m, QuantizedLinear):
+                m.set(g["weight"], g["scales"], g["biases"])
+            else:
+                m.weight = g["weight"].to(self.dtype)
+        for layer in self.model.layers:
+            a, f = layer.self_attn, layer.mlp
+            a.n_heads = a.q_proj.weight.shape[0] // a.head_dim          # local (TP-sharded) head counts
+            a.n_kv_heads = a.k_proj.weight.shape[0] // a.head_dim
+            _fuse_rows([a.q_proj, a.k_proj, a.v_proj], a.qkv_proj)
+            _fuse_rows([f.gate_proj, f.up_proj], f.gate_up_proj)
+        self._arenas.clear()
+        return self
+
+    def set_tensor_parallel(self, rank: int, world: int, allreduce):
+        """allreduce(tensor_f32) sums in place across ranks on the current stream."""
+        self.tp_rank, self.tp_world, self._allreduce = rank, world, allreduce
+
+    # -- sampling heads (overridden by the vocab-parallel variant in tp.py) ------------------------
+    def graph_safe(self, B: int) -> bool:
+        """A decode step of batch B runs only graph-capturable b200p kernels (no interim dense GEMM)."""
+        if B <= ops.DENSE_INTERIM_MIN_M:
+            return True
+        head = self.lm_head if self.lm_head is not None else self.model.embed_tokens
+        from .._lib import lib
+        return bool(lib().b200p_qmm_tensor_supported(B, head.out_features, head.in_features, head.group_size,
+                                                    head.bits, ops.dtype_code(self.dtype), EPI_STORE_F32))
+
+    def greedy_tokens(self, logits, tok_out, probs_out=None):
+        """mx.argmax(logits, -1) (utils.py:352) into static buffers."""
+        ops.argmax(logits, out=tok_out, probs_out=probs_out)
+
+    def sample_tokens(self, logits, temp, top_p, seed, offset, tok_out, probs_out=None):
+        """top_p_sampling / categorical(logits / temp) (utils.py:354-361)."""
+        ops.sample_top_p(logits, temp, top_p, seed, offset, out=tok_out, probs_out=probs_out)
+
+    # -- caches ----------------------------------------------------------------------------------
+    def make_cache(self, batch_size: int, step: Optional[int] = None, paged: bool = True) -> List[BatchedKVCache]:
+        klass = PagedKVCache if paged else BatchedKVCache
+        caches = [klass(self.head_dim, l.self_attn.n_kv_heads, batch_size) for l in self.model.layers]
+        bind_cache_group(caches, self.device, step)
+        return caches
+
+    # -- scratch ---------------------------------------------------------------------------------
+    def _arena(self, M: int, B: int) -> dict:
+        key = (M, B)
+        a = self._arenas.get(key)
+        if a is None:
+            dev, dt, args = self.device, self.dtype, self.args
+            att = self.model.layers[0].self_attn
+            inter_local = self.model.layers[0].mlp.down_proj.in_features
+            nqkv = (att.n_heads + 2 * att.n_kv_heads) * att.head_dim
+            head = self.lm_head if self.lm_head is not None else self.model.embed_tokens
+            dims = [(nqkv, args.hidden_size), (args.hidden_size, att.n_heads * att.head_dim),
+                    (2 * inter_local, args.hidden_size), (args.hidden_size, inter_local),
+                    (head.out_features, args.hidden_size)]
+            ws = max(max(ops.qmm_workspace_bytes(M, n, k) for n, k in dims),
+                     ops.attn_workspace_bytes(B, M // B, att.n_heads, att.head_dim), 16)
+            a = dict(
+                h=torch.empty((M, args.hidden_size), dtype=torch.float32, device=dev),
+                x=torch.empty((M, args.hidden_size), dtype=dt, device=dev),
+                qkv=torch.empty((M, nqkv), dtype=dt, device=dev),
+                q=torch.empty((M, att.n_heads * att.head_dim), dtype=dt, device=dev),
+                att=torch.empty((M, att.n_heads * att.head_dim), dtype=dt, device=dev),
+                act=torch.empty((M, inter_local), dtype=dt, device=dev),
+                xl=torch.empty((M, args.hidden_size), dtype=dt, device=dev),
+                ws=torch.empty((ws,), dtype=torch.uint8, device=dev),
+            )
+            if len(self._arenas) > 8:
+                self._arenas.clear()
+            self._arenas[key] = a
+        return a
+
+    # -- forward ---------------------------------------------------------------------------------
+    def _layers_forward(self, ids_i32: torch.Tensor, B: int, L: int, cache: List[BatchedKVCache], a: dict):
+        """Run embed + all blocks for B*L tokens whose rows sit at cache lengths + [0, L)."""
+        args = self.args
+        self.model.embed_tokens.embed(ids_i32, out=a["h"])
+        tp = self.tp_world > 1
+        for layer, c in zip(self.model.layers, cache):
+            at, mlp = layer.self_attn, layer.mlp
+            lengths = c.lengths(self.device)
+            ops.rmsnorm(a["h"], layer.input_layernorm.weight, layer.input_layernorm.eps, out=a["x"])
+            at.qkv_proj(a["x"], EPI_STORE, out=a["qkv"], workspace=a["ws"])
+            ops.rope_kv_append(a["qkv"], a["q"], c.keys, c.values, lengths, B, L, at.n_heads, at.n_kv_heads,
+                               at.head_dim, args.rope_theta, self.rope_scale,
+                               at.q_norm.weight if at.q_norm else None, at.k_norm.weight if at.k_norm else None,
+                               args.rms_norm_eps)
+            ops.attn(a["q"], c.keys, c.values, lengths, a["att"], B, L, at.n_heads, at.n_kv_heads, at.head_dim,
+                     at.scale, workspace=a["ws"])
+            if tp and self.tp_rank != 0:
+                a["h"].zero_()
+            at.o_proj(a["att"], EPI_ADD_RESIDUAL, out=a["h"], workspace=a["ws"])
+            if tp:
+                self._allreduce(a["h"])
+            ops.rmsnorm(a["h"], layer.post_attention_layernorm.weight, layer.post_attention_layernorm.eps, out=a["x"])
+            mlp.gate_up_proj(a["x"], EPI_SILU_MUL, out=a["act"], workspace=a["ws"])
+            if tp and self.tp_rank != 0:
+                a["h"].zero_()
+            mlp.down_proj(a["act"], EPI_ADD_RESIDUAL, out=a["h"], workspace=a["ws"])
+            if tp:
+                self._allreduce(a["h"])
+
+    def _head(self, h_rows: torch.Tensor, a: dict, logits_out: Optional[torch.Tensor] = None):
+        """final RMSNorm + lm_head / tied embed_tokens.as_linear (llama.py:231,249-252) -> float32 logits."""
+        n = self.model.norm
+        rows = h_rows.shape[0]
+        x = ops.rmsnorm(h_rows, n.weight, n.eps, out=a["xl"][:rows])
+        head = self.lm_head if self.lm_head is not None else self.model.embed_tokens
+        return QuantizedLinear.__call__(head, x, EPI_STORE_F32, out=logits_out, workspace=a["ws"])
+
+    def __call__(self, inputs, cache: Optional[List[BatchedKVCache]] = None, last_only: bool = False):
+        """inputs int [B, L] -> logits float32 [B, L, V] (or [B, 1, V] with last_only, the only rows
+        generate_step reads, utils.py:404 / SURVEY B10).  Under TP the vocab axis is this rank's shard."""
+        if not isinstance(inputs, torch.Tensor):
+            inputs = torch.as_tensor(inputs)
+        inputs = inputs.to(self.device)
+        B, L = inputs.shape
+        ids = inputs.to(torch.int32).contiguous()
+        own_cache = cache is None
+        if own_cache:
+            cache = self.make_cache(B, step=max(L, 1))
+        prepare_cache(cache, B, L, self.dtype, self.device)
+        Lc = max(1, min(L, MAX_TOKENS_PER_FORWARD // B))
+        outs = []
+        for l0 in range(0, L, Lc):
+            l1 = min(L, l0 + Lc)
+            n = l1 - l0
+            a = self._arena(B * n, B)
+            chunk = ids[:, l0:l1].contiguous().view(-1)
+            self._layers_forward(chunk, B, n, cache, a)
+            advance_cache(cache, n)
+            if last_only:
+                if l1 == L:
+                    last_h = a["h"] if n == 1 else a["h"].view(B, n, -1)[:, -1, :].contiguous()
+                    return self._head(last_h, a).view(B, 1, -1)
+            else:
+                outs.append(self._head(a["h"], a).view(B, n, -1))
+        return outs[0] if len(outs) == 1 else torch.cat(outs, 1)
+
+
+# ---------------------------------------------------------------------------------------------------
+def bind_cache_group(caches: List[BatchedKVCache], device, step: Optional[int] = None):
+    """Make all layers of one generation share a single device lengths tensor."""
+    if not caches:
+        return
+    B = caches[0].batch_size
+    shared = torch.zeros((B,), dtype=torch.int32, device=device)
+    for c in caches:
+        if step is not None:
+            c.step = step
+        c.share_lengths(shared)
+        c._sync_lengths()
+
+
+def prepare_cache(caches: List[BatchedKVCache], B: int, L: int, dtype, device) -> bool:
+    """Ensure every layer can take L more tokens per row.  Returns True if any buffer moved."""
+    moved = False
+    for c in caches:
+        assert c.batch_size == B, "KV cache batch size mismatch"
+        need = (max(c._offsets) if c._offsets else 0) + L
+        moved |= c.ensure_capacity(need, dtype, device)
+        c.lengths(device)
+    return moved
+
+
+def advance_cache(caches: List[BatchedKVCache], L: int):
+    """lengths += L once per distinct device tensor; host mirrors on every layer."""
+    seen = set()
+    for c in caches:
+        t = c._lengths
+        if t.data_ptr() not in seen:
+            seen.add(t.data_ptr())
+            ops.advance_lengths(t, L)
+        c.advance_host(L)

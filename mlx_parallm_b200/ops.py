@@ -1,0 +1,182 @@
+"""Thin torch-tensor wrappers over the C-ABI (include/b200p.h).
+
+torch is plumbing here: device memory, the current stream, CUDA-graph capture.  Every function
+launches hand-written sm_100a kernels from libb200parallm.so on ``torch.cuda.current_stream()``;
+none of them has a CPU or eager-PyTorch fallback -- a CPU tensor raises.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import (DQ_F32_MULADD, EPI_ADD_RESIDUAL, EPI_SILU_MUL, EPI_STORE, EPI_STORE_F32, check, lib)
+
+_DT = {torch.float32: _lib.F32, torch.float16: _lib.F16, torch.bfloat16: _lib.BF16}
+
+
+def dtype_code(dt: torch.dtype) -> int:
+    try:
+        return _DT[dt]
+    except KeyError:
+        raise TypeError(f"unsupported storage dtype {dt}") from None
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _dev(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise _lib.B200PError("b200p ops need CUDA tensors: there is no CPU fallback")
+
+
+def _p(t: Optional[torch.Tensor]) -> int:
+    return 0 if t is None else t.data_ptr()
+
+
+# ------------------------------------------------------------------------------------------------
+def dequantize(w, scales, biases, group_size=64, bits=4, mode=DQ_F32_MULADD, out=None):
+    """mx.dequantize: w int32/uint32 [N, K*bits/32] -> [N, K] in scales.dtype."""
+    _dev(w, scales, biases)
+    N = w.shape[0]
+    K = w.shape[1] * 32 // bits
+    if out is None:
+        out = torch.empty((N, K), dtype=scales.dtype, device=w.device)
+    check(lib().b200p_dequantize(_p(w), _p(scales), _p(biases), _p(out), N, K, group_size, bits,
+                                 dtype_code(scales.dtype), mode, _stream()), "b200p_dequantize")
+    return out
+
+
+def embed(ids, w, scales, biases, group_size=64, bits=4, mode=DQ_F32_MULADD, out=None, out_f32=True):
+    """QuantizedEmbedding.__call__: ids int32 [M] -> [M, K] (float32 carrier of dtype-rounded values)."""
+    _dev(ids, w, scales, biases)
+    assert ids.dtype == torch.int32 and ids.is_contiguous()
+    M = ids.numel()
+    V = w.shape[0]
+    K = w.shape[1] * 32 // bits
+    if out is None:
+        out = torch.empty((M, K), dtype=torch.float32 if out_f32 else scales.dtype, device=w.device)
+    check(lib().b200p_embed(_p(ids), _p(w), _p(scales), _p(biases), _p(out), M, V, K, group_size, bits,
+                            dtype_code(scales.dtype), mode, 1 if out_f32 else 0, _stream()), "b200p_embed")
+    return out
+
+
+def qmm_workspace_bytes(M, N, K) -> int:
+    return int(lib().b200p_qmm_workspace_bytes(M, N, K))
+
+
+def qmm(x, w, scales, biases, group_size=64, bits=4, epilogue=EPI_STORE, out=None, workspace=None):
+    """quantized_matmul(x, w, scales, biases, transpose=True) with a fused epilogue.
+
+    x [M, K] (row stride = x.stride(0)); out per epilogue:
+      EPI_STORE -> [M, N] x.dtype; EPI_STORE_F32 -> [M, N] float32; EPI_ADD_RESIDUAL -> out (float32
+      [M, N], required) += result; EPI_SILU_MUL -> [M, N/2] x.dtype."""
+    _dev(x, w, scales, biases, out)
+    assert x.dim() == 2 and x.stride(1) == 1
+    M, K = x.shape
+    N = w.shape[0]
+    assert w.shape[1] * 32 // bits == K, (w.shape, K, bits)
+    if out is None:
+        if epilogue == EPI_STORE:
+            out = torch.empty((M, N), dtype=x.dtype, device=x.device)
+        elif epilogue == EPI_STORE_F32:
+            out = torch.empty((M, N), dtype=torch.float32, device=x.device)
+        elif epilogue == EPI_SILU_MUL:
+            out = torch.empty((M, N // 2), dtype=x.dtype, device=x.device)
+        else:
+            raise ValueError("EPI_ADD_RESIDUAL needs the residual tensor as `out`")
+    if M > DENSE_INTERIM_MIN_M and not lib().b200p_qmm_tensor_supported(M, N, K, group_size, bits, dtype_code(x.dtype), epilogue):
+        return _qmm_dense_interim(x, w, scales, biases, group_size, bits, epilogue, out)
+    ws_ptr, ws_bytes = (0, 0) if workspace is None else (workspace.data_ptr(), workspace.numel() * workspace.element_size())
+    check(lib().b200p_qmm(_p(x), _p(w), _p(scales), _p(biases), _p(out), M, N, K, x.stride(0), out.stride(0),
+                          group_size, bits, dtype_code(x.dtype), epilogue, ws_ptr, ws_bytes, _stream()), "b200p_qmm")
+    return out
+
+
+# INTERIM (prefill only, SURVEY 8f-2 "next" row): until the tcgen05 tile kernel covers a shape, large-M
+# calls dequantise with our kernel and hand the dense GEMM to cuBLAS through torch.matmul.  The decode
+# hot path (M <= DENSE_INTERIM_MIN_M) never comes here.
+DENSE_INTERIM_MIN_M = 64
+
+
+def _qmm_dense_interim(x, w, scales, biases, group_size, bits, epilogue, out):
+    wd = dequantize(w, scales, biases, group_size, bits, mode=_lib.DQ_FMA)
+    if x.dtype == torch.float32:
+        acc = x @ wd.t()
+    else:
+        acc = torch.matmul(x, wd.t()).float() if epilogue != EPI_STORE else torch.matmul(x, wd.t())
+    if epilogue == EPI_STORE:
+        out.copy_(acc)
+    elif epilogue == EPI_STORE_F32:
+        out.copy_(acc)
+    elif epilogue == EPI_ADD_RESIDUAL:
+        out.add_(acc)
+    else:
+        n2 = acc.shape[1] // 2
+        out.copy_(torch.nn.functional.silu(acc[:, :n2]) * acc[:, n2:])
+    return out
+
+
+def rmsnorm(x, w, eps, out=None):
+    """mx.fast.rms_norm on the float32 residual stream -> w.dtype."""
+    _dev(x, w, out)
+    assert x.dtype == torch.float32 and x.is_contiguous()
+    M, H = x.shape
+    if out is None:
+        out = torch.empty((M, H), dtype=w.dtype, device=x.device)
+    check(lib().b200p_rmsnorm(_p(x), _p(w), _p(out), M, H, float(eps), dtype_code(w.dtype), _stream()), "b200p_rmsnorm")
+    return out
+
+
+def rope_kv_append(qkv, q_out, kcache, vcache, lengths, B, L, Hq, Hkv, D, rope_base, rope_scale=1.0,
+                   q_norm_w=None, k_norm_w=None, norm_eps=1e-6):
+    _dev(qkv, q_out, kcache, vcache, lengths)
+    assert lengths.dtype == torch.int32
+    Tcap = kcache.shape[2]
+    check(lib().b200p_rope_kv_append(_p(qkv), _p(q_out), _p(kcache), _p(vcache), _p(lengths), _p(q_norm_w),
+                                     _p(k_norm_w), B, L, Hq, Hkv, D, Tcap, float(rope_base), float(rope_scale),
+                                     float(norm_eps), dtype_code(qkv.dtype), _stream()), "b200p_rope_kv_append")
+
+
+def advance_lengths(lengths, delta: int):
+    _dev(lengths)
+    check(lib().b200p_advance_lengths(_p(lengths), lengths.numel(), int(delta), _stream()), "b200p_advance_lengths")
+
+
+def attn_workspace_bytes(B, L, Hq, D) -> int:
+    return int(lib().b200p_attn_workspace_bytes(B, L, Hq, D))
+
+
+def attn(q, kcache, vcache, lengths, out, B, L, Hq, Hkv, D, scale, workspace=None):
+    _dev(q, kcache, vcache, lengths, out)
+    Tcap = kcache.shape[2]
+    ws_ptr, ws_bytes = (0, 0) if workspace is None else (workspace.data_ptr(), workspace.numel() * workspace.element_size())
+    check(lib().b200p_attn(_p(q), _p(kcache), _p(vcache), _p(lengths), _p(out), B, L, Hq, Hkv, D, Tcap, float(scale),
+                           dtype_code(q.dtype), ws_ptr, ws_bytes, _stream()), "b200p_attn")
+    return out
+
+
+def argmax(logits, out=None, probs_out=None):
+    """mx.argmax(logits, -1): float32 [B, V] -> int32 [B]."""
+    _dev(logits, out, probs_out)
+    assert logits.dtype == torch.float32 and logits.dim() == 2 and logits.stride(1) == 1
+    B, V = logits.shape
+    if out is None:
+        out = torch.empty((B,), dtype=torch.int32, device=logits.device)
+    check(lib().b200p_argmax(_p(logits), _p(out), _p(probs_out), B, V, logits.stride(0), _stream()), "b200p_argmax")
+    return out
+
+
+def sample_top_p(logits, temperature, top_p, seed, offset, out=None, probs_out=None):
+    _dev(logits, out, probs_out)
+    assert logits.dtype == torch.float32 and logits.dim() == 2 and logits.stride(1) == 1
+    B, V = logits.shape
+    if out is None:
+        out = torch.empty((B,), dtype=torch.int32, device=logits.device)
+    check(lib().b200p_sample_top_p(_p(logits), _p(out), _p(probs_out), B, V, logits.stride(0), float(temperature),
+                                   float(top_p), int(seed) & (2**64 - 1), int(offset) & (2**64 - 1), _stream()),
+          "b200p_sample_top_p")
+    return out

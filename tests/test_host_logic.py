@@ -1,0 +1,97 @@
+"""Host-side logic that needs no GPU: args, caches, byte model, synthetic checkpoints, detokenizer."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from mlx_parallm_b200 import synth
+from mlx_parallm_b200.models import llama, qwen3
+from mlx_parallm_b200.models.base import BatchedKVCache, PagedKVCache
+from mlx_parallm_b200.tokenizer_utils import NaiveStreamingDetokenizer, TokenizerWrapper
+
+
+def test_model_args_from_dict_drops_unknown_keys_and_defaults():
+    cfg = synth.get_config("mistral-7b")                 # carries sliding_window, which ModelArgs lacks
+    a = llama.ModelArgs.from_dict(cfg)
+    assert a.num_key_value_heads == 8 and not hasattr(a, "sliding_window")
+    cfg2 = {k: v for k, v in cfg.items() if k not in ("num_key_value_heads", "tie_word_embeddings")}
+    a2 = llama.ModelArgs.from_dict(cfg2)
+    assert a2.num_key_value_heads == 32 and a2.tie_word_embeddings is True     # llama.py:30,33-34
+    with pytest.raises(ValueError):
+        llama.ModelArgs.from_dict(dict(cfg, rope_scaling={"type": "linear"}))   # no 'factor'
+    with pytest.raises(ValueError):
+        llama.ModelArgs.from_dict(dict(cfg, rope_scaling={"type": "yarn", "factor": 2}))
+    q = qwen3.ModelArgs.from_dict(synth.get_config("qwen3-14b"))
+    assert q.head_dim == 128
+
+
+def test_byte_model_matches_baseline_md():
+    gb = lambda n: synth.weight_bytes_per_step(synth.get_config(n)) / 1e9
+    assert gb("mistral-7b") == pytest.approx(4.000, abs=2e-3)
+    assert gb("llama-3-8b") == pytest.approx(4.222, abs=2e-3)
+    assert gb("qwen3-14b") == pytest.approx(7.870, abs=2e-3)
+    assert gb("llama-3-70b") == pytest.approx(73.848, abs=2e-3)
+    assert synth.kv_bytes_per_token(synth.get_config("llama-3-8b")) == 131072
+    assert synth.kv_bytes_per_token(synth.get_config("qwen3-14b")) == 163840
+    assert synth.kv_bytes_per_token(synth.get_config("llama-3-70b")) == 327680
+
+
+@pytest.mark.parametrize("klass", [BatchedKVCache, PagedKVCache])
+def test_cache_surface_on_cpu_tensors(klass):
+    c = klass(8, 2, batch_size=3)
+    assert c.keys is None and c.offset == 0 and c.step == 256 and c.offsets == [0, 0, 0]
+    c.step = 4
+    k = torch.arange(3 * 2 * 3 * 8, dtype=torch.float32).reshape(3, 2, 3, 8)
+    kf, vf = c.update_and_fetch(k, -k)
+    assert kf.shape == (3, 2, 3, 8) and c.keys.shape[2] == 4 and c.offsets == [3, 3, 3] and c.offset == 3
+    assert torch.equal(kf, k) and torch.equal(vf, -k)
+    kf, _ = c.update_and_fetch(k[:, :, :2], k[:, :, :2])
+    assert kf.shape[2] == 5 and c.keys.shape[2] == 8 and torch.equal(kf[:, :, :3], k)
+    assert c.lengths("cpu").tolist() == [5, 5, 5]
+    buf = c.keys
+    c.reset()
+    assert c.offsets == [0, 0, 0] and c.keys is buf and c.lengths("cpu").tolist() == [0, 0, 0]
+    c.reset(2)
+    assert c.keys is None and c.batch_size == 2 and c.offsets == [0, 0]
+
+
+def test_synthetic_checkpoint_roundtrip(tmp_path):
+    cfg = synth.get_config("tiny-llama")
+    w = synth.random_weights(cfg, seed=5, dtype="bfloat16")
+    w2 = synth.random_weights(cfg, seed=5, dtype="bfloat16", only=lambda n: "layers.1." in n)
+    assert all(torch.equal(w[k], v) for k, v in w2.items()) and len(w2) == 7 * 3 + 2
+    synth.save_checkpoint(str(tmp_path), cfg, w)
+    from safetensors import safe_open
+    with safe_open(os.path.join(tmp_path, "model.safetensors"), framework="pt") as f:
+        assert f.metadata() == {"format": "mlx"}
+        t = f.get_tensor("model.layers.0.mlp.down_proj.weight")
+        assert t.dtype == torch.uint32 and t.shape == (128, 256 * 4 // 32)
+        assert f.get_tensor("model.layers.0.mlp.down_proj.scales").shape == (128, 4)
+    assert json.load(open(os.path.join(tmp_path, "config.json")))["quantization"] == {"group_size": 64, "bits": 4}
+
+
+class _FakeTok:
+    eos_token_id = 0
+    eos_token = "<eos>"
+    pad_token = None
+
+    def decode(self, ids, **kw):
+        return "".join(chr(96 + i) if i else "<eos>" for i in ids)
+
+
+def test_streaming_detokenizer_and_wrapper_passthrough():
+    tw = TokenizerWrapper(_FakeTok())
+    assert tw.eos_token_id == 0 and tw._tokenizer.eos_token == "<eos>" and tw.eos_token_ids == {0}
+    d = tw.detokenizer
+    d.reset()
+    segs = []
+    for t in (1, 2, 3):
+        d.add_token(t)
+        segs.append(d.last_segment)
+    d.finalize()
+    segs.append(d.last_segment)
+    assert "".join(segs) == "abc" == d.text and d.tokens == [1, 2, 3]
+    tw.pad_token = "<eos>"                                 # setattr passes through (utils.py:513-515)
+    assert tw._tokenizer.pad_token == "<eos>"
