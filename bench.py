@@ -1,0 +1,387 @@
+#!/usr/bin/env python
+"""bench.py -- decode tok/s of the batched decode step (BASELINE.json metric), one JSON line on rank 0.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload ...]
+
+N == 1: Llama-3-8B architecture, MLX 4-bit group-64, batch 64, 8192-token KV context (BASELINE.json
+configs[2], the configuration the metric is quoted on), random-init weights + synthetic KV (no network).
+N  > 1: the same workload tensor-parallel over N ranks (strong scaling), launched by torch.distributed.run.
+
+A "step" = one decode step of the whole batch: embed -> 32 blocks -> head -> argmax, KV append included.
+  value   device-timed tok/s (CUDA events around K graph replays, inputs resident in HBM)
+  e2e     the same step driven with HOST token buffers: pinned H2D of the step's ids + D2H of its result
+  roofline  dominant kernel (by bytes) timed with CUDA events in an eager instrumented pass
+  cpu_baseline  the oracle (numpy port of the reference path) on a bounded sample, rank 0, N == 1 only
+--impl reference times that CPU port alone (MLX itself is not installable here: see DESIGN.md).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "decode_tokens_per_sec"
+UNIT = "tok/s"
+
+WORKLOADS = {
+    # name: (config, batch, context tokens)
+    "llama3-8b-4bit-b64-t8192": ("llama-3-8b", 64, 8192),
+    "llama3-8b-4bit-b64-t256": ("llama-3-8b", 64, 256),
+    "llama3-8b-4bit-b8-t8192": ("llama-3-8b", 8, 8192),
+    "llama3-8b-4bit-b1-t8192": ("llama-3-8b", 1, 8192),
+    "mistral-7b-4bit-b8-t256": ("mistral-7b", 8, 256),
+    "qwen3-14b-4bit-b64-t256": ("qwen3-14b", 64, 256),
+    "small": ("small-llama", 4, 64),
+}
+HEADLINE = "llama3-8b-4bit-b64-t8192"
+DEFAULT_SWEEP = ["llama3-8b-4bit-b64-t256", "llama3-8b-4bit-b8-t8192", "llama3-8b-4bit-b1-t8192"]
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, gpu_index: int):
+        self.rows, self.proc, self.idx = [], None, gpu_index
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = max([int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()] or [0])
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 7 for n, v in zip(names, r[3:7]) if v.lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": reasons, "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------ our arm
+def build_model(cfg_name, device, tp_rank=0, tp_world=1, seed=1234):
+    import torch
+    from mlx_parallm_b200 import synth
+    from mlx_parallm_b200.utils import _get_classes
+    cfg = synth.get_config(cfg_name)
+    w = synth.random_weights(cfg, seed=seed, dtype="float16", device=device)
+    if tp_world > 1:
+        from mlx_parallm_b200 import tp
+        w = tp.shard_weights(w, cfg, tp_rank, tp_world)
+    Model, Args = _get_classes(cfg)
+    model = Model(Args.from_dict(cfg)).load_weights(w, device=device)
+    del w
+    torch.cuda.empty_cache()
+    return cfg, model
+
+
+def make_session(model, B, T, extra, seed=7):
+    """KV cache holding T synthetic context tokens per row (capacity T + extra) and a decode session."""
+    import torch
+    from mlx_parallm_b200.utils import DecodeSession
+    cache = model.make_cache(B, step=T + extra)
+    g = torch.Generator(device=model.device)
+    g.manual_seed(seed)
+    for c in cache:
+        c.ensure_capacity(T + extra, model.dtype, model.device)
+        # synthetic context: decode-step cost does not depend on the values; unit-scale keys keep softmax sane
+        c.keys.normal_(0.0, 0.3, generator=g)
+        c.values.normal_(0.0, 0.3, generator=g)
+        c.offsets_list = [T] * B
+        c.offset = T
+    sess = DecodeSession(model, cache, B, greedy=True)
+    sess.tok.copy_(torch.randint(0, model.args.vocab_size, (B,), generator=g, device=model.device, dtype=torch.int32))
+    return cache, sess
+
+
+def time_steps(sess, steps, warmup, dist=None):
+    import torch
+    for _ in range(warmup):
+        sess.run()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+        torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        sess.run()
+    e1.record()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    ms = e0.elapsed_time(e1)
+    if dist is not None:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms / steps
+
+
+def time_e2e(sess, steps, warmup, dist=None):
+    """Same step through host buffers: pinned H2D of the ids, graph replay, D2H of the sampled ids, every step."""
+    import torch
+    B = sess.B
+    h_in = torch.zeros((B,), dtype=torch.int32).pin_memory()
+    h_out = torch.zeros((B,), dtype=torch.int32).pin_memory()
+    h_in.copy_(sess.tok.cpu())
+
+    def one():
+        sess.tok.copy_(h_in, non_blocking=True)
+        sess.run()
+        h_out.copy_(sess.tok, non_blocking=True)
+        torch.cuda.current_stream().synchronize()      # the caller reads the ids on the host
+        h_in.copy_(h_out)
+
+    for _ in range(warmup):
+        one()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        one()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if dist is not None:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms / steps, 4 * B, 4 * B
+
+
+def kernel_profile(sess, steps=3):
+    """Eager (no graph) instrumented pass: CUDA events around every b200p launch -> mean ms per kernel kind and
+    launches per step."""
+    import torch
+    from mlx_parallm_b200 import ops
+    saved = sess.use_graph
+    sess.use_graph = False
+    sess.run()
+    torch.cuda.synchronize()
+    ops.PROFILER = {}
+    n0 = ops.LAUNCHES
+    for _ in range(steps):
+        sess.run()
+    torch.cuda.synchronize()
+    prof, ops.PROFILER = ops.PROFILER, None
+    launches = (ops.LAUNCHES - n0) // steps
+    sess.use_graph = saved
+    out = {}
+    for k, evs in prof.items():
+        ts = [s.elapsed_time(e) for s, e in evs]
+        out[k] = {"calls_per_step": len(ts) // steps, "mean_ms": sum(ts) / len(ts), "total_ms_per_step": sum(ts) / steps}
+    return out, launches
+
+
+def run_workload(name, model, cfg, steps, warmup, tp_world, dist, with_profile, hbm_peak):
+    import torch
+    from mlx_parallm_b200 import synth
+    _, B, T = WORKLOADS[name]
+    extra = 2 * (warmup + steps) + 64
+    cache, sess = make_session(model, B, T, extra)
+    ms = time_steps(sess, steps, warmup, dist)
+    t_mid = T + warmup + steps / 2.0
+    w_bytes = synth.weight_bytes_per_step(cfg)
+    kv_tok = synth.kv_bytes_per_token(cfg)
+    step_bytes = w_bytes + B * t_mid * kv_tok
+    res = {"workload": name, "batch": B, "context": T, "ms_per_step": ms, "tok_s": B / ms * 1e3,
+           "bytes_per_step": step_bytes, "step_gbs_per_gpu": step_bytes / tp_world / ms / 1e6,
+           "step_frac_of_hbm_peak": step_bytes / tp_world / ms / 1e6 / hbm_peak}
+    if with_profile:
+        e2e_ms, h2d, d2h = time_e2e(sess, steps, warmup, dist)
+        res["e2e"] = {"ms_per_step": e2e_ms, "tok_s": B / e2e_ms * 1e3, "h2d": h2d, "d2h": d2h}
+        prof, launches = kernel_profile(sess)
+        res["kernels"] = prof
+        res["launches_per_step"] = launches
+        # dominant kernel by algorithmic bytes
+        t_now = cache[0].offset
+        attn_bytes = B * t_now * kv_tok / cfg["num_hidden_layers"] / tp_world        # per launch (one layer)
+        kinds = {"b200p_attn": attn_bytes}
+        inter, h = cfg["intermediate_size"], cfg["hidden_size"]
+        bits, gs = cfg["quantization"]["bits"], cfg["quantization"]["group_size"]
+        for k in prof:
+            if k.startswith("b200p_qmm[N="):
+                n_, k_ = (int(v.split("=")[1]) for v in k[len("b200p_qmm["):-1].split(","))
+                kinds[k] = n_ * k_ * bits / 8 + 2 * n_ * (k_ // gs) * 2
+        per_step = {k: kinds[k] * prof[k]["calls_per_step"] for k in kinds if k in prof}
+        dom = max(per_step, key=per_step.get)
+        ach = kinds[dom] / (prof[dom]["mean_ms"] * 1e-3) / 1e9
+        res["roofline"] = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
+                           "frac": ach / hbm_peak, "traffic": None,
+                           "algorithmic_bytes_per_launch": kinds[dom],
+                           "share_of_step_time": prof[dom]["total_ms_per_step"] / sum(v["total_ms_per_step"] for v in prof.values())}
+    del sess, cache
+    torch.cuda.empty_cache()
+    return res
+
+
+# ------------------------------------------------------------------------------------------ CPU arm
+def cpu_reference(cfg_name, B, T, budget_layers=1, repeats=1, seed=1234):
+    """The oracle (numpy restatement of the reference's decode step) timed on the host cores on a bounded
+    sample: `budget_layers` transformer blocks + the head at the full batch and context; the full-model step
+    is extrapolated as t_layer * L + t_head (the reference's step is L identical blocks + head)."""
+    import numpy as np
+    import torch
+    from mlx_parallm_b200 import synth
+    from oracle.model import OracleConfig, OracleModel
+    cfg = synth.get_config(cfg_name)
+    L = cfg["num_hidden_layers"]
+    sub = dict(cfg, num_hidden_layers=budget_layers)
+    w = synth.random_weights(sub, seed=seed, dtype="float16", device="cpu")
+    om = OracleModel(OracleConfig.from_hf(sub, "float16"), synth.to_numpy_weights(w), numerics="reference")
+    rng = np.random.default_rng(7)
+    cache = om.make_cache(B)
+    for c in cache:
+        c.step = T + 8
+        c._ensure(T + 8)
+        c.keys[:, :, :T] = rng.standard_normal((1, c.n_kv_heads, T, c.head_dim), dtype=np.float32) * 0.3
+        c.values[:, :, :T] = rng.standard_normal((1, c.n_kv_heads, T, c.head_dim), dtype=np.float32) * 0.3
+        c.offsets_list = [T] * B
+    ids = rng.integers(0, cfg["vocab_size"], (B, 1))
+    om.forward(ids, cache, last_only=True)                     # warm: builds the dequantised weight cache
+    # time blocks+head, then head alone (0-layer model shares the weights dict)
+    t0 = time.perf_counter()
+    for _ in range(repeats):
+        om.forward(ids, cache, last_only=True)
+    t_all = (time.perf_counter() - t0) / repeats
+    om0 = OracleModel(OracleConfig.from_hf(dict(cfg, num_hidden_layers=0), "float16"), om.w, numerics="reference")
+    om0._deq_cache = om._deq_cache
+    t0 = time.perf_counter()
+    for _ in range(max(repeats, 2)):
+        om0.forward(ids, [], last_only=True)
+    t_head = (time.perf_counter() - t0) / max(repeats, 2)
+    t_layer = max(t_all - t_head, 1e-9) / budget_layers
+    t_step = t_layer * L + t_head
+    return {"value": B / t_step, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
+            "sample": f"{budget_layers} of {L} blocks + head at B={B}, T={T}, numpy/BLAS threads={os.cpu_count()}; "
+                      f"t_layer={t_layer * 1e3:.1f} ms, t_head={t_head * 1e3:.1f} ms, extrapolated t_layer*{L}+t_head",
+            "ms_per_step": t_step * 1e3}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=32)
+    ap.add_argument("--warmup", type=int, default=4)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=HEADLINE)
+    ap.add_argument("--sweep", default=",".join(DEFAULT_SWEEP), help="comma list of extra workloads ('' = none)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    cfg_name, B, T = WORKLOADS[args.workload]
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        cb = cpu_reference(cfg_name, B, T, repeats=max(1, min(args.steps, 3)))
+        line = {"metric": METRIC, "value": cb["value"], "unit": UNIT, "impl": "reference", "n_gpus": args.gpus,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": args.workload, "batch": B, "context": T,
+                           "note": "reference arithmetic lives in mlx==0.25.2 (not installable offline); this is the numpy port of the same step"},
+                "cpu_baseline": cb,
+                "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return
+
+    import torch
+    from mlx_parallm_b200 import _lib, ops
+    torch.cuda.set_device(local_rank)
+    _lib.require_device()
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist = dist_mod
+    hbm_peak, peak_src = peaks()
+    cfg, model = build_model(cfg_name, f"cuda:{local_rank}", rank, world)
+    if world > 1:
+        from mlx_parallm_b200 import tp
+        tp.attach(model, dist, rank, world)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    main_res = run_workload(args.workload, model, cfg, args.steps, args.warmup, world, dist, True, hbm_peak)
+    clocks = sampler.stop()
+    sweep = []
+    for name in [s for s in args.sweep.split(",") if s and s != args.workload]:
+        cn = WORKLOADS[name][0]
+        if cn != cfg_name:
+            del model
+            torch.cuda.empty_cache()
+            cfg, model = build_model(cn, f"cuda:{local_rank}", rank, world)
+            if world > 1:
+                tp.attach(model, dist, rank, world)
+            cfg_name = cn
+        try:
+            r = run_workload(name, model, cfg, max(8, args.steps // 2), args.warmup, world, dist, False, hbm_peak)
+            sweep.append({k: r[k] for k in ("workload", "ms_per_step", "tok_s", "step_frac_of_hbm_peak")})
+        except Exception as ex:  # a sweep entry must not sink the headline line
+            sweep.append({"workload": name, "error": str(ex)[:200]})
+    cb = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            cb = cpu_reference(WORKLOADS[args.workload][0], B, T)
+        except Exception as ex:
+            cb = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {ex}"[:200]}
+    if rank == 0:
+        rf = main_res["roofline"]
+        line = {"metric": METRIC, "value": main_res["tok_s"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": main_res["ms_per_step"], "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f16 storage / f32 accumulate (4-bit g64 weights)",
+                "data": "synthetic (random-init MLX-format weights, synthetic KV context)",
+                "config": {"workload": args.workload, "batch": B, "context": T, "parallelism": f"tp{world}",
+                           "l2_policy": "inputs larger than L2 (weights 4.2 GB + KV >> 126 MB are re-streamed every step)"},
+                "e2e": {"value": main_res["e2e"]["tok_s"], "unit": UNIT, "h2d_bytes_per_step": main_res["e2e"]["h2d"],
+                        "d2h_bytes_per_step": main_res["e2e"]["d2h"], "ms_per_step": main_res["e2e"]["ms_per_step"]},
+                "gpu_launches": main_res["launches_per_step"] * args.steps,
+                "roofline": {k: rf[k] for k in ("bound", "achieved", "peak", "unit", "frac", "traffic")},
+                "roofline_detail": {"kernel": rf["kernel"], "peak_source": peak_src,
+                                    "algorithmic_bytes_per_launch": rf["algorithmic_bytes_per_launch"],
+                                    "share_of_step_time": rf["share_of_step_time"],
+                                    "step_bytes": main_res["bytes_per_step"],
+                                    "step_frac_of_hbm_peak": main_res["step_frac_of_hbm_peak"],
+                                    "step_frac_of_8TBs_nominal": main_res["step_gbs_per_gpu"] / 8000.0},
+                "kernels": {k: {"calls": v["calls_per_step"], "mean_us": round(v["mean_ms"] * 1e3, 2)} for k, v in main_res["kernels"].items()},
+                "clocks": clocks, "sweep": sweep}
+        if cb is not None:
+            line["cpu_baseline"] = cb
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -37,6 +37,26 @@ def _p(t: Optional[torch.Tensor]) -> int:
     return 0 if t is None else t.data_ptr()
 
 
+# ---- launch accounting / optional per-kernel CUDA-event timing (bench.py, profiles/) ----------------
+LAUNCHES = 0            # b200p kernel-launching calls issued from Python (captured ones count once)
+PROFILER = None         # set to a dict name -> list[(start_event, end_event)] to time each call
+
+
+def _call(name: str, rc_fn):
+    """Run one C-ABI launch; count it; bracket it with events when a profiler is attached."""
+    global LAUNCHES
+    LAUNCHES += 1
+    if PROFILER is None:
+        check(rc_fn(), name if isinstance(name, str) else name[0])
+        return
+    key = name if isinstance(name, str) else f"{name[0]}[N={name[1]},K={name[2]}]"
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    check(rc_fn(), key)
+    e.record()
+    PROFILER.setdefault(key, []).append((s, e))
+
+
 # ------------------------------------------------------------------------------------------------
 def dequantize(w, scales, biases, group_size=64, bits=4, mode=DQ_F32_MULADD, out=None):
     """mx.dequantize: w int32/uint32 [N, K*bits/32] -> [N, K] in scales.dtype."""
@@ -45,8 +65,8 @@ def dequantize(w, scales, biases, group_size=64, bits=4, mode=DQ_F32_MULADD, out
     K = w.shape[1] * 32 // bits
     if out is None:
         out = torch.empty((N, K), dtype=scales.dtype, device=w.device)
-    check(lib().b200p_dequantize(_p(w), _p(scales), _p(biases), _p(out), N, K, group_size, bits,
-                                 dtype_code(scales.dtype), mode, _stream()), "b200p_dequantize")
+    _call("b200p_dequantize", lambda: lib().b200p_dequantize(_p(w), _p(scales), _p(biases), _p(out), N, K, group_size, bits,
+                                 dtype_code(scales.dtype), mode, _stream()))
     return out
 
 
@@ -59,8 +79,8 @@ def embed(ids, w, scales, biases, group_size=64, bits=4, mode=DQ_F32_MULADD, out
     K = w.shape[1] * 32 // bits
     if out is None:
         out = torch.empty((M, K), dtype=torch.float32 if out_f32 else scales.dtype, device=w.device)
-    check(lib().b200p_embed(_p(ids), _p(w), _p(scales), _p(biases), _p(out), M, V, K, group_size, bits,
-                            dtype_code(scales.dtype), mode, 1 if out_f32 else 0, _stream()), "b200p_embed")
+    _call("b200p_embed", lambda: lib().b200p_embed(_p(ids), _p(w), _p(scales), _p(biases), _p(out), M, V, K, group_size, bits,
+                            dtype_code(scales.dtype), mode, 1 if out_f32 else 0, _stream()))
     return out
 
 
@@ -91,8 +111,8 @@ def qmm(x, w, scales, biases, group_size=64, bits=4, epilogue=EPI_STORE, out=Non
     if M > DENSE_INTERIM_MIN_M and not lib().b200p_qmm_tensor_supported(M, N, K, group_size, bits, dtype_code(x.dtype), epilogue):
         return _qmm_dense_interim(x, w, scales, biases, group_size, bits, epilogue, out)
     ws_ptr, ws_bytes = (0, 0) if workspace is None else (workspace.data_ptr(), workspace.numel() * workspace.element_size())
-    check(lib().b200p_qmm(_p(x), _p(w), _p(scales), _p(biases), _p(out), M, N, K, x.stride(0), out.stride(0),
-                          group_size, bits, dtype_code(x.dtype), epilogue, ws_ptr, ws_bytes, _stream()), "b200p_qmm")
+    _call(("b200p_qmm", N, K), lambda: lib().b200p_qmm(_p(x), _p(w), _p(scales), _p(biases), _p(out), M, N, K, x.stride(0), out.stride(0),
+                          group_size, bits, dtype_code(x.dtype), epilogue, ws_ptr, ws_bytes, _stream()))
     return out
 
 
@@ -127,7 +147,7 @@ def rmsnorm(x, w, eps, out=None):
     M, H = x.shape
     if out is None:
         out = torch.empty((M, H), dtype=w.dtype, device=x.device)
-    check(lib().b200p_rmsnorm(_p(x), _p(w), _p(out), M, H, float(eps), dtype_code(w.dtype), _stream()), "b200p_rmsnorm")
+    _call("b200p_rmsnorm", lambda: lib().b200p_rmsnorm(_p(x), _p(w), _p(out), M, H, float(eps), dtype_code(w.dtype), _stream()))
     return out
 
 
@@ -136,14 +156,14 @@ def rope_kv_append(qkv, q_out, kcache, vcache, lengths, B, L, Hq, Hkv, D, rope_b
     _dev(qkv, q_out, kcache, vcache, lengths)
     assert lengths.dtype == torch.int32
     Tcap = kcache.shape[2]
-    check(lib().b200p_rope_kv_append(_p(qkv), _p(q_out), _p(kcache), _p(vcache), _p(lengths), _p(q_norm_w),
+    _call("b200p_rope_kv_append", lambda: lib().b200p_rope_kv_append(_p(qkv), _p(q_out), _p(kcache), _p(vcache), _p(lengths), _p(q_norm_w),
                                      _p(k_norm_w), B, L, Hq, Hkv, D, Tcap, float(rope_base), float(rope_scale),
-                                     float(norm_eps), dtype_code(qkv.dtype), _stream()), "b200p_rope_kv_append")
+                                     float(norm_eps), dtype_code(qkv.dtype), _stream()))
 
 
 def advance_lengths(lengths, delta: int):
     _dev(lengths)
-    check(lib().b200p_advance_lengths(_p(lengths), lengths.numel(), int(delta), _stream()), "b200p_advance_lengths")
+    _call("b200p_advance_lengths", lambda: lib().b200p_advance_lengths(_p(lengths), lengths.numel(), int(delta), _stream()))
 
 
 def attn_workspace_bytes(B, L, Hq, D) -> int:
@@ -154,8 +174,8 @@ def attn(q, kcache, vcache, lengths, out, B, L, Hq, Hkv, D, scale, workspace=Non
     _dev(q, kcache, vcache, lengths, out)
     Tcap = kcache.shape[2]
     ws_ptr, ws_bytes = (0, 0) if workspace is None else (workspace.data_ptr(), workspace.numel() * workspace.element_size())
-    check(lib().b200p_attn(_p(q), _p(kcache), _p(vcache), _p(lengths), _p(out), B, L, Hq, Hkv, D, Tcap, float(scale),
-                           dtype_code(q.dtype), ws_ptr, ws_bytes, _stream()), "b200p_attn")
+    _call("b200p_attn", lambda: lib().b200p_attn(_p(q), _p(kcache), _p(vcache), _p(lengths), _p(out), B, L, Hq, Hkv, D, Tcap, float(scale),
+                           dtype_code(q.dtype), ws_ptr, ws_bytes, _stream()))
     return out
 
 
@@ -166,7 +186,7 @@ def argmax(logits, out=None, probs_out=None):
     B, V = logits.shape
     if out is None:
         out = torch.empty((B,), dtype=torch.int32, device=logits.device)
-    check(lib().b200p_argmax(_p(logits), _p(out), _p(probs_out), B, V, logits.stride(0), _stream()), "b200p_argmax")
+    _call("b200p_argmax", lambda: lib().b200p_argmax(_p(logits), _p(out), _p(probs_out), B, V, logits.stride(0), _stream()))
     return out
 
 
@@ -176,7 +196,6 @@ def sample_top_p(logits, temperature, top_p, seed, offset, out=None, probs_out=N
     B, V = logits.shape
     if out is None:
         out = torch.empty((B,), dtype=torch.int32, device=logits.device)
-    check(lib().b200p_sample_top_p(_p(logits), _p(out), _p(probs_out), B, V, logits.stride(0), float(temperature),
-                                   float(top_p), int(seed) & (2**64 - 1), int(offset) & (2**64 - 1), _stream()),
-          "b200p_sample_top_p")
+    _call("b200p_sample_top_p", lambda: lib().b200p_sample_top_p(_p(logits), _p(out), _p(probs_out), B, V, logits.stride(0), float(temperature),
+                                   float(top_p), int(seed) & (2**64 - 1), int(offset) & (2**64 - 1), _stream()))
     return out

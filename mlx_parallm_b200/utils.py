@@ -144,6 +144,9 @@ class _DecodeStep:
             c.advance_host(1)
 
 
+DecodeSession = _DecodeStep      # public name: one replayable decode step over a model + cache group
+
+
 def generate_step(
     prompts,
     model: DecoderModel,

@@ -216,8 +216,9 @@ def sdpa(q, k, v, scale: float, mask=None, dtype: str = "float32") -> np.ndarray
     B, Hq, Lq, D = q.shape
     Hkv = k.shape[1]
     G = Hq // Hkv
-    qg = q.reshape(B, Hkv, G, Lq, D)
-    s = np.einsum("bhgld,bhtd->bhglt", qg * np.float32(scale), k)
+    T = k.shape[2]
+    qg = (q * np.float32(scale)).reshape(B, Hkv, G * Lq, D)
+    s = np.matmul(qg, k.transpose(0, 1, 3, 2)).reshape(B, Hkv, G, Lq, T)
     if mask is not None:
         m = np.asarray(mask, np.float32)
         m = m.reshape(m.shape[0], 1, 1, *m.shape[-2:]) if m.ndim == 3 else m.reshape(1, 1, 1, *m.shape[-2:])
@@ -225,7 +226,7 @@ def sdpa(q, k, v, scale: float, mask=None, dtype: str = "float32") -> np.ndarray
     s = s - s.max(-1, keepdims=True)
     p = np.exp(s)
     p = p / p.sum(-1, keepdims=True)
-    o = np.einsum("bhglt,bhtd->bhgld", p, v).reshape(B, Hq, Lq, D)
+    o = np.matmul(p.reshape(B, Hkv, G * Lq, T), v).reshape(B, Hq, Lq, D)
     return round_to(o, dtype)
 
 

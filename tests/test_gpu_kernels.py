@@ -1,0 +1,261 @@
+"""Kernel-level parity: every C-ABI entry point against the oracle on the same seeded inputs."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import mlx_ops as ref
+from helpers import rel_err
+
+pytestmark = pytest.mark.gpu
+
+TD = {"float32": torch.float32, "float16": torch.float16, "bfloat16": torch.bfloat16}
+
+
+def t_(a, dtype):
+    return torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).to(TD[dtype]).cuda()
+
+
+def w_(a):
+    return torch.from_numpy(np.ascontiguousarray(a).view(np.int32)).cuda()
+
+
+def bits_of(t, dtype):
+    if dtype == "float32":
+        return t.cpu().numpy().view(np.uint32)
+    return t.cpu().view(torch.int16).numpy().view(np.uint16)
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from mlx_parallm_b200 import ops as o, _lib
+    _lib.require_device()
+    return o
+
+
+# ---------------------------------------------------------------- dequantize: bit-exact, all modes
+@pytest.mark.parametrize("bits", [4, 8])
+@pytest.mark.parametrize("dtype", ["float32", "float16", "bfloat16"])
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_dequantize_bit_exact_golden(ops, golden_dir, bits, dtype, mode):
+    g = np.load(os.path.join(golden_dir, "dequantize_bits.npz"))
+    out = ops.dequantize(w_(g[f"w_{bits}"]), t_(g[f"s_{bits}_{dtype}"], dtype), t_(g[f"b_{bits}_{dtype}"], dtype), 64, bits, mode)
+    assert np.array_equal(bits_of(out, dtype), g[f"out_{bits}_{dtype}_{mode}"])
+
+
+@pytest.mark.parametrize("bits,dtype", [(4, "float16"), (8, "bfloat16"), (4, "float32")])
+def test_dequantize_bit_exact_random_large(ops, bits, dtype):
+    rng = np.random.default_rng(11)
+    N, K = 257, 4096
+    wq = rng.integers(0, 2 ** 32, (N, K * bits // 32), dtype=np.uint32)
+    s = ref.round_to(rng.uniform(-0.02, 0.02, (N, K // 64)), dtype)
+    b = ref.round_to(rng.uniform(-0.2, 0.2, (N, K // 64)), dtype)
+    for mode in (0, 1, 2):
+        out = ops.dequantize(w_(wq), t_(s, dtype), t_(b, dtype), 64, bits, mode)
+        exp = ref.storage_bits(ref.dequantize(wq, s, b, 64, bits, dtype, mode), dtype)
+        assert np.array_equal(bits_of(out, dtype), exp), mode
+
+
+def test_dequantize_empty_and_embed_gather(ops):
+    rng = np.random.default_rng(12)
+    V, K = 300, 128
+    wq = rng.integers(0, 2 ** 32, (V, K // 8), dtype=np.uint32)
+    s = ref.round_to(rng.uniform(-0.02, 0.02, (V, 2)), "float16")
+    b = ref.round_to(rng.uniform(-0.2, 0.2, (V, 2)), "float16")
+    out = ops.dequantize(w_(wq[:0]), t_(s[:0], "float16"), t_(b[:0], "float16"))
+    assert out.shape == (0, K)
+    ids = np.array([5, 0, 299, 5, 17], np.int32)
+    e = ops.embed(torch.from_numpy(ids).cuda(), w_(wq), t_(s, "float16"), t_(b, "float16"))
+    exp = ref.dequantize(wq[ids], s[ids], b[ids], 64, 4, "float16")
+    assert e.dtype == torch.float32 and np.array_equal(e.cpu().numpy(), exp)
+
+
+# ---------------------------------------------------------------- quantized matmul
+def qmm_case(ops, M, N, K, bits, dtype, epi, seed=0, path=0, ragged_ld=False):
+    from mlx_parallm_b200 import _lib
+    rng = np.random.default_rng(seed)
+    wq = rng.integers(0, 2 ** 32, (N, K * bits // 32), dtype=np.uint32)
+    nb = (1 << bits) - 1
+    s = ref.round_to(rng.uniform(0.5, 1.5, (N, K // 64)) * rng.choice([-1, 1], (N, K // 64)) * (2 / nb) / np.sqrt(K), dtype)
+    b = ref.round_to(-s * nb / 2 + rng.normal(0, 0.01 / np.sqrt(K), (N, K // 64)), dtype)
+    x = ref.round_to(rng.standard_normal((M, K)), dtype)
+    acc = ref.quantized_matmul_grouped(x, wq, s, b, 64, bits) if M * N * K <= 2 ** 24 else \
+        ref.quantized_matmul(x, wq, s, b, 64, bits).astype(np.float64)
+    xt = t_(x, dtype)
+    if ragged_ld:
+        big = torch.zeros((M, K + 64), dtype=xt.dtype, device="cuda")
+        big[:, :K] = xt
+        xt = big[:, :K]
+    ws = torch.empty((max(ops.qmm_workspace_bytes(M, N, K), 16),), dtype=torch.uint8, device="cuda")
+    _lib.check(_lib.lib().b200p_qmm_set_path(path))
+    try:
+        if epi == _lib.EPI_ADD_RESIDUAL:
+            res = rng.standard_normal((M, N)).astype(np.float32)
+            out = torch.from_numpy(res.copy()).cuda()
+            ops.qmm(xt, w_(wq), t_(s, dtype), t_(b, dtype), 64, bits, epi, out=out, workspace=ws)
+            exp = res + acc
+        else:
+            out = ops.qmm(xt, w_(wq), t_(s, dtype), t_(b, dtype), 64, bits, epi, workspace=ws)
+            if epi == _lib.EPI_SILU_MUL:
+                g, u = acc[:, :N // 2], acc[:, N // 2:]
+                exp = g / (1 + np.exp(-g)) * u
+            else:
+                exp = acc
+    finally:
+        _lib.lib().b200p_qmm_set_path(0)
+    return out.float().cpu().numpy(), exp
+
+
+@pytest.mark.parametrize("dtype", ["float32", "float16", "bfloat16"])
+@pytest.mark.parametrize("bits", [4, 8])
+@pytest.mark.parametrize("M", [1, 3, 8])
+def test_qmv_store_matches_oracle(ops, dtype, bits, M):
+    got, exp = qmm_case(ops, M, 96, 512, bits, dtype, 0, seed=M, path=1)
+    tol = {"float32": 2e-5, "float16": 2e-3, "bfloat16": 1e-2}[dtype]     # output rounding of the storage type
+    assert rel_err(got, exp) < tol
+
+
+@pytest.mark.parametrize("epi", [1, 2, 3])
+def test_qmv_epilogues(ops, epi):
+    got, exp = qmm_case(ops, 5, 128, 256, 4, "float16", epi, seed=epi, path=1, ragged_ld=True)
+    assert rel_err(got, exp) < (2e-3 if epi == 3 else 2e-5)
+
+
+def test_qmv_tiny_model_shapes(ops):
+    # K = 64 (one group per row, tiny hidden) and K = 128 (tiny down_proj), float32 like config 1
+    for K in (64, 128):
+        got, exp = qmm_case(ops, 8, 64, K, 4, "float32", 1, seed=K, path=1)
+        assert rel_err(got, exp) < 2e-5
+
+
+def test_qmm_rejects_bad_arguments(ops):
+    from mlx_parallm_b200 import _lib
+    x = torch.zeros((1, 96), dtype=torch.float16, device="cuda")
+    w = torch.zeros((4, 12), dtype=torch.int32, device="cuda")
+    s = torch.zeros((4, 1), dtype=torch.float16, device="cuda")
+    with pytest.raises(_lib.B200PError):
+        ops.qmm(x, w, s, s, 64, 4)                      # K=96 not a multiple of group 64
+
+
+# ---------------------------------------------------------------- rmsnorm / rope+append / attention
+@pytest.mark.parametrize("dtype", ["float32", "float16", "bfloat16"])
+def test_rmsnorm(ops, dtype):
+    rng = np.random.default_rng(3)
+    x = rng.standard_normal((7, 512)).astype(np.float32) * 3
+    w = ref.round_to(1 + 0.1 * rng.standard_normal(512), dtype)
+    y = ops.rmsnorm(torch.from_numpy(x).cuda(), t_(w, dtype), 1e-5)
+    exp = ref.rms_norm(x, w, 1e-5, dtype)
+    # identical up to 1 ulp of the storage type (fp32 reduction order differs)
+    assert rel_err(y.float().cpu().numpy(), exp) < {"float32": 1e-6, "float16": 1.1e-3, "bfloat16": 8.1e-3}[dtype]
+
+
+@pytest.mark.parametrize("dtype,D,qk_norm", [("float16", 128, False), ("bfloat16", 128, True), ("float32", 16, False), ("float16", 64, True)])
+def test_rope_kv_append(ops, dtype, D, qk_norm):
+    rng = np.random.default_rng(4)
+    B, L, Hq, Hkv, Tcap = 3, 2, 4, 2, 40
+    lengths = np.array([0, 7, 33], np.int32)
+    qkv = ref.round_to(rng.standard_normal((B * L, (Hq + 2 * Hkv) * D)), dtype)
+    qn = ref.round_to(1 + 0.1 * rng.standard_normal(D), dtype)
+    kn = ref.round_to(1 + 0.1 * rng.standard_normal(D), dtype)
+    q_out = torch.zeros((B, L, Hq, D), dtype=TD[dtype], device="cuda")
+    kc = torch.zeros((B, Hkv, Tcap, D), dtype=TD[dtype], device="cuda")
+    vc = torch.zeros_like(kc)
+    ops.rope_kv_append(t_(qkv, dtype), q_out, kc, vc, torch.from_numpy(lengths).cuda(), B, L, Hq, Hkv, D, 10000.0, 1.0,
+                       t_(qn, dtype) if qk_norm else None, t_(kn, dtype) if qk_norm else None, 1e-6)
+    r = qkv.reshape(B, L, Hq + 2 * Hkv, D)
+    q, k, v = r[:, :, :Hq], r[:, :, Hq:Hq + Hkv], r[:, :, Hq + Hkv:]
+    if qk_norm:
+        q = ref.rms_norm(q, qn, 1e-6, dtype)
+        k = ref.rms_norm(k, kn, 1e-6, dtype)
+    qe = ref.rope(q.transpose(0, 2, 1, 3), lengths, 10000.0, 1.0, dtype).transpose(0, 2, 1, 3)
+    ke = ref.rope(k.transpose(0, 2, 1, 3), lengths, 10000.0, 1.0, dtype)
+    tol = {"float32": 3e-6, "float16": 1.5e-3, "bfloat16": 1e-2}[dtype]
+    assert rel_err(q_out.float().cpu().numpy(), qe) < tol
+    kcn, vcn = kc.float().cpu().numpy(), vc.float().cpu().numpy()
+    for b in range(B):
+        s = lengths[b]
+        assert rel_err(kcn[b, :, s:s + L], ke[b]) < tol
+        assert np.array_equal(vcn[b, :, s:s + L], v[b].transpose(1, 0, 2))
+        assert not kcn[b, :, s + L:].any() and not kcn[b, :, :s].any()      # nothing else touched
+
+
+def attn_case(ops, B, L, Hq, Hkv, D, lengths, dtype, path, seed=5):
+    from mlx_parallm_b200 import _lib
+    rng = np.random.default_rng(seed)
+    Tcap = int(max(lengths)) + L + 3
+    q = ref.round_to(rng.standard_normal((B, L, Hq, D)), dtype)
+    k = ref.round_to(rng.standard_normal((B, Hkv, Tcap, D)), dtype)
+    v = ref.round_to(rng.standard_normal((B, Hkv, Tcap, D)), dtype)
+    out = torch.zeros((B, L, Hq * D), dtype=TD[dtype], device="cuda")
+    ws = torch.empty((max(ops.attn_workspace_bytes(B, L, Hq, D), 16),), dtype=torch.uint8, device="cuda")
+    _lib.check(_lib.lib().b200p_attn_set_path(path))
+    try:
+        ops.attn(t_(q, dtype), t_(k, dtype), t_(v, dtype), torch.from_numpy(np.asarray(lengths, np.int32)).cuda(), out,
+                 B, L, Hq, Hkv, D, D ** -0.5, workspace=ws)
+    finally:
+        _lib.lib().b200p_attn_set_path(0)
+    exp = np.zeros((B, L, Hq * D), np.float32)
+    for b in range(B):
+        T = lengths[b] + L
+        mask = ref.additive_causal_mask_variable(L, [lengths[b]], T)
+        o = ref.sdpa(q[b:b + 1].transpose(0, 2, 1, 3), k[b:b + 1, :, :T], v[b:b + 1, :, :T], D ** -0.5, mask if L > 1 else None)
+        exp[b] = o.transpose(0, 2, 1, 3).reshape(L, Hq * D)
+    return out.float().cpu().numpy(), exp
+
+
+@pytest.mark.parametrize("dtype,D,Hq,Hkv", [("float32", 16, 4, 4), ("float16", 128, 8, 2), ("bfloat16", 128, 5, 1), ("float16", 64, 4, 2)])
+def test_attention_generic_decode_ragged_lengths(ops, dtype, D, Hq, Hkv):
+    got, exp = attn_case(ops, 3, 1, Hq, Hkv, D, [0, 5, 130], dtype, path=1)
+    assert rel_err(got, exp) < {"float32": 2e-5, "float16": 1.5e-3, "bfloat16": 1e-2}[dtype]
+
+
+def test_attention_generic_prefill_causal(ops):
+    got, exp = attn_case(ops, 2, 9, 4, 2, 64, [0, 4], "float16", path=1)
+    assert rel_err(got, exp) < 1.5e-3
+
+
+# ---------------------------------------------------------------- samplers
+def test_argmax_ties_and_probs(ops):
+    rng = np.random.default_rng(6)
+    lg = rng.standard_normal((5, 1000)).astype(np.float32)
+    lg[0, 17] = lg[0, 900] = 9.0                       # tie -> lowest index
+    lg[1, 999] = 12.0
+    probs = torch.zeros(5, device="cuda")
+    tok = ops.argmax(torch.from_numpy(lg).cuda(), probs_out=probs)
+    assert tok.tolist() == ref.argmax_tokens(lg)[:, 0].tolist() and tok[0].item() == 17
+    sm = ref.softmax(lg)
+    assert np.allclose(probs.cpu().numpy(), sm[np.arange(5), tok.cpu().numpy()], rtol=1e-4)
+
+
+def test_argmax_large_vocab_unaligned(ops):
+    rng = np.random.default_rng(7)
+    lg = rng.standard_normal((3, 151937)).astype(np.float32)
+    t = torch.from_numpy(lg).cuda()
+    assert ops.argmax(t).tolist() == lg.argmax(-1).tolist()
+
+
+@pytest.mark.parametrize("top_p,temp", [(0.9, 1.0), (0.5, 0.7), (1.0, 1.3)])
+def test_top_p_sampling_distribution(ops, top_p, temp):
+    """Distributional parity (A.7: MLX's threefry stream is not reproducible outside MLX): draws must stay in
+    the oracle's nucleus and match its renormalised probabilities (chi-square style bound on the big bins)."""
+    rng = np.random.default_rng(8)
+    V, n = 200, 20000
+    lg = (rng.standard_normal(V) * 2.0).astype(np.float32)
+    dist = ref.top_p_distribution(lg[None], top_p, temp)[0]
+    logits = torch.from_numpy(np.tile(lg, (n, 1))).cuda()
+    tok = ops.sample_top_p(logits, temp, top_p, seed=123, offset=0).cpu().numpy()
+    assert dist[tok].min() > 0, "sampled a token outside the nucleus"
+    freq = np.bincount(tok, minlength=V) / n
+    big = dist > 0.01
+    assert np.abs(freq[big] - dist[big]).max() < 4 * np.sqrt(dist[big].max() / n) + 2e-3
+    tok2 = ops.sample_top_p(logits, temp, top_p, seed=123, offset=0).cpu().numpy()
+    assert np.array_equal(tok, tok2)                     # counter-based RNG: reproducible
+    tok3 = ops.sample_top_p(logits, temp, top_p, seed=123, offset=1).cpu().numpy()
+    assert not np.array_equal(tok, tok3)
+
+
+def test_top_p_empty_nucleus_returns_argmax(ops):
+    lg = np.log(np.array([[0.6, 0.3, 0.1]], np.float32))
+    tok = ops.sample_top_p(torch.from_numpy(np.tile(lg, (64, 1))).cuda(), 1.0, 0.5, 1, 0)
+    assert (tok.cpu().numpy() == 0).all()
