@@ -286,8 +286,8 @@ class DecoderModel:
             dims = [(nqkv, args.hidden_size), (args.hidden_size, att.n_heads * att.head_dim),
                     (2 * inter_local, args.hidden_size), (args.hidden_size, inter_local),
                     (head.out_features, args.hidden_size)]
-            ws = max(max(ops.qmm_workspace_bytes(M, n, k) for n, k in dims),
-                     ops.attn_workspace_bytes(B, M // B, att.n_heads, att.head_dim), 16)
+            ws_q = max(max(ops.qmm_workspace_bytes(M, n, k) for n, k in dims), 16)
+            ws_a = max(ops.attn_workspace_bytes(B, M // B, att.n_heads, att.head_dim), 16)
             a = dict(
                 h=torch.empty((M, args.hidden_size), dtype=torch.float32, device=dev),
                 x=torch.empty((M, args.hidden_size), dtype=dt, device=dev),
@@ -296,7 +296,9 @@ class DecoderModel:
                 att=torch.empty((M, att.n_heads * att.head_dim), dtype=dt, device=dev),
                 act=torch.empty((M, inter_local), dtype=dt, device=dev),
                 xl=torch.empty((M, args.hidden_size), dtype=dt, device=dev),
-                ws=torch.empty((ws,), dtype=torch.uint8, device=dev),
+                # split-K tile counters live at the head of the qmm workspace: zero once, kernels self-clean
+                ws=torch.zeros((ws_q,), dtype=torch.uint8, device=dev),
+                ws_attn=torch.empty((ws_a,), dtype=torch.uint8, device=dev),
             )
             if len(self._arenas) > 8:
                 self._arenas.clear()
@@ -319,7 +321,7 @@ class DecoderModel:
                                at.q_norm.weight if at.q_norm else None, at.k_norm.weight if at.k_norm else None,
                                args.rms_norm_eps)
             ops.attn(a["q"], c.keys, c.values, lengths, a["att"], B, L, at.n_heads, at.n_kv_heads, at.head_dim,
-                     at.scale, workspace=a["ws"])
+                     at.scale, workspace=a["ws_attn"])
             if tp and self.tp_rank != 0:
                 a["h"].zero_()
             at.o_proj(a["att"], EPI_ADD_RESIDUAL, out=a["h"], workspace=a["ws"])

@@ -87,7 +87,7 @@ def qmm_case(ops, M, N, K, bits, dtype, epi, seed=0, path=0, ragged_ld=False):
         big = torch.zeros((M, K + 64), dtype=xt.dtype, device="cuda")
         big[:, :K] = xt
         xt = big[:, :K]
-    ws = torch.empty((max(ops.qmm_workspace_bytes(M, N, K), 16),), dtype=torch.uint8, device="cuda")
+    ws = torch.zeros((max(ops.qmm_workspace_bytes(M, N, K), 16),), dtype=torch.uint8, device="cuda")
     _lib.check(_lib.lib().b200p_qmm_set_path(path))
     try:
         if epi == _lib.EPI_ADD_RESIDUAL:
