@@ -96,10 +96,11 @@ using namespace b200p;
 extern "C" int b200p_dequantize(const uint32_t* w, const void* scales, const void* biases, void* out,
                                 int64_t N, int64_t K, int group_size, int bits, int dtype, int mode,
                                 void* stream) {
+  B200P_REQUIRE(N >= 0, B200P_ERR_ARG, "N < 0");
+  if (N == 0) return B200P_OK;                      // empty input: nothing to launch (pointers may be null)
   int rc = check_quant_args(w, scales, biases, K, group_size, bits, mode);
   if (rc) return rc;
   B200P_REQUIRE(out && aligned(out, 16), B200P_ERR_ALIGN, "out must be non-null and 16-byte aligned");
-  B200P_REQUIRE(N >= 0, B200P_ERR_ARG, "N < 0");
   B200P_DISPATCH_DTYPE(dtype, T, return (launch_dequant<T, T>(w, scales, biases, out, nullptr, N, N, K,
                                                               group_size, bits, mode, (cudaStream_t)stream)));
   return B200P_OK;
@@ -108,6 +109,7 @@ extern "C" int b200p_dequantize(const uint32_t* w, const void* scales, const voi
 extern "C" int b200p_embed(const int32_t* ids, const uint32_t* w, const void* scales, const void* biases,
                            void* out, int64_t M, int64_t V, int64_t K, int group_size, int bits, int dtype,
                            int mode, int out_f32, void* stream) {
+  if (M == 0) return B200P_OK;
   int rc = check_quant_args(w, scales, biases, K, group_size, bits, mode);
   if (rc) return rc;
   B200P_REQUIRE(ids && out && aligned(out, 16), B200P_ERR_ALIGN, "ids/out must be non-null, out 16-byte aligned");

@@ -19,6 +19,7 @@
 // split-K partials are L2 traffic.
 #include <cuda.h>
 
+#include <stdlib.h>
 #include <type_traits>
 
 #include "common.cuh"
@@ -171,6 +172,23 @@ template <typename T> __device__ __forceinline__ uint32_t dup16(T v) {
   return u | (u << 16);
 }
 
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define TL(slot)                                                                        \
+  do {                                                                                  \
+    if (p.tl != nullptr && blockIdx.y == 0 && blockIdx.z == 0 && blockIdx.x < 16)       \
+      p.tl[blockIdx.x * 16 + (slot)] = gtimer();                                        \
+  } while (0)
+
+#define TC(i, k)                                                                                      \
+  do {                                                                                                \
+    if (p.tl != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (i) >= 16 && (i) < 20) \
+      p.tl[256 + ((i) - 16) * 16 + (k)] = (unsigned long long)clock64();                               \
+  } while (0)
+
 __device__ __forceinline__ float silu_tc(float g) { return g / (1.0f + __expf(-g)); }
 
 // ------------------------------------------------------------------------------------------------ kernel
@@ -190,9 +208,12 @@ struct TcParams {
   int epi;
   int num_kb;      // K / 64
   int splits;
+  int kb_unit;     // 8 when scales/biases rows allow 128-bit loads (num_kb % 8 == 0), else 1
   int in_stages;
   int in_stage_bytes;
   int tmem_cols;
+  unsigned long long* tl;   // optional per-CTA timeline (ns stamps), profiling only
+  int debug;        // bit0: skip dequant math+stores, bit1: skip MMA issue, bit2: skip epilogue stores (profiling only)
 };
 
 template <typename T, int BITS>
@@ -223,10 +244,12 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
   const int rowB0 = silu ? p.N / 2 + pair * 128 : pair * 256 + 128;
   const int tok0 = tile * TN;
   // K range of this split
-  const int kb_begin = (int)(((int64_t)p.num_kb * split) / p.splits);
-  const int kb_end = (int)(((int64_t)p.num_kb * (split + 1)) / p.splits);
+  const int n_units = p.num_kb / p.kb_unit;           // split boundaries fall on kb_unit multiples
+  const int kb_begin = p.kb_unit * (int)(((int64_t)n_units * split) / p.splits);
+  const int kb_end = (split == p.splits - 1) ? p.num_kb : p.kb_unit * (int)(((int64_t)n_units * (split + 1)) / p.splits);
   const int nkb = kb_end - kb_begin;
 
+  if (threadIdx.x == 0) TL(0);
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.in_stages; ++s) { mbar_init(full_in(s), 1); mbar_init(empty_in(s), 1); }
     for (int s = 0; s < A_STAGES; ++s) { mbar_init(full_a(s), DQ_THREADS / 32); mbar_init(empty_a(s), 1); }
@@ -243,20 +266,28 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
   pdl_wait();   // X (and the residual) come from the previous kernel
+  if (threadIdx.x == 0) TL(1);
 
   if (warp == 0) {
     // ===================================== TMA producer =====================================
     if (lane == 0) {
-      const uint32_t tx = (uint32_t)(W_STAGE_BYTES + TN * 128);
+      const bool do_w = !(p.debug & 8), do_x = !(p.debug & 16);
+      const uint32_t tx = (uint32_t)((do_w ? W_STAGE_BYTES : 0) + (do_x ? TN * 128 : 0));
       for (int i = 0; i < nkb; ++i) {
         const int s = i % p.in_stages, ph = (i / p.in_stages) & 1;
+        TC(i, 12);
         mbar_wait(empty_in(s), ph ^ 1);
+        TC(i, 13);
         const uint32_t dst = in_ring + s * p.in_stage_bytes;
-        mbar_arrive_expect_tx(full_in(s), tx);
+        if (tx) mbar_arrive_expect_tx(full_in(s), tx); else mbar_arrive(full_in(s));
         const int kb = kb_begin + i;
-        tma_load_2d(dst, &tm_w, kb * PKB, rowA0, full_in(s));
-        tma_load_2d(dst + 128 * PKB, &tm_w, kb * PKB, rowB0, full_in(s));
-        tma_load_2d(dst + W_STAGE_BYTES, &tm_x, kb * 64, tok0, full_in(s));
+        if (do_w) {
+          tma_load_2d(dst, &tm_w, kb * PKB, rowA0, full_in(s));
+          tma_load_2d(dst + 128 * PKB, &tm_w, kb * PKB, rowB0, full_in(s));
+        }
+        if (do_x) tma_load_2d(dst + W_STAGE_BYTES, &tm_x, kb * 64, tok0, full_in(s));
+        if (i == 0) TL(2);
+        if (i == nkb - 1) TL(3);
       }
     }
   } else if (warp == 1) {
@@ -268,10 +299,14 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     for (int i = 0; i < nkb; ++i) {
       const int si = i % p.in_stages, phi = (i / p.in_stages) & 1;
       const int sa = i % A_STAGES, pha = (i / A_STAGES) & 1;
+      if (lane == 0) TC(i, 8);
       mbar_wait(full_in(si), phi);
+      if (lane == 0) TC(i, 9);
       mbar_wait(full_a(sa), pha);
       tc_fence_after();
+      if (lane == 0) TC(i, 10);
       if (lane == 0) {
+        if (!(p.debug & 2)) {
         const uint32_t xs = in_ring + si * p.in_stage_bytes + W_STAGE_BYTES;
         const uint32_t as = a_ring + sa * A_STAGE_BYTES;
 #pragma unroll
@@ -283,11 +318,20 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
             umma_f16(tmem_base + (uint32_t)(blk * TN), ad, bd, idesc, (i > 0 || k4 > 0) ? 1u : 0u);
           }
         }
+        }
+        if (p.debug & 64) {
+          mbar_arrive(empty_in(si)); mbar_arrive(empty_a(sa));
+          if (i == nkb - 1) mbar_arrive(accum_full);
+        } else {
         umma_commit(empty_in(si));
         umma_commit(empty_a(sa));
         if (i == nkb - 1) umma_commit(accum_full);
+        }
+        TC(i, 11);
       }
       __syncwarp();
+      if (lane == 0 && i == 0) TL(4);
+      if (lane == 0 && i == nkb - 1) TL(5);
     }
   } else {
     // ===================================== dequantisers =====================================
@@ -297,42 +341,81 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     const bool row_ok = grow < p.N;
     const T* sp = reinterpret_cast<const T*>(p.scales) + (int64_t)(row_ok ? grow : 0) * p.num_kb;
     const T* bp = reinterpret_cast<const T*>(p.biases) + (int64_t)(row_ok ? grow : 0) * p.num_kb;
-    const T zero = Tr<T>::from_f(0.f);
-    T s_next = row_ok && nkb > 0 ? sp[kb_begin] : zero;
-    T b_next = row_ok && nkb > 0 ? bp[kb_begin] : zero;
     // swizzled positions
     const uint32_t a_row_off = (uint32_t)(blk * (128 * 128) + (r >> 3) * 1024 + (r & 7) * 128);
     const uint32_t a_xor = (uint32_t)(r & 7);
-    for (int i = 0; i < nkb; ++i) {
+    // TMA SWIZZLE_32B / SWIZZLE_64B of the packed tile: 16-byte chunk index ^= address bits [7, 7+log2(PKB/16))
+    const uint32_t w_sw = (BITS == 4) ? ((uint32_t)(dt >> 2) & 1u) : ((uint32_t)(dt >> 1) & 3u);
+
+    auto process = [&](int i, uint32_t s2, uint32_t b2) {
       const int si = i % p.in_stages, phi = (i / p.in_stages) & 1;
       const int sa = i % A_STAGES, pha = (i / A_STAGES) & 1;
-      const uint32_t s2 = dup16(s_next), b2 = dup16(b_next);
-      if (i + 1 < nkb && row_ok) { s_next = sp[kb_begin + i + 1]; b_next = bp[kb_begin + i + 1]; }
+      if (dt == 0) TC(i, 0);
       mbar_wait(full_in(si), phi);
+      if (dt == 0) TC(i, 1);
+      if (dt == 0 && i == 0) TL(6);
+      if (dt == 0 && i == 8) TL(12);
+      if (dt == 0 && i == 16) TL(13);
       const uint32_t wsrc = in_ring + si * p.in_stage_bytes + (uint32_t)(dt * PKB);
       uint4 pk[PKB / 16];
 #pragma unroll
-      for (int c = 0; c < PKB / 16; ++c) {
-        // TMA SWIZZLE_32B / SWIZZLE_64B: 16-byte chunk index ^= address bits [7, 7+log2(PKB/16))
-        const uint32_t sw = (BITS == 4) ? ((uint32_t)(dt >> 2) & 1u) : ((uint32_t)(dt >> 1) & 3u);
-        pk[c] = lds128(wsrc + (((uint32_t)c ^ sw) << 4));
-      }
+      for (int c = 0; c < PKB / 16; ++c) pk[c] = lds128(wsrc + (((uint32_t)c ^ w_sw) << 4));
+      if (dt == 0) TC(i, 2);
       mbar_wait(empty_a(sa), pha ^ 1);
+      if (dt == 0) TC(i, 3);
       const uint32_t adst = a_ring + sa * A_STAGE_BYTES + a_row_off;
       const uint32_t* pw = reinterpret_cast<const uint32_t*>(pk);
+      if (!(p.debug & 1)) {
 #pragma unroll
-      for (int c = 0; c < 8; ++c) {                  // 8 chunks of 8 values = 64 k
-        uint4 v = (BITS == 4) ? dequant_word4<T>(pw[c], s2, b2) : dequant_word8<T>(pw[2 * c], pw[2 * c + 1], s2, b2);
-        sts128(adst + (((uint32_t)c ^ a_xor) << 4), v);
+        for (int c = 0; c < 8; ++c) {                // 8 chunks of 8 values = 64 k
+          uint4 v = (BITS == 4) ? dequant_word4<T>(pw[c], s2, b2) : dequant_word8<T>(pw[2 * c], pw[2 * c + 1], s2, b2);
+          sts128(adst + (((uint32_t)c ^ a_xor) << 4), v);
+        }
       }
-      fence_proxy_async();                           // generic-proxy stores -> visible to the tensor core (async proxy)
+      if (dt == 0) TC(i, 4);
+      if (!(p.debug & 32)) fence_proxy_async();      // generic-proxy stores -> visible to the tensor core (async proxy)
       __syncwarp();
       if (lane == 0) mbar_arrive(full_a(sa));
+      if (dt == 0) TC(i, 5);
+      if (dt == 0 && i == 0) TL(7);
+      if (dt == 0 && i == nkb - 1) TL(8);
+    };
+
+    if (p.kb_unit == 8) {
+      // scales / biases of 8 consecutive k-blocks per 128-bit load, prefetched one group (8 k-blocks) ahead
+      const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
+      const uint4* sp4 = reinterpret_cast<const uint4*>(sp + kb_begin);
+      const uint4* bp4 = reinterpret_cast<const uint4*>(bp + kb_begin);
+      uint4 sv_n = (row_ok && nkb > 0) ? ldg_stream(sp4) : z4;
+      uint4 bv_n = (row_ok && nkb > 0) ? ldg_stream(bp4) : z4;
+      for (int i0 = 0; i0 < nkb; i0 += 8) {
+        const uint4 sv = sv_n, bv = bv_n;
+        if (i0 + 8 < nkb && row_ok) { sv_n = ldg_stream(sp4 + (i0 >> 3) + 1); bv_n = ldg_stream(bp4 + (i0 >> 3) + 1); }
+        const uint32_t sw[4] = {sv.x, sv.y, sv.z, sv.w}, bw[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          if (i0 + j < nkb) {
+            const uint32_t s2 = (j & 1) ? prmt(sw[j >> 1], 0u, 0x3232u) : prmt(sw[j >> 1], 0u, 0x1010u);
+            const uint32_t b2 = (j & 1) ? prmt(bw[j >> 1], 0u, 0x3232u) : prmt(bw[j >> 1], 0u, 0x1010u);
+            process(i0 + j, s2, b2);
+          }
+        }
+      }
+    } else {
+      const T zero = Tr<T>::from_f(0.f);
+      T s_next = row_ok && nkb > 0 ? sp[kb_begin] : zero;
+      T b_next = row_ok && nkb > 0 ? bp[kb_begin] : zero;
+      for (int i = 0; i < nkb; ++i) {
+        const uint32_t s2 = dup16(s_next), b2 = dup16(b_next);
+        if (i + 1 < nkb && row_ok) { s_next = sp[kb_begin + i + 1]; b_next = bp[kb_begin + i + 1]; }
+        process(i, s2, b2);
+      }
     }
 
     // ===================================== epilogue =========================================
     mbar_wait(accum_full, 0);
     tc_fence_after();
+    if (dt == 0) TL(9);
     const int q = warp & 3;                          // TMEM lane quarter this warp may read
     const int th = (warp - 2) >> 2;                  // token half
     const int er = q * 32 + lane;                    // row within the 128-row block
@@ -365,7 +448,7 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
       }
     };
 
-    for (int t = t_lo; t < t_hi; t += 8) {
+    for (int t = t_lo; t < t_hi && !(p.debug & 4); t += 8) {
       float v0[8], v1[8];
       tmem_ld8(lane_base + (uint32_t)t, v0);
       tmem_ld8(lane_base + (uint32_t)(TN + t), v1);
@@ -409,9 +492,11 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
       }
     }
     tc_fence_before();
+    if (dt == 0) TL(10);
   }
   pdl_launch_dependents();
   __syncthreads();
+  if (threadIdx.x == 0) TL(11);
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols);
@@ -422,6 +507,9 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static unsigned long long* g_timeline = nullptr;
+extern "C" void b200p_debug_set_timeline(void* dev_ptr) { g_timeline = (unsigned long long*)dev_ptr; }
 
 static EncodeTiledFn get_encode() {
   static EncodeTiledFn fn = nullptr;
@@ -438,6 +526,7 @@ constexpr int SMEM_BUDGET = 227 * 1024;
 constexpr int MIN_TC_M = 5;      // below this the CUDA-core GEMV wins (weights read once either way)
 
 struct TcPlan {
+  int kb_unit;
   int TN, tiles, pairs, splits, in_stages, in_stage_bytes, tmem_cols, smem_bytes;
 };
 
@@ -450,10 +539,11 @@ static TcPlan make_plan(int64_t M, int64_t N, int64_t K, int bits, int epi) {
   const int num_kb = (int)(K / 64);
   const int ctas = pl.pairs * pl.tiles;
   const int sms = sm_count();
+  pl.kb_unit = (num_kb % 8 == 0) ? 8 : 1;
   int splits = 1;
   if (ctas < (sms * 3) / 4) {
     splits = sms / ctas;
-    int max_by_k = num_kb / 4;
+    int max_by_k = pl.kb_unit == 8 ? num_kb / 8 : num_kb / 4;
     if (splits > max_by_k) splits = max_by_k;
     if (splits < 1) splits = 1;
   }
@@ -550,8 +640,10 @@ int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b
   size_t need = counters + (pl.splits > 1 ? (size_t)pl.pairs * pl.tiles * pl.splits * 2 * pl.TN * 128 * sizeof(float) : 0);
   B200P_REQUIRE(ws_bytes >= need && aligned(ws, 16), B200P_ERR_ARG, "qmm workspace too small (%zu < %zu)", ws_bytes, need);
   p.M_tok = (int)M; p.N = (int)N; p.K = (int)K; p.TN = pl.TN; p.ldy = ldy; p.epi = epi;
-  p.num_kb = (int)(K / 64); p.splits = pl.splits; p.in_stages = pl.in_stages; p.in_stage_bytes = pl.in_stage_bytes;
+  p.num_kb = (int)(K / 64); p.splits = pl.splits; p.kb_unit = pl.kb_unit; p.in_stages = pl.in_stages; p.in_stage_bytes = pl.in_stage_bytes;
   p.tmem_cols = pl.tmem_cols;
+  p.tl = g_timeline;
+  { const char* d = getenv("B200P_TC_DEBUG"); p.debug = d ? atoi(d) : 0; }
   if (dtype == B200P_F16) {
     return bits == 4 ? launch_tc<__half, 4>(tmw, tmx, p, pl, st) : launch_tc<__half, 8>(tmw, tmx, p, pl, st);
   } else {

@@ -59,8 +59,12 @@ class BatchedKVCache:
                 self._lengths = None
         self.offset = 0
         self._offsets = [0] * self.batch_size
-        if self._lengths is not None and not self._lengths_shared:
-            self._lengths.zero_()
+        if self._lengths is not None:
+            if self._lengths.numel() != self.batch_size:
+                self._lengths = None if not self._lengths_shared else torch.zeros(
+                    (self.batch_size,), dtype=torch.int32, device=self._lengths.device)
+            else:
+                self._lengths.zero_()          # shared across layers: zeroing it from every layer is idempotent
 
     def update_and_fetch(self, keys, values):
         """Append [B, Hkv, L, D] at each row's offset and return views up to the max end

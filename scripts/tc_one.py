@@ -1,0 +1,43 @@
+"""Launch the tensor-path GEMM a few times eagerly (for ncu)."""
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from mlx_parallm_b200 import ops, _lib
+L = _lib.lib(); _lib.require_device()
+M, N, K, epi = [int(v) for v in sys.argv[1:5]]
+dt = torch.float16
+g = torch.Generator(device="cuda"); g.manual_seed(1)
+mats = []
+for i in range(4):
+    w = torch.randint(-2**31, 2**31, (N, K // 8), generator=g, device="cuda", dtype=torch.int64).to(torch.int32)
+    s = (torch.rand((N, K // 64), generator=g, device="cuda") * 0.01).to(dt)
+    b = (torch.rand((N, K // 64), generator=g, device="cuda") * 0.01).to(dt)
+    mats.append((w, s, b))
+x = torch.randn((M, K), device="cuda").to(dt)
+ws = torch.zeros((max(ops.qmm_workspace_bytes(M, N, K), 16),), dtype=torch.uint8, device="cuda")
+out = torch.zeros((M, N if epi != 3 else N // 2), device="cuda", dtype=torch.float32 if epi in (1, 2) else dt)
+_lib.check(L.b200p_qmm_set_path(2))
+import ctypes
+tl = torch.zeros((16 * 16 + 64,), dtype=torch.int64, device="cuda")
+evs = []
+for i in range(8):
+    if i == 7:
+        L.b200p_debug_set_timeline(ctypes.c_void_p(tl.data_ptr()))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    ops.qmm(x, *mats[i % 4], 64, 4, epi, out=out, workspace=ws)
+    e1.record()
+    evs.append((e0, e1))
+torch.cuda.synchronize()
+print("event us per launch:", [round(a.elapsed_time(b) * 1e3, 1) for a, b in evs])
+t2 = tl.cpu()[256:].view(4, 16)
+t = tl.cpu()[:256].view(16, 16)
+b0 = int(t2[0, 0])
+lab = ['dq_top','dq_fullin','dq_lds','dq_emptya','dq_math','dq_arrived','','','mma_top','mma_fullin','mma_fulla','mma_issued','prod_top','prod_emptyin']
+for it in range(4):
+    print('iter', 16 + it, ' '.join(f'{lab[k]}={int(t2[it, k]) - b0}' for k in range(14) if lab[k]))
+names = ["start", "setup_done", "prod_first_tma", "prod_last_tma", "mma_first", "mma_last", "dq_first_full_in", "dq_first_done", "dq_last_done", "accum_full", "epi_done", "end", "dq_i8", "dq_i16"]
+for c in (0, 1, 5):
+    base = int(t[c, 0])
+    print("CTA", c, " ".join(f"{n}={int(t[c, j]) - base}" for j, n in enumerate(names) if int(t[c, j])))
+print("done")

@@ -259,3 +259,46 @@ def test_top_p_empty_nucleus_returns_argmax(ops):
     lg = np.log(np.array([[0.6, 0.3, 0.1]], np.float32))
     tok = ops.sample_top_p(torch.from_numpy(np.tile(lg, (64, 1))).cuda(), 1.0, 0.5, 1, 0)
     assert (tok.cpu().numpy() == 0).all()
+
+
+# ---------------------------------------------------------------- tcgen05 tile path of b200p_qmm
+TC_CASES = [  # M, N, K, bits, dtype, epilogue
+    (8, 256, 256, 4, "float16", 1), (16, 512, 1024, 4, "float16", 0), (64, 1024, 512, 4, "float16", 2),
+    (64, 2048, 1024, 4, "float16", 3), (5, 1000, 192, 4, "float16", 1), (100, 1000, 448, 4, "bfloat16", 1),
+    (300, 512, 512, 4, "float16", 0), (64, 512, 2048, 8, "float16", 1), (33, 768, 640, 4, "bfloat16", 3),
+    (64, 256, 4096, 4, "float16", 2),          # deep K with few row blocks -> split-K + last-arriver fix-up
+]
+
+
+@pytest.mark.parametrize("M,N,K,bits,dtype,epi", TC_CASES)
+def test_qmm_tensor_path_matches_oracle(ops, M, N, K, bits, dtype, epi):
+    got, exp = qmm_case(ops, M, N, K, bits, dtype, epi, seed=M + N, path=2)
+    # A is the storage-rounded dequantised weight (round_T(q*s+b)), accumulation fp32 in TMEM
+    tol = {"float16": 3e-3, "bfloat16": 2e-2}[dtype]
+    assert rel_err(got, exp) < tol
+
+
+def test_qmm_tensor_path_is_deterministic_and_matches_gemv(ops):
+    a1, _ = qmm_case(ops, 64, 512, 4096, 4, "float16", 1, seed=3, path=2)
+    a2, _ = qmm_case(ops, 64, 512, 4096, 4, "float16", 1, seed=3, path=2)
+    g, _ = qmm_case(ops, 64, 512, 4096, 4, "float16", 1, seed=3, path=1)
+    assert np.array_equal(a1, a2)
+    assert rel_err(a1, g) < 1e-3
+
+
+# ---------------------------------------------------------------- split-K tensor decode attention
+@pytest.mark.parametrize("dtype,Hq,Hkv,lengths", [
+    ("float16", 8, 2, [0, 5, 130]),             # ragged rows incl. an empty cache (only the new token)
+    ("bfloat16", 5, 1, [15, 16, 17]),           # G = 5 (Qwen3-14B at TP=8), tile-boundary lengths
+    ("float16", 32, 8, [700, 3]),               # Llama-3-8B head layout
+    ("float16", 8, 1, [5000, 4999, 1, 2500]),   # G = 8 (70B), long rows -> sequence split across CTAs
+])
+def test_attention_tensor_decode(ops, dtype, Hq, Hkv, lengths):
+    got, exp = attn_case(ops, len(lengths), 1, Hq, Hkv, 128, lengths, dtype, path=2)
+    assert rel_err(got, exp) < {"float16": 2e-3, "bfloat16": 1.2e-2}[dtype]
+
+
+def test_attention_tensor_matches_generic(ops):
+    a, _ = attn_case(ops, 2, 1, 8, 2, 128, [1000, 37], "float16", path=2, seed=9)
+    g, _ = attn_case(ops, 2, 1, 8, 2, 128, [1000, 37], "float16", path=1, seed=9)
+    assert rel_err(a, g) < 2e-3
