@@ -124,6 +124,15 @@ int b200p_attn_set_path(int path);
 int b200p_argmax(const float* logits, int32_t* tokens, float* probs_out, int64_t B, int64_t V,
                  int64_t ldl, void* stream);
 
+/* Vocab-parallel greedy head (tensor parallelism; new -- the reference is single-device): each rank
+ * reduces ITS logits shard [B, V_local] to a 16-byte record per row {max, sum exp(l - max), global
+ * argmax index (int bits), 0}; after an all-gather of the records b200p_argmax_merge picks the token
+ * (highest max, lowest global index among ties = mx.argmax's rule) and softmax(logits)[token]. */
+int b200p_argmax_partial(const float* logits, float* rec_out, int64_t B, int64_t V, int64_t ldl,
+                         int32_t vocab_offset, void* stream);
+int b200p_argmax_merge(const float* recs /* [W, B, 4] */, int32_t* tokens, float* probs_out, int W,
+                       int64_t B, void* stream);
+
 /* top_p_sampling(logits, top_p, temperature) / mx.random.categorical(logits/temp)
  *                                                        [sample_utils.py:3-39; utils.py:354-361]
  * Draws from the renormalised nucleus {tokens whose inclusive sorted cumulative mass <= top_p}

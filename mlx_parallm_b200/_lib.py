@@ -38,6 +38,8 @@ SIGNATURES = {
     "b200p_attn_workspace_bytes": (_sz, [_i64, _i64, _i32, _i32]),
     "b200p_attn_set_path": (_i32, [_i32]),
     "b200p_argmax": (_i32, [_vp, _vp, _vp, _i64, _i64, _i64, _vp]),
+    "b200p_argmax_partial": (_i32, [_vp, _vp, _i64, _i64, _i64, _i32, _vp]),
+    "b200p_argmax_merge": (_i32, [_vp, _vp, _vp, _i32, _i64, _vp]),
     "b200p_sample_top_p": (_i32, [_vp, _vp, _vp, _i64, _i64, _i64, _f32, _f32, _u64, _u64, _vp]),
 }
 

@@ -53,7 +53,7 @@ __device__ __forceinline__ void osm_merge(float& m, float& s, float om, float os
 
 __global__ void __launch_bounds__(SAMP_THREADS)
 argmax_kernel(const float* __restrict__ logits, int32_t* __restrict__ tokens, float* __restrict__ probs_out,
-              int64_t V, int64_t ldl) {
+              int64_t V, int64_t ldl, float4* __restrict__ rec_out, int vocab_offset) {
   __shared__ float shv[32];
   __shared__ int shi[32];
   __shared__ float shm[32], shs[32];
@@ -62,7 +62,7 @@ argmax_kernel(const float* __restrict__ logits, int32_t* __restrict__ tokens, fl
   float best = -INFINITY;
   int bi = 0x7fffffff;
   float om = -INFINITY, os = 0.f;
-  const bool want_p = probs_out != nullptr;
+  const bool want_p = probs_out != nullptr || rec_out != nullptr;
   const bool vec = (ldl % 4 == 0) && ((reinterpret_cast<uintptr_t>(logits) & 15) == 0);
   int64_t V4 = vec ? V / 4 : 0;
   for (int64_t i = threadIdx.x; i < V4; i += blockDim.x) {
@@ -90,13 +90,35 @@ argmax_kernel(const float* __restrict__ logits, int32_t* __restrict__ tokens, fl
   }
   block_argmax(best, bi, shv, shi);  // contains __syncthreads, publishes shm/shs too
   if (threadIdx.x == 0) {
-    tokens[blockIdx.x] = (bi == 0x7fffffff) ? 0 : bi;
-    if (want_p) {
-      float m = -INFINITY, s = 0.f;
+    const int tok = (bi == 0x7fffffff) ? 0 : bi;
+    float m = -INFINITY, s = 0.f;
+    if (want_p)
       for (int w = 0; w < (int)(blockDim.x >> 5); ++w) osm_merge(m, s, shm[w], shs[w]);
-      probs_out[blockIdx.x] = (s > 0.f) ? __expf(best - m) / s : 0.f;
+    if (rec_out != nullptr) {   // vocab-parallel shard: publish (max, sum exp(l - max), global index)
+      rec_out[blockIdx.x] = make_float4(best, s, __int_as_float(tok + vocab_offset), 0.f);
+    } else {
+      tokens[blockIdx.x] = tok;
+      if (probs_out != nullptr) probs_out[blockIdx.x] = (s > 0.f) ? __expf(best - m) / s : 0.f;
     }
   }
+}
+
+// merge W per-shard records per row: highest max wins, lowest global index among ties (shards hold
+// ascending vocab ranges, so this is mx.argmax's lowest-index rule); prob = 1 / sum_r s_r exp(m_r - M).
+__global__ void argmax_merge_kernel(const float4* __restrict__ recs, int32_t* __restrict__ tokens,
+                                    float* __restrict__ probs_out, int W, int64_t B) {
+  pdl_wait();
+  const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  float best = -INFINITY, m = -INFINITY, s = 0.f;
+  int bi = 0x7fffffff;
+  for (int r = 0; r < W; ++r) {
+    const float4 rec = recs[(int64_t)r * B + b];
+    argmax_combine(best, bi, rec.x, __float_as_int(rec.z));
+    osm_merge(m, s, rec.x, rec.y);
+  }
+  tokens[b] = (bi == 0x7fffffff) ? 0 : bi;
+  if (probs_out != nullptr) probs_out[b] = (s > 0.f) ? __expf(best - m) / s : 0.f;
 }
 
 // ---- Philox4x32-10 -------------------------------------------------------------------------------
@@ -297,8 +319,31 @@ extern "C" int b200p_argmax(const float* logits, int32_t* tokens, float* probs_o
   B200P_REQUIRE(logits && tokens, B200P_ERR_ARG, "null pointer");
   B200P_REQUIRE(V > 0 && V < (1ll << 31) && ldl >= V, B200P_ERR_ARG, "bad V/ldl");
   if (B == 0) return B200P_OK;
-  argmax_kernel<<<(unsigned)B, SAMP_THREADS, 0, (cudaStream_t)stream>>>(logits, tokens, probs_out, V, ldl);
+  argmax_kernel<<<(unsigned)B, SAMP_THREADS, 0, (cudaStream_t)stream>>>(logits, tokens, probs_out, V, ldl, nullptr, 0);
   B200P_LAUNCH_CHECK("argmax_kernel");
+  return B200P_OK;
+}
+
+extern "C" int b200p_argmax_partial(const float* logits, float* rec_out, int64_t B, int64_t V, int64_t ldl,
+                                    int32_t vocab_offset, void* stream) {
+  B200P_REQUIRE(logits && rec_out, B200P_ERR_ARG, "null pointer");
+  B200P_REQUIRE(V > 0 && V < (1ll << 31) && ldl >= V && vocab_offset >= 0, B200P_ERR_ARG, "bad V/ldl/offset");
+  B200P_REQUIRE(aligned(rec_out, 16), B200P_ERR_ALIGN, "rec_out must be 16-byte aligned");
+  if (B == 0) return B200P_OK;
+  argmax_kernel<<<(unsigned)B, SAMP_THREADS, 0, (cudaStream_t)stream>>>(logits, nullptr, nullptr, V, ldl,
+                                                                       reinterpret_cast<float4*>(rec_out), vocab_offset);
+  B200P_LAUNCH_CHECK("argmax_kernel(partial)");
+  return B200P_OK;
+}
+
+extern "C" int b200p_argmax_merge(const float* recs, int32_t* tokens, float* probs_out, int W, int64_t B,
+                                  void* stream) {
+  B200P_REQUIRE(recs && tokens, B200P_ERR_ARG, "null pointer");
+  B200P_REQUIRE(W > 0 && aligned(recs, 16), B200P_ERR_ARG, "bad shard count / alignment");
+  if (B == 0) return B200P_OK;
+  argmax_merge_kernel<<<(unsigned)((B + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const float4*>(recs), tokens, probs_out, W, B);
+  B200P_LAUNCH_CHECK("argmax_merge_kernel");
   return B200P_OK;
 }
 

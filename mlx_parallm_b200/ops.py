@@ -190,6 +190,24 @@ def argmax(logits, out=None, probs_out=None):
     return out
 
 
+def argmax_partial(logits, vocab_offset: int, rec_out):
+    """Vocab-shard reduction for the tensor-parallel greedy head: float32 [B, V_local] -> records [B, 4]."""
+    _dev(logits, rec_out)
+    assert logits.dtype == torch.float32 and logits.dim() == 2 and logits.stride(1) == 1
+    B, V = logits.shape
+    _call("b200p_argmax_partial", lambda: lib().b200p_argmax_partial(_p(logits), _p(rec_out), B, V, logits.stride(0),
+                                                                     int(vocab_offset), _stream()))
+    return rec_out
+
+
+def argmax_merge(recs, out, probs_out=None):
+    """records [W, B, 4] (all-gathered) -> tokens int32 [B] (+ softmax prob of the token)."""
+    _dev(recs, out, probs_out)
+    W, B = recs.shape[0], recs.shape[1]
+    _call("b200p_argmax_merge", lambda: lib().b200p_argmax_merge(_p(recs), _p(out), _p(probs_out), W, B, _stream()))
+    return out
+
+
 def sample_top_p(logits, temperature, top_p, seed, offset, out=None, probs_out=None):
     _dev(logits, out, probs_out)
     assert logits.dtype == torch.float32 and logits.dim() == 2 and logits.stride(1) == 1
