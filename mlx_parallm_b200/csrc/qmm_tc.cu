@@ -1,22 +1,34 @@
-// Tensor-core path of b200p_qmm: W4A16 / W8A16 GEMM on tcgen05 with accumulators in TMEM.
+// Tensor-core path of b200p_qmm: W4A16 / W8A16 GEMM on tcgen05, A operand AND accumulators in TMEM.
 //
 //   Y[tok, n] = sum_k X[tok, k] * (q[n,k] * s[n, k/64] + b[n, k/64])
 //
-// "swap-AB": the 128 rows of a weight block are the M side of the MMA (A operand, K-major, dequantised
-// into shared memory in the canonical SWIZZLE_128B layout), the tokens are the N side (B operand = X tile,
-// loaded by TMA with SWIZZLE_128B), D[128 x TN] fp32 lives in TMEM.  A CTA owns a PAIR of 128-row weight
-// blocks (they share the X tile; for SILU_MUL the pair is gate block p / up block p) and a K range
-// (split-K); partial accumulators are merged by the last-arriving CTA of a tile (deterministic order).
+// "swap-AB": 128 rows of the weight matrix are the M side of the MMA, the tokens are the N side.
+//   A  = dequantised weights [128 x 64] 16-bit, written by the dequant warps STRAIGHT INTO TMEM with tcgen05.st
+//        (row m in lane m, k packed two per 32-bit column) -- no shared-memory round trip, no proxy fence;
+//   B  = X tile [TN x 64] 16-bit, TMA-loaded into shared memory with SWIZZLE_128B (K-major);
+//   D  = [128 x TN] fp32 in TMEM.
+// A CTA owns a PAIR of 128-row weight blocks per output tile (they share the X tile; for SILU_MUL the pair is
+// gate block p / up block p).
 //
-// warp roles (320 threads):  warp 0 = TMA producer, warp 1 = TMEM owner + single-thread MMA issuer,
-// warps 2..9 = dequantisers (one weight row per thread per k-block) and, after the main loop, the epilogue
-// (TMEM -> registers -> epilogue -> global, lanes along n so stores are coalesced).
+// Scheduling is persistent "stream-K": the work of a launch is the linear sequence of units
+// (output tile, K stage of 128 packed bytes per row = 256 k at 4 bits); CTA c of G takes the contiguous range
+// [c*U/G, (c+1)*U/G), so every SM streams the same number of weight bytes whatever N, K are.  A tile whose K
+// range is shared by several CTAs is summed with fp32 L2 atomics (red.global.add): straight into y for
+// ADD_RESIDUAL, else into a per-boundary fp32 accumulator that the last-arriving CTA reads, applies the epilogue
+// to and re-zeroes.  Split tiles are therefore summed in arrival order (last-bit run-to-run differences).
 //
-// rings:  IN  (packed weights 2x128 rows x 64 k + X tile TN x 64)  filled by TMA, freed by MMA completion
-//         A   (2 x [128 x 64] 16-bit, SW128)                       filled by dequantisers, freed by MMA completion
+// warp roles (576 threads): warps 0..15 = dequantisers (4 groups of 4 warps: group g handles block g&1 on
+// k-blocks of parity g>>1; a thread owns one weight row) and, at the end of each segment, the epilogue
+// (TMEM -> registers -> global, lanes along n so stores are coalesced); warp 16 = TMA producer; warp 17 = TMEM
+// owner + MMA issuer.  Both issue from a converged warp under elect.sync so the tcgen05 / TMA operands live in
+// uniform registers (under `lane == 0` ptxas wraps every UTCHMMA in a ~70-cycle uniformisation loop).
+//
+// rings:  IN  (packed weights 2 x [128 rows x 128 B] + KPS X tiles [TN x 64]) in shared memory, SWIZZLE_128B,
+//             filled by TMA, freed by MMA completion (tcgen05.commit);
+//         A   (4 or 6 slots x 2 blocks x 32 TMEM columns), filled by the dequantisers, freed by MMA completion.
 //
 // Algorithmic HBM bytes per launch: N*K*bits/8 + 2*N*(K/64)*2 (weights, scales, biases) -- X, Y and the
-// split-K partials are L2 traffic.
+// stream-K partials are L2 traffic.
 #include <cuda.h>
 
 #include <stdlib.h>
@@ -53,8 +65,20 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       "r"(parity)
       : "memory");
 }
+// one lane of a CONVERGED warp; unlike `lane == 0` the compiler knows the guarded code is warp-uniform, so tcgen05 /
+// TMA operands go straight to uniform registers (no per-instruction uniformisation loop)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "elect.sync _|P1, 0xffffffff;\n"
+      "selp.b32 %0, 1, 0, P1;\n"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
@@ -75,15 +99,15 @@ __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
 __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
   asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
 }
-// D[tmem] (+)= A[smem desc] * B[smem desc]^T ; kind::f16 covers f16 and bf16 inputs with fp32 accumulation
-__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accum) {
+// D[tmem] (+)= A[tmem] * B[smem desc]^T ; kind::f16 covers f16 and bf16 inputs with fp32 accumulation
+__device__ __forceinline__ void umma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accum) {
   asm volatile(
       "{\n"
       ".reg .pred p;\n"
       "setp.ne.b32 p, %4, 0;\n"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n"
       "}\n" ::"r"(d_tmem),
-      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accum)
+      "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accum)
       : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
@@ -98,19 +122,33 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, float (&v)[8]) {
   for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[i]);
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// each lane writes 32 consecutive 32-bit columns of ITS TMEM lane (= 64 consecutive 16-bit k of one A row)
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,"
+      "%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
+      "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
+      "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
   uint32_t r;
   asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
   return r;
 }
+__device__ __forceinline__ uint32_t lop3_and_or(uint32_t a, uint32_t mask, uint32_t orv) {
+  uint32_t r;
+  asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(r) : "r"(a), "r"(mask), "r"(orv));   // (a & mask) | orv
+  return r;
+}
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   uint4 r;
   asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr));
   return r;
-}
-__device__ __forceinline__ void sts128(uint32_t addr, uint4 v) {
-  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
@@ -124,47 +162,59 @@ __device__ __forceinline__ uint64_t make_desc_sw128(uint32_t smem_addr) {
 }
 
 // ------------------------------------------------------------------------------------------------ dequant
-template <typename T> struct Magic;
-template <> struct Magic<__half> {
-  static constexpr uint32_t BYTES = 0x64646464u;      // 0x64nn = 1024 + nn
-  static __device__ __forceinline__ uint32_t fix(uint32_t h2, uint32_t s2, uint32_t b2) {
-    __half2 q = __hsub2(*reinterpret_cast<__half2*>(&h2), __half2half2(__ushort_as_half(0x6400)));
-    __half2 r = __hfma2(q, *reinterpret_cast<__half2*>(&s2), *reinterpret_cast<__half2*>(&b2));
-    return *reinterpret_cast<uint32_t*>(&r);
-  }
+// Integer code -> 16-bit float through the exponent-magic trick (no I2F): OR the code into the mantissa of a
+// power of two, subtract the power of two (exact), then ONE fused q*s+b per pair (half2 / bf162 FMA).
+template <typename T> struct H2;
+template <> struct H2<__half> {
+  typedef __half2 V;
+  static constexpr uint32_t MAGIC = 0x64006400u;        // 1024.0 | q        -> 1024 + q   (q < 1024)
+  static constexpr uint32_t MAGIC_BYTES = 0x64646464u;
+  static __device__ __forceinline__ V as(uint32_t u) { return *reinterpret_cast<V*>(&u); }
+  static __device__ __forceinline__ uint32_t bits(V v) { return *reinterpret_cast<uint32_t*>(&v); }
+  static __device__ __forceinline__ V q_lo(uint32_t m) { return __hsub2(as(m), as(0x64006400u)); }              // (1024+q) - 1024
+  static __device__ __forceinline__ V q_hi(uint32_t m) { return __hfma2(as(m), as(0x2C002C00u), as(0xD400D400u)); }  // (1024+16q)/16 - 64
+  static __device__ __forceinline__ uint32_t fma(V q, uint32_t s2, uint32_t b2) { return bits(__hfma2(q, as(s2), as(b2))); }
 };
-template <> struct Magic<__nv_bfloat16> {
-  static constexpr uint32_t BYTES = 0x43434343u;      // 0x43nn = 128 + nn (nn < 128)
-  static __device__ __forceinline__ uint32_t fix(uint32_t h2, uint32_t s2, uint32_t b2) {
-    __nv_bfloat162 q = __hsub2(*reinterpret_cast<__nv_bfloat162*>(&h2), __bfloat162bfloat162(__ushort_as_bfloat16(0x4300)));
-    __nv_bfloat162 r = __hfma2(q, *reinterpret_cast<__nv_bfloat162*>(&s2), *reinterpret_cast<__nv_bfloat162*>(&b2));
-    return *reinterpret_cast<uint32_t*>(&r);
-  }
+template <> struct H2<__nv_bfloat16> {
+  typedef __nv_bfloat162 V;
+  static constexpr uint32_t MAGIC = 0x43004300u;        // 128.0 | q         -> 128 + q    (q < 128)
+  static constexpr uint32_t MAGIC_BYTES = 0x43434343u;
+  static __device__ __forceinline__ V as(uint32_t u) { return *reinterpret_cast<V*>(&u); }
+  static __device__ __forceinline__ uint32_t bits(V v) { return *reinterpret_cast<uint32_t*>(&v); }
+  static __device__ __forceinline__ V q_lo(uint32_t m) { return __hsub2(as(m), as(0x43004300u)); }
+  static __device__ __forceinline__ uint32_t fma(V q, uint32_t s2, uint32_t b2) { return bits(__hfma2(q, as(s2), as(b2))); }
 };
 
-// 8 consecutive 4-bit codes of one word -> 8 dequantised 16-bit values in k order
-template <typename T>
-__device__ __forceinline__ uint4 dequant_word4(uint32_t w, uint32_t s2, uint32_t b2) {
-  uint32_t e = w & 0x0f0f0f0fu;          // bytes n0 n2 n4 n6
-  uint32_t o = (w >> 4) & 0x0f0f0f0fu;   // bytes n1 n3 n5 n7
-  uint32_t lo = prmt(e, o, 0x5140u);     // n0 n1 n2 n3
-  uint32_t hi = prmt(e, o, 0x7362u);     // n4 n5 n6 n7
-  uint4 r;
-  r.x = Magic<T>::fix(prmt(lo, Magic<T>::BYTES, 0x4140u), s2, b2);
-  r.y = Magic<T>::fix(prmt(lo, Magic<T>::BYTES, 0x4342u), s2, b2);
-  r.z = Magic<T>::fix(prmt(hi, Magic<T>::BYTES, 0x4140u), s2, b2);
-  r.w = Magic<T>::fix(prmt(hi, Magic<T>::BYTES, 0x4342u), s2, b2);
-  return r;
-}
-// 8 consecutive 8-bit codes (two words) -> 8 dequantised values (f16 only: 1024 + q is exact for q < 1024)
-template <typename T>
-__device__ __forceinline__ uint4 dequant_word8(uint32_t w0, uint32_t w1, uint32_t s2, uint32_t b2) {
-  uint4 r;
-  r.x = Magic<T>::fix(prmt(w0, Magic<T>::BYTES, 0x4140u), s2, b2);
-  r.y = Magic<T>::fix(prmt(w0, Magic<T>::BYTES, 0x4342u), s2, b2);
-  r.z = Magic<T>::fix(prmt(w1, Magic<T>::BYTES, 0x4140u), s2, b2);
-  r.w = Magic<T>::fix(prmt(w1, Magic<T>::BYTES, 0x4342u), s2, b2);
-  return r;
+// 8 consecutive codes (one word at 4 bits, two words at 8 bits) -> 8 dequantised 16-bit values, k order,
+// as four packed pairs (the layout of four consecutive TMEM columns of an A row).
+template <typename T, int BITS>
+__device__ __forceinline__ void dequant8(const uint32_t* pw, uint32_t s2, uint32_t b2, uint32_t* out) {
+  typedef H2<T> H;
+  if constexpr (BITS == 4) {
+    const uint32_t w = pw[0];
+    uint32_t a04, a15, a26, a37;
+    if constexpr (std::is_same<T, __half>::value) {
+      const uint32_t t = w >> 8;
+      a04 = H::fma(H::q_lo(lop3_and_or(w, 0x000f000fu, H::MAGIC)), s2, b2);     // codes 0 | 4
+      a15 = H::fma(H::q_hi(lop3_and_or(w, 0x00f000f0u, H::MAGIC)), s2, b2);     // codes 1 | 5 (x16 in the mantissa)
+      a26 = H::fma(H::q_lo(lop3_and_or(t, 0x000f000fu, H::MAGIC)), s2, b2);     // codes 2 | 6
+      a37 = H::fma(H::q_hi(lop3_and_or(t, 0x00f000f0u, H::MAGIC)), s2, b2);     // codes 3 | 7
+    } else {
+      a04 = H::fma(H::q_lo(lop3_and_or(w, 0x000f000fu, H::MAGIC)), s2, b2);
+      a15 = H::fma(H::q_lo(lop3_and_or(w >> 4, 0x000f000fu, H::MAGIC)), s2, b2);
+      a26 = H::fma(H::q_lo(lop3_and_or(w >> 8, 0x000f000fu, H::MAGIC)), s2, b2);
+      a37 = H::fma(H::q_lo(lop3_and_or(w >> 12, 0x000f000fu, H::MAGIC)), s2, b2);
+    }
+    out[0] = prmt(a04, a15, 0x5410u);   // k0 k1
+    out[1] = prmt(a26, a37, 0x5410u);   // k2 k3
+    out[2] = prmt(a04, a15, 0x7632u);   // k4 k5
+    out[3] = prmt(a26, a37, 0x7632u);   // k6 k7
+  } else {
+    out[0] = H::fma(H::q_lo(prmt(pw[0], H::MAGIC_BYTES, 0x4140u)), s2, b2);
+    out[1] = H::fma(H::q_lo(prmt(pw[0], H::MAGIC_BYTES, 0x4342u)), s2, b2);
+    out[2] = H::fma(H::q_lo(prmt(pw[1], H::MAGIC_BYTES, 0x4140u)), s2, b2);
+    out[3] = H::fma(H::q_lo(prmt(pw[1], H::MAGIC_BYTES, 0x4342u)), s2, b2);
+  }
 }
 
 template <typename T> __device__ __forceinline__ uint32_t dup16(T v) {
@@ -172,93 +222,77 @@ template <typename T> __device__ __forceinline__ uint32_t dup16(T v) {
   return u | (u << 16);
 }
 
-__device__ __forceinline__ unsigned long long gtimer() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
-#define TL(slot)                                                                        \
-  do {                                                                                  \
-    if (p.tl != nullptr && blockIdx.y == 0 && blockIdx.z == 0 && blockIdx.x < 16)       \
-      p.tl[blockIdx.x * 16 + (slot)] = gtimer();                                        \
-  } while (0)
-
-#define TC(i, k)                                                                                      \
-  do {                                                                                                \
-    if (p.tl != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (i) >= 16 && (i) < 20) \
-      p.tl[256 + ((i) - 16) * 16 + (k)] = (unsigned long long)clock64();                               \
-  } while (0)
-
 __device__ __forceinline__ float silu_tc(float g) { return g / (1.0f + __expf(-g)); }
 
 // ------------------------------------------------------------------------------------------------ kernel
-constexpr int TC_THREADS = 320;
-constexpr int DQ_THREADS = 256;
-constexpr int A_STAGES = 3;
-constexpr int A_STAGE_BYTES = 2 * 128 * 128;  // two [128 x 64] 16-bit tiles
+constexpr int DQ_WARPS = 16;
+constexpr int DQ_THREADS = DQ_WARPS * 32;
+constexpr int TC_THREADS = 64 + DQ_THREADS;     // + TMA warp + MMA warp
+constexpr int TMEM_COLS = 512;
+constexpr int MAX_TN = 128;
+constexpr int W_TILE_BYTES = 128 * 128;          // one weight block of one stage: 128 rows x 128 packed bytes
 
 struct TcParams {
   const void* scales;
   const void* biases;
   void* y;
-  float* ws_partial;
-  int* ws_counter;
+  float* ws_acc;       // one fp32 [2*TN x 128] accumulator per CTA boundary (zero on entry, left zero)
+  int* ws_counter;     // one arrival counter per output tile (zero on entry, left zero)
   int M_tok, N, K, TN;
   int64_t ldy;
   int epi;
-  int num_kb;      // K / 64
-  int splits;
-  int kb_unit;     // 8 when scales/biases rows allow 128-bit loads (num_kb % 8 == 0), else 1
+  int num_kb;          // K / 64
+  int num_st;          // stages along K = ceil(num_kb / KPS)
+  int pairs, tiles_m;  // output tile t = pair * tiles_m + token tile
+  long long U;         // total units = pairs * tiles_m * num_st
+  int vec_sb;          // 1: scales/biases rows allow aligned 128-bit loads (num_kb % 8 == 0)
   int in_stages;
   int in_stage_bytes;
-  int tmem_cols;
-  unsigned long long* tl;   // optional per-CTA timeline (ns stamps), profiling only
-  int debug;        // bit0: skip dequant math+stores, bit1: skip MMA issue, bit2: skip epilogue stores (profiling only)
+  int debug;           // profiling only: 2 skip MMA issue, 4 skip epilogue + fix-up, 8 skip the TMEM store of A, 16 skip LDS + dequant math
 };
+
+// CTA that owns linear unit x when U units are dealt to G CTAs as [c*U/G, (c+1)*U/G)
+__device__ __forceinline__ int owner_of(long long x, long long U, int G) { return (int)(((x + 1) * G - 1) / U); }
 
 template <typename T, int BITS>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x, const TcParams p) {
   constexpr int PKB = 64 * BITS / 8;            // packed bytes per row per k-block
-  constexpr int W_STAGE_BYTES = 2 * 128 * PKB;
+  constexpr int KPS = 128 / PKB;                // k-blocks per stage (a stage row is one 128-byte line)
+  constexpr int LKPS = (KPS == 4) ? 2 : 1;
+  constexpr int W_STAGE_BYTES = 2 * W_TILE_BYTES;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  // carve: [A ring][IN ring][barriers]
-  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t a_ring = smem_base;
-  const uint32_t in_ring = a_ring + A_STAGES * A_STAGE_BYTES;
+  const uint32_t in_ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bar_base = in_ring + p.in_stages * p.in_stage_bytes;
-  // barrier layout (8 bytes each)
+  const int S = p.in_stages;
+  const int TN = p.TN;
+  // TMEM columns: D block b at b*TN; A ring behind it: slot s, block b at a_col0 + s*64 + b*32
+  const int NSLOT = TN > 64 ? 4 : 6;
+  const uint32_t a_col0 = TN > 64 ? 256u : 128u;
   auto full_in = [&](int s) { return bar_base + 8u * s; };
-  auto empty_in = [&](int s) { return bar_base + 8u * (p.in_stages + s); };
-  auto full_a = [&](int s) { return bar_base + 8u * (2 * p.in_stages + s); };
-  auto empty_a = [&](int s) { return bar_base + 8u * (2 * p.in_stages + A_STAGES + s); };
-  const uint32_t accum_full = bar_base + 8u * (2 * p.in_stages + 2 * A_STAGES);
-  const uint32_t tmem_slot = accum_full + 8u;
+  auto empty_in = [&](int s) { return bar_base + 8u * (S + s); };
+  auto full_a = [&](int s) { return bar_base + 8u * (2 * S + s); };
+  auto empty_a = [&](int s) { return bar_base + 8u * (2 * S + 8 + s); };
+  const uint32_t accum_full = bar_base + 8u * (2 * S + 16);
+  const uint32_t accum_empty = accum_full + 8u;
+  const uint32_t tmem_slot = accum_empty + 8u;
   const uint32_t flag_slot = tmem_slot + 4u;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int pair = blockIdx.x, tile = blockIdx.y, split = blockIdx.z;
-  const int TN = p.TN;
+  const int G = (int)gridDim.x, cta = (int)blockIdx.x;
+  const long long u_begin = (p.U * cta) / G, u_end = (p.U * (cta + 1)) / G;
   const bool silu = p.epi == B200P_EPI_SILU_MUL;
-  const int rowA0 = silu ? pair * 128 : pair * 256;
-  const int rowB0 = silu ? p.N / 2 + pair * 128 : pair * 256 + 128;
-  const int tok0 = tile * TN;
-  // K range of this split
-  const int n_units = p.num_kb / p.kb_unit;           // split boundaries fall on kb_unit multiples
-  const int kb_begin = p.kb_unit * (int)(((int64_t)n_units * split) / p.splits);
-  const int kb_end = (split == p.splits - 1) ? p.num_kb : p.kb_unit * (int)(((int64_t)n_units * (split + 1)) / p.splits);
-  const int nkb = kb_end - kb_begin;
 
-  if (threadIdx.x == 0) TL(0);
   if (threadIdx.x == 0) {
-    for (int s = 0; s < p.in_stages; ++s) { mbar_init(full_in(s), 1); mbar_init(empty_in(s), 1); }
-    for (int s = 0; s < A_STAGES; ++s) { mbar_init(full_a(s), DQ_THREADS / 32); mbar_init(empty_a(s), 1); }
+    for (int s = 0; s < S; ++s) { mbar_init(full_in(s), 1); mbar_init(empty_in(s), 1); }
+    for (int s = 0; s < NSLOT; ++s) { mbar_init(full_a(s), 8); mbar_init(empty_a(s), 1); }
     mbar_init(accum_full, 1);
+    mbar_init(accum_empty, DQ_WARPS);
     fence_barrier_init();
     tma_prefetch_desc(&tm_w);
     tma_prefetch_desc(&tm_x);
   }
-  if (warp == 1) tmem_alloc(tmem_slot, (uint32_t)p.tmem_cols);
+  if (warp == DQ_WARPS + 1) tmem_alloc(tmem_slot, TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -266,240 +300,274 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
   pdl_wait();   // X (and the residual) come from the previous kernel
-  if (threadIdx.x == 0) TL(1);
 
-  if (warp == 0) {
+  if (warp == DQ_WARPS) {
     // ===================================== TMA producer =====================================
-    if (lane == 0) {
-      const bool do_w = !(p.debug & 8), do_x = !(p.debug & 16);
-      const uint32_t tx = (uint32_t)((do_w ? W_STAGE_BYTES : 0) + (do_x ? TN * 128 : 0));
-      for (int i = 0; i < nkb; ++i) {
-        const int s = i % p.in_stages, ph = (i / p.in_stages) & 1;
-        TC(i, 12);
-        mbar_wait(empty_in(s), ph ^ 1);
-        TC(i, 13);
-        const uint32_t dst = in_ring + s * p.in_stage_bytes;
-        if (tx) mbar_arrive_expect_tx(full_in(s), tx); else mbar_arrive(full_in(s));
-        const int kb = kb_begin + i;
-        if (do_w) {
-          tma_load_2d(dst, &tm_w, kb * PKB, rowA0, full_in(s));
-          tma_load_2d(dst + 128 * PKB, &tm_w, kb * PKB, rowB0, full_in(s));
+    {
+      const uint32_t tx = (uint32_t)(W_STAGE_BYTES + KPS * TN * 128);
+      int si = 0, ph = 0;
+      for (long long u = u_begin; u < u_end;) {
+        const int tile = (int)(u / p.num_st), s0 = (int)(u % p.num_st);
+        const int ns = (int)min((long long)(p.num_st - s0), u_end - u);
+        const int pair = tile / p.tiles_m, tm = tile % p.tiles_m;
+        const int rowA0 = silu ? pair * 128 : pair * 256;
+        const int rowB0 = silu ? p.N / 2 + pair * 128 : pair * 256 + 128;
+        for (int st = s0; st < s0 + ns; ++st) {
+          mbar_wait(empty_in(si), ph ^ 1);
+          const uint32_t dst = in_ring + si * p.in_stage_bytes;
+          if (elect_one()) {
+            mbar_arrive_expect_tx(full_in(si), tx);
+            tma_load_2d(dst, &tm_w, st * 128, rowA0, full_in(si));
+            tma_load_2d(dst + W_TILE_BYTES, &tm_w, st * 128, rowB0, full_in(si));
+#pragma unroll
+            for (int jj = 0; jj < KPS; ++jj)
+              tma_load_2d(dst + W_STAGE_BYTES + jj * TN * 128, &tm_x, (st * KPS + jj) * 64, tm * TN, full_in(si));
+          }
+          __syncwarp();
+          if (++si == S) { si = 0; ph ^= 1; }
         }
-        if (do_x) tma_load_2d(dst + W_STAGE_BYTES, &tm_x, kb * 64, tok0, full_in(s));
-        if (i == 0) TL(2);
-        if (i == nkb - 1) TL(3);
+        u += ns;
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == DQ_WARPS + 1) {
     // ===================================== MMA issuer =======================================
     // instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32 (1<<4), a/b format (0 f16, 1 bf16) at
     // bits 7/10, K-major A and B, N>>3 at bit 17, M>>4 at bit 24
-    const uint32_t fmt = (sizeof(T) == 2 && std::is_same<T, __nv_bfloat16>::value) ? 1u : 0u;
+    const uint32_t fmt = std::is_same<T, __nv_bfloat16>::value ? 1u : 0u;
     const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(TN >> 3) << 17) | ((128u >> 4) << 24);
-    for (int i = 0; i < nkb; ++i) {
-      const int si = i % p.in_stages, phi = (i / p.in_stages) & 1;
-      const int sa = i % A_STAGES, pha = (i / A_STAGES) & 1;
-      if (lane == 0) TC(i, 8);
-      mbar_wait(full_in(si), phi);
-      if (lane == 0) TC(i, 9);
-      mbar_wait(full_a(sa), pha);
-      tc_fence_after();
-      if (lane == 0) TC(i, 10);
-      if (lane == 0) {
-        if (!(p.debug & 2)) {
-        const uint32_t xs = in_ring + si * p.in_stage_bytes + W_STAGE_BYTES;
-        const uint32_t as = a_ring + sa * A_STAGE_BYTES;
-#pragma unroll
-        for (int blk = 0; blk < 2; ++blk) {
-#pragma unroll
-          for (int k4 = 0; k4 < 4; ++k4) {
-            const uint64_t ad = make_desc_sw128(as + blk * (128 * 128) + k4 * 32);
-            const uint64_t bd = make_desc_sw128(xs + k4 * 32);
-            umma_f16(tmem_base + (uint32_t)(blk * TN), ad, bd, idesc, (i > 0 || k4 > 0) ? 1u : 0u);
-          }
-        }
-        }
-        if (p.debug & 64) {
-          mbar_arrive(empty_in(si)); mbar_arrive(empty_a(sa));
-          if (i == nkb - 1) mbar_arrive(accum_full);
-        } else {
-        umma_commit(empty_in(si));
-        umma_commit(empty_a(sa));
-        if (i == nkb - 1) umma_commit(accum_full);
-        }
-        TC(i, 11);
+    int si = 0, ph = 0, slot = 0, pha = 0, seg = 0;
+    for (long long u = u_begin; u < u_end; ++seg) {
+      const int s0 = (int)(u % p.num_st);
+      const int ns = (int)min((long long)(p.num_st - s0), u_end - u);
+      if (seg > 0) {                                  // the epilogue of the previous segment has drained D
+        mbar_wait(accum_empty, (uint32_t)((seg - 1) & 1));
+        tc_fence_after();
       }
-      __syncwarp();
-      if (lane == 0 && i == 0) TL(4);
-      if (lane == 0 && i == nkb - 1) TL(5);
+      for (int j = 0; j < ns; ++j) {
+        mbar_wait(full_in(si), (uint32_t)ph);
+        const uint32_t xs = in_ring + si * p.in_stage_bytes + W_STAGE_BYTES;
+        for (int jj = 0; jj < KPS; ++jj) {
+          mbar_wait(full_a(slot), (uint32_t)pha);
+          tc_fence_after();
+          if (elect_one()) {
+            if (!(p.debug & 2)) {
+#pragma unroll
+              for (int blk = 0; blk < 2; ++blk) {
+#pragma unroll
+                for (int k4 = 0; k4 < 4; ++k4) {
+                  const uint32_t at = tmem_base + a_col0 + (uint32_t)(slot * 64 + blk * 32 + k4 * 8);
+                  umma_f16_ts(tmem_base + (uint32_t)(blk * TN), at, make_desc_sw128(xs + jj * TN * 128 + k4 * 32), idesc,
+                              (j > 0 || jj > 0 || k4 > 0) ? 1u : 0u);
+                }
+              }
+            }
+            umma_commit(empty_a(slot));
+            if (jj == KPS - 1) {
+              umma_commit(empty_in(si));
+              if (j == ns - 1) umma_commit(accum_full);
+            }
+          }
+          __syncwarp();
+          if (++slot == NSLOT) { slot = 0; pha ^= 1; }
+        }
+        if (++si == S) { si = 0; ph ^= 1; }
+      }
+      u += ns;
     }
   } else {
     // ===================================== dequantisers =====================================
-    const int dt = threadIdx.x - 64;                 // 0..255 : one weight row of the pair each
-    const int blk = dt >> 7, r = dt & 127;
-    const int grow = (blk ? rowB0 : rowA0) + r;      // global weight row
-    const bool row_ok = grow < p.N;
-    const T* sp = reinterpret_cast<const T*>(p.scales) + (int64_t)(row_ok ? grow : 0) * p.num_kb;
-    const T* bp = reinterpret_cast<const T*>(p.biases) + (int64_t)(row_ok ? grow : 0) * p.num_kb;
-    // swizzled positions
-    const uint32_t a_row_off = (uint32_t)(blk * (128 * 128) + (r >> 3) * 1024 + (r & 7) * 128);
-    const uint32_t a_xor = (uint32_t)(r & 7);
-    // TMA SWIZZLE_32B / SWIZZLE_64B of the packed tile: 16-byte chunk index ^= address bits [7, 7+log2(PKB/16))
-    const uint32_t w_sw = (BITS == 4) ? ((uint32_t)(dt >> 2) & 1u) : ((uint32_t)(dt >> 1) & 3u);
-
-    auto process = [&](int i, uint32_t s2, uint32_t b2) {
-      const int si = i % p.in_stages, phi = (i / p.in_stages) & 1;
-      const int sa = i % A_STAGES, pha = (i / A_STAGES) & 1;
-      if (dt == 0) TC(i, 0);
-      mbar_wait(full_in(si), phi);
-      if (dt == 0) TC(i, 1);
-      if (dt == 0 && i == 0) TL(6);
-      if (dt == 0 && i == 8) TL(12);
-      if (dt == 0 && i == 16) TL(13);
-      const uint32_t wsrc = in_ring + si * p.in_stage_bytes + (uint32_t)(dt * PKB);
-      uint4 pk[PKB / 16];
-#pragma unroll
-      for (int c = 0; c < PKB / 16; ++c) pk[c] = lds128(wsrc + (((uint32_t)c ^ w_sw) << 4));
-      if (dt == 0) TC(i, 2);
-      mbar_wait(empty_a(sa), pha ^ 1);
-      if (dt == 0) TC(i, 3);
-      const uint32_t adst = a_ring + sa * A_STAGE_BYTES + a_row_off;
-      const uint32_t* pw = reinterpret_cast<const uint32_t*>(pk);
-      if (!(p.debug & 1)) {
-#pragma unroll
-        for (int c = 0; c < 8; ++c) {                // 8 chunks of 8 values = 64 k
-          uint4 v = (BITS == 4) ? dequant_word4<T>(pw[c], s2, b2) : dequant_word8<T>(pw[2 * c], pw[2 * c + 1], s2, b2);
-          sts128(adst + (((uint32_t)c ^ a_xor) << 4), v);
-        }
-      }
-      if (dt == 0) TC(i, 4);
-      if (!(p.debug & 32)) fence_proxy_async();      // generic-proxy stores -> visible to the tensor core (async proxy)
-      __syncwarp();
-      if (lane == 0) mbar_arrive(full_a(sa));
-      if (dt == 0) TC(i, 5);
-      if (dt == 0 && i == 0) TL(7);
-      if (dt == 0 && i == nkb - 1) TL(8);
-    };
-
-    if (p.kb_unit == 8) {
-      // scales / biases of 8 consecutive k-blocks per 128-bit load, prefetched one group (8 k-blocks) ahead
-      const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
-      const uint4* sp4 = reinterpret_cast<const uint4*>(sp + kb_begin);
-      const uint4* bp4 = reinterpret_cast<const uint4*>(bp + kb_begin);
-      uint4 sv_n = (row_ok && nkb > 0) ? ldg_stream(sp4) : z4;
-      uint4 bv_n = (row_ok && nkb > 0) ? ldg_stream(bp4) : z4;
-      for (int i0 = 0; i0 < nkb; i0 += 8) {
-        const uint4 sv = sv_n, bv = bv_n;
-        if (i0 + 8 < nkb && row_ok) { sv_n = ldg_stream(sp4 + (i0 >> 3) + 1); bv_n = ldg_stream(bp4 + (i0 >> 3) + 1); }
-        const uint32_t sw[4] = {sv.x, sv.y, sv.z, sv.w}, bw[4] = {bv.x, bv.y, bv.z, bv.w};
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          if (i0 + j < nkb) {
-            const uint32_t s2 = (j & 1) ? prmt(sw[j >> 1], 0u, 0x3232u) : prmt(sw[j >> 1], 0u, 0x1010u);
-            const uint32_t b2 = (j & 1) ? prmt(bw[j >> 1], 0u, 0x3232u) : prmt(bw[j >> 1], 0u, 0x1010u);
-            process(i0 + j, s2, b2);
-          }
-        }
-      }
-    } else {
-      const T zero = Tr<T>::from_f(0.f);
-      T s_next = row_ok && nkb > 0 ? sp[kb_begin] : zero;
-      T b_next = row_ok && nkb > 0 ? bp[kb_begin] : zero;
-      for (int i = 0; i < nkb; ++i) {
-        const uint32_t s2 = dup16(s_next), b2 = dup16(b_next);
-        if (i + 1 < nkb && row_ok) { s_next = sp[kb_begin + i + 1]; b_next = bp[kb_begin + i + 1]; }
-        process(i, s2, b2);
-      }
-    }
-
-    // ===================================== epilogue =========================================
-    mbar_wait(accum_full, 0);
-    tc_fence_after();
-    if (dt == 0) TL(9);
-    const int q = warp & 3;                          // TMEM lane quarter this warp may read
-    const int th = (warp - 2) >> 2;                  // token half
-    const int er = q * 32 + lane;                    // row within the 128-row block
-    const int n0 = rowA0 + er, n1 = rowB0 + er;
-    const int t_lo = th * (TN / 2), t_hi = t_lo + TN / 2;
+    const int grp = warp >> 2;                         // 0..3
+    const int blk = grp & 1, kpar = grp >> 1;
+    const int q = warp & 3;                          // TMEM lane quarter this warp may touch
+    const int r = q * 32 + lane;                     // weight row within the 128-row block
     const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
-    const bool multi = p.splits > 1;
-    float* part = nullptr;
-    const int tile_id = blockIdx.y * gridDim.x + blockIdx.x;
-    if (multi) part = p.ws_partial + ((int64_t)tile_id * p.splits + split) * (2 * (int64_t)TN * 128);
+    // SWIZZLE_128B tile [128 rows x 128 B]: row r at (r/8)*1024 + (r%8)*128, 16-byte chunk c at (c ^ (r%8))
+    const uint32_t w_row_off = (uint32_t)(blk * W_TILE_BYTES + (r >> 3) * 1024 + (r & 7) * 128);
+    const uint32_t w_xor = (uint32_t)(r & 7);
+    const int dq_tid = threadIdx.x;
 
-    auto finish = [&](int t, float a0, float a1) {   // final epilogue for token t (tile-local), rows n0 / n1
-      const int tok = tok0 + t;
-      if (tok >= p.M_tok) return;
-      if (p.epi == B200P_EPI_STORE) {
-        T* y = reinterpret_cast<T*>(p.y) + (int64_t)tok * p.ldy;
-        if (n0 < p.N) y[n0] = Tr<T>::from_f(a0);
-        if (n1 < p.N) y[n1] = Tr<T>::from_f(a1);
-      } else if (p.epi == B200P_EPI_STORE_F32) {
-        float* y = reinterpret_cast<float*>(p.y) + (int64_t)tok * p.ldy;
-        if (n0 < p.N) y[n0] = a0;
-        if (n1 < p.N) y[n1] = a1;
-      } else if (p.epi == B200P_EPI_ADD_RESIDUAL) {
-        float* y = reinterpret_cast<float*>(p.y) + (int64_t)tok * p.ldy;
-        if (n0 < p.N) y[n0] += a0;
-        if (n1 < p.N) y[n1] += a1;
-      } else {
-        T* y = reinterpret_cast<T*>(p.y) + (int64_t)tok * p.ldy;
-        if (n0 < p.N / 2) y[n0] = Tr<T>::from_f(silu_tc(a0) * a1);
-      }
-    };
+    int seg = 0;
+    // position of the next k-block this thread handles: global k-block iteration, its stage ring slot, its A slot
+    int it_mine = kpar, st_mine = 0, si = 0, ph = 0, slot = kpar, pha = 0;
+    for (long long u = u_begin; u < u_end; ++seg) {
+      const int tile = (int)(u / p.num_st), s0 = (int)(u % p.num_st);
+      const int ns = (int)min((long long)(p.num_st - s0), u_end - u);
+      const int pair = tile / p.tiles_m, tm = tile % p.tiles_m;
+      const int rowA0 = silu ? pair * 128 : pair * 256;
+      const int rowB0 = silu ? p.N / 2 + pair * 128 : pair * 256 + 128;
+      const int tok0 = tm * TN;
+      const int grow = (blk ? rowB0 : rowA0) + r;
+      const bool row_ok = grow < p.N;
+      const T* sp = reinterpret_cast<const T*>(p.scales) + (int64_t)(row_ok ? grow : 0) * p.num_kb;
+      const T* bp = reinterpret_cast<const T*>(p.biases) + (int64_t)(row_ok ? grow : 0) * p.num_kb;
+      const int kb_lo = s0 * KPS, kb_hi = (s0 + ns) * KPS;     // k-blocks of this segment (the tail may pass num_kb)
 
-    for (int t = t_lo; t < t_hi && !(p.debug & 4); t += 8) {
-      float v0[8], v1[8];
-      tmem_ld8(lane_base + (uint32_t)t, v0);
-      tmem_ld8(lane_base + (uint32_t)(TN + t), v1);
-      tmem_ld_wait();
-      if (!multi) {
+      auto process = [&](uint32_t s2, uint32_t b2) {
+        mbar_wait(full_in(si), (uint32_t)ph);
+        const int jj = it_mine & (KPS - 1);
+        const uint32_t wsrc = in_ring + si * p.in_stage_bytes + w_row_off;
+        uint32_t o[32];
+        if (!(p.debug & 16)) {
+          uint4 pk[PKB / 16];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) finish(t + j, v0[j], v1[j]);
-      } else {
+          for (int c = 0; c < PKB / 16; ++c) pk[c] = lds128(wsrc + ((((uint32_t)(jj * (PKB / 16) + c)) ^ w_xor) << 4));
+          const uint32_t* pw = reinterpret_cast<const uint32_t*>(pk);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          part[(int64_t)(t + j) * 128 + er] = v0[j];
-          part[((int64_t)TN + t + j) * 128 + er] = v1[j];
+          for (int c = 0; c < 8; ++c) dequant8<T, BITS>(pw + c * (BITS / 4), s2, b2, o + 4 * c);
+        } else {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) o[c] = s2;
         }
-      }
-    }
-    if (multi) {
-      __threadfence();
-      named_bar_sync(1, DQ_THREADS);
-      if (dt == 0) {
-        int old = atomicAdd(p.ws_counter + tile_id, 1);
-        int last = (old == p.splits - 1);
-        if (last) p.ws_counter[tile_id] = 0;          // self-cleaning for the next launch
-        asm volatile("st.shared.u32 [%0], %1;" ::"r"(flag_slot), "r"(last) : "memory");
-      }
-      named_bar_sync(1, DQ_THREADS);
-      int last;
-      asm volatile("ld.shared.u32 %0, [%1];" : "=r"(last) : "r"(flag_slot));
-      if (last) {
-        __threadfence();
-        const float* base = p.ws_partial + (int64_t)tile_id * p.splits * (2 * (int64_t)TN * 128);
-        for (int t = t_lo; t < t_hi; ++t) {
-          if (tok0 + t >= p.M_tok) break;
-          float a0 = 0.f, a1 = 0.f;
-          for (int s = 0; s < p.splits; ++s) {        // fixed order -> deterministic
-            const float* ps = base + (int64_t)s * (2 * (int64_t)TN * 128);
-            a0 += __ldcg(ps + (int64_t)t * 128 + er);
-            a1 += __ldcg(ps + ((int64_t)TN + t) * 128 + er);
+        mbar_wait(empty_a(slot), (uint32_t)(pha ^ 1));
+        tc_fence_after();
+        if (!(p.debug & 8)) {
+          tmem_st32(lane_base + a_col0 + (uint32_t)(slot * 64 + blk * 32), o);
+          tmem_st_wait();
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(full_a(slot));
+        it_mine += 2;
+        const int st_new = it_mine >> LKPS;
+        if (st_new != st_mine) { st_mine = st_new; if (++si == S) { si = 0; ph ^= 1; } }
+        slot += 2;
+        if (slot >= NSLOT) { slot -= NSLOT; pha ^= 1; }
+      };
+
+      // this thread takes the k-blocks of parity kpar (stage starts are even, so global and local parity agree)
+      if (p.vec_sb) {
+        // scales / biases of 8 consecutive k-blocks per 128-bit load, prefetched one group ahead
+        const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
+        const uint4* sp4 = reinterpret_cast<const uint4*>(sp);
+        const uint4* bp4 = reinterpret_cast<const uint4*>(bp);
+        const int g_first = kb_lo >> 3, g_last = (kb_hi - 1) >> 3;
+        const uint32_t sel = kpar ? 0x3232u : 0x1010u;
+        uint4 sv_n = row_ok ? __ldg(sp4 + g_first) : z4;
+        uint4 bv_n = row_ok ? __ldg(bp4 + g_first) : z4;
+        for (int g8 = g_first; g8 <= g_last; ++g8) {
+          const uint4 sv = sv_n, bv = bv_n;
+          if (g8 < g_last && row_ok) { sv_n = __ldg(sp4 + g8 + 1); bv_n = __ldg(bp4 + g8 + 1); }
+          const uint32_t sw[4] = {sv.x, sv.y, sv.z, sv.w}, bw[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+          for (int j2 = 0; j2 < 4; ++j2) {
+            const int kb = g8 * 8 + 2 * j2 + kpar;
+            if (kb >= kb_lo && kb < kb_hi) process(prmt(sw[j2], 0u, sel), prmt(bw[j2], 0u, sel));
           }
-          finish(t, a0, a1);
+        }
+      } else {
+        const T zero = Tr<T>::from_f(0.f);
+        for (int kb = kb_lo + kpar; kb < kb_hi; kb += 2) {
+          const bool ok = row_ok && kb < p.num_kb;            // k-blocks past K are zero-filled by TMA: A = 0
+          const T sv = ok ? sp[kb] : zero, bv = ok ? bp[kb] : zero;
+          process(dup16(sv), dup16(bv));
         }
       }
+
+      // ===================================== epilogue of the segment =========================
+      mbar_wait(accum_full, (uint32_t)(seg & 1));
+      tc_fence_after();
+      const int n0 = rowA0 + r, n1 = rowB0 + r;        // output columns of this thread (block 0 / block 1)
+      const bool full = (s0 == 0 && ns == p.num_st);
+      // a tile shared by several CTAs is summed with L2 atomics: straight into y for ADD_RESIDUAL, else into the
+      // fp32 accumulator owned by the tile's first CTA; the last CTA to arrive applies the epilogue and re-zeroes it
+      const bool via_acc = !full && p.epi != B200P_EPI_ADD_RESIDUAL;
+      const int c_first = via_acc ? owner_of((long long)tile * p.num_st, p.U, G) : cta;
+      float* acc = p.ws_acc + (int64_t)c_first * (2 * (int64_t)TN * 128);
+
+      auto finish = [&](int t, float a0, float a1) {   // final epilogue for token t (tile-local), rows n0 / n1
+        const int tok = tok0 + t;
+        if (tok >= p.M_tok) return;
+        if (p.epi == B200P_EPI_STORE) {
+          T* y = reinterpret_cast<T*>(p.y) + (int64_t)tok * p.ldy;
+          if (n0 < p.N) y[n0] = Tr<T>::from_f(a0);
+          if (n1 < p.N) y[n1] = Tr<T>::from_f(a1);
+        } else if (p.epi == B200P_EPI_STORE_F32) {
+          float* y = reinterpret_cast<float*>(p.y) + (int64_t)tok * p.ldy;
+          if (n0 < p.N) y[n0] = a0;
+          if (n1 < p.N) y[n1] = a1;
+        } else if (p.epi == B200P_EPI_ADD_RESIDUAL) {
+          float* y = reinterpret_cast<float*>(p.y) + (int64_t)tok * p.ldy;
+          if (full) {
+            if (n0 < p.N) y[n0] += a0;
+            if (n1 < p.N) y[n1] += a1;
+          } else {
+            if (n0 < p.N) atomicAdd(y + n0, a0);
+            if (n1 < p.N) atomicAdd(y + n1, a1);
+          }
+        } else {
+          T* y = reinterpret_cast<T*>(p.y) + (int64_t)tok * p.ldy;
+          if (n0 < p.N / 2) y[n0] = Tr<T>::from_f(silu_tc(a0) * a1);
+        }
+      };
+
+      // 8-token chunks are dealt round-robin to the four warp groups; every thread reads both blocks' rows
+      for (int t = grp * 8; t < TN && !(p.debug & 4); t += 32) {
+        float v0[8], v1[8];
+        tmem_ld8(lane_base + (uint32_t)t, v0);
+        tmem_ld8(lane_base + (uint32_t)(TN + t), v1);
+        tmem_ld_wait();
+        if (!via_acc) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) finish(t + j, v0[j], v1[j]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            if (tok0 + t + j < p.M_tok) {
+              if (p.debug & 32) {
+                acc[(int64_t)(t + j) * 128 + r] = v0[j];
+                acc[((int64_t)TN + t + j) * 128 + r] = v1[j];
+              } else {
+                atomicAdd(acc + (int64_t)(t + j) * 128 + r, v0[j]);
+                atomicAdd(acc + ((int64_t)TN + t + j) * 128 + r, v1[j]);
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(accum_empty);         // D may be overwritten by the next segment's MMAs
+      if (via_acc && !(p.debug & (4 | 64))) {
+        const int nseg = owner_of((long long)tile * p.num_st + p.num_st - 1, p.U, G) - c_first + 1;
+        __threadfence();
+        named_bar_sync(1, DQ_THREADS);
+        if (dq_tid == 0) {
+          const int old = atomicAdd(p.ws_counter + tile, 1);
+          const int last = (old == nseg - 1);
+          if (last) p.ws_counter[tile] = 0;            // self-cleaning for the next launch
+          asm volatile("st.shared.u32 [%0], %1;" ::"r"(flag_slot), "r"(last) : "memory");
+        }
+        named_bar_sync(1, DQ_THREADS);
+        int last;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(last) : "r"(flag_slot));
+        if (last) {
+          __threadfence();
+          for (int t = grp * 8; t < TN; t += 32) {
+            float v0[8], v1[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {               // 16 independent L2 loads in flight
+              v0[j] = __ldcg(acc + (int64_t)(t + j) * 128 + r);
+              v1[j] = __ldcg(acc + ((int64_t)TN + t + j) * 128 + r);
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              finish(t + j, v0[j], v1[j]);
+              __stcg(acc + (int64_t)(t + j) * 128 + r, 0.f);
+              __stcg(acc + ((int64_t)TN + t + j) * 128 + r, 0.f);
+            }
+          }
+        }
+        named_bar_sync(1, DQ_THREADS);                 // flag_slot is reused by the next segment
+      }
+      u += ns;
     }
-    tc_fence_before();
-    if (dt == 0) TL(10);
   }
   pdl_launch_dependents();
+  tc_fence_before();
   __syncthreads();
-  if (threadIdx.x == 0) TL(11);
-  if (warp == 1) {
+  if (warp == DQ_WARPS + 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols);
+    tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 
@@ -507,9 +575,6 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static unsigned long long* g_timeline = nullptr;
-extern "C" void b200p_debug_set_timeline(void* dev_ptr) { g_timeline = (unsigned long long*)dev_ptr; }
 
 static EncodeTiledFn get_encode() {
   static EncodeTiledFn fn = nullptr;
@@ -523,41 +588,32 @@ static EncodeTiledFn get_encode() {
 }
 
 constexpr int SMEM_BUDGET = 227 * 1024;
-constexpr int MIN_TC_M = 5;      // below this the CUDA-core GEMV wins (weights read once either way)
+constexpr int MIN_TC_M = 5;        // below this the CUDA-core GEMV wins (weights read once either way)
+constexpr int MIN_UNITS_PER_CTA = 2;
 
 struct TcPlan {
-  int kb_unit;
-  int TN, tiles, pairs, splits, in_stages, in_stage_bytes, tmem_cols, smem_bytes;
+  int TN, tiles_m, pairs, grid, in_stages, in_stage_bytes, smem_bytes;
+  long long U;
 };
 
 static TcPlan make_plan(int64_t M, int64_t N, int64_t K, int bits, int epi) {
   TcPlan pl;
-  int tn = (int)(M >= 256 ? 256 : ((M + 15) / 16) * 16);
+  const int tn = (int)(M >= MAX_TN ? MAX_TN : ((M + 15) / 16) * 16);
   pl.TN = tn;
-  pl.tiles = (int)((M + tn - 1) / tn);
+  pl.tiles_m = (int)((M + tn - 1) / tn);
   pl.pairs = (int)(epi == B200P_EPI_SILU_MUL ? (N / 2 + 127) / 128 : (N + 255) / 256);
-  const int num_kb = (int)(K / 64);
-  const int ctas = pl.pairs * pl.tiles;
+  const int kps = bits == 4 ? 4 : 2;                       // k-blocks per 128-byte stage row
+  const int num_st = (int)((K / 64 + kps - 1) / kps);
+  pl.U = (long long)pl.pairs * pl.tiles_m * num_st;
+  long long g = (pl.U + MIN_UNITS_PER_CTA - 1) / MIN_UNITS_PER_CTA;
   const int sms = sm_count();
-  pl.kb_unit = (num_kb % 8 == 0) ? 8 : 1;
-  int splits = 1;
-  if (ctas < (sms * 3) / 4) {
-    splits = sms / ctas;
-    int max_by_k = pl.kb_unit == 8 ? num_kb / 8 : num_kb / 4;
-    if (splits > max_by_k) splits = max_by_k;
-    if (splits < 1) splits = 1;
-  }
-  pl.splits = splits;
-  const int pkb = 64 * bits / 8;
-  pl.in_stage_bytes = 2 * 128 * pkb + tn * 128;
-  int avail = SMEM_BUDGET - 1024 /*align*/ - A_STAGES * A_STAGE_BYTES - 512 /*barriers*/;
+  pl.grid = (int)(g > sms ? sms : (g < 1 ? 1 : g));
+  pl.in_stage_bytes = 2 * W_TILE_BYTES + kps * tn * 128;
+  const int avail = SMEM_BUDGET - 1024 /*align*/ - 512 /*barriers*/;
   int st = avail / pl.in_stage_bytes;
-  if (st > 12) st = 12;
+  if (st > 8) st = 8;
   pl.in_stages = st;
-  int cols = 32;
-  while (cols < 2 * tn) cols <<= 1;
-  pl.tmem_cols = cols;
-  pl.smem_bytes = 1024 + A_STAGES * A_STAGE_BYTES + st * pl.in_stage_bytes + 512;
+  pl.smem_bytes = 1024 + st * pl.in_stage_bytes + 512;
   return pl;
 }
 
@@ -570,23 +626,22 @@ bool qmm_tc_supported(int64_t M, int64_t N, int64_t K, int gs, int bits, int dty
   if (N % 8 != 0) return false;
   if (epi == B200P_EPI_SILU_MUL && (N / 2) % 8 != 0) return false;
   if (N >= (1ll << 31) || M >= (1ll << 31)) return false;
-  TcPlan pl = make_plan(M, N, K, bits, epi);
-  return pl.in_stages >= 2;
+  return true;
+}
+
+static size_t ws_counter_bytes(int64_t M, int64_t N) {
+  const int64_t tn = M >= MAX_TN ? MAX_TN : ((M + 15) / 16) * 16;
+  const int64_t tiles_m = (M + tn - 1) / tn;
+  return ((size_t)(tiles_m * ((N + 255) / 256 + 1)) * sizeof(int) + 255) & ~(size_t)255;
 }
 
 size_t qmm_tc_workspace_bytes(int64_t M, int64_t N, int64_t K) {
-  // worst case over epilogues / bit widths for this shape: counters + split-K partials
-  size_t best = 0;
-  for (int epi = 0; epi < 4; epi += 3) {
-    for (int bits = 4; bits <= 8; bits += 4) {
-      if (M < MIN_TC_M || K % 64) continue;
-      TcPlan pl = make_plan(M, N, K, bits, epi);
-      size_t counters = ((size_t)pl.pairs * pl.tiles * sizeof(int) + 255) & ~(size_t)255;
-      size_t partial = pl.splits > 1 ? (size_t)pl.pairs * pl.tiles * pl.splits * 2 * pl.TN * 128 * sizeof(float) : 0;
-      if (counters + partial > best) best = counters + partial;
-    }
-  }
-  return best;
+  (void)K;
+  if (M < MIN_TC_M) return 0;
+  const int64_t tn = M >= MAX_TN ? MAX_TN : ((M + 15) / 16) * 16;
+  // per-tile arrival counters + one fp32 [2*TN x 128] accumulator per CTA boundary; all must be ZERO on first use
+  // (the kernel leaves them zero)
+  return ws_counter_bytes(M, N) + (size_t)sm_count() * 2 * tn * 128 * sizeof(float);
 }
 
 template <typename T, int BITS>
@@ -598,8 +653,7 @@ static int launch_tc(const CUtensorMap& tmw, const CUtensorMap& tmx, const TcPar
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(qmm_tc_kernel)");
     attr_set = true;
   }
-  dim3 grid((unsigned)pl.pairs, (unsigned)pl.tiles, (unsigned)pl.splits);
-  kern<<<grid, TC_THREADS, pl.smem_bytes, st>>>(tmw, tmx, p);
+  kern<<<dim3((unsigned)pl.grid), TC_THREADS, pl.smem_bytes, st>>>(tmw, tmx, p);
   B200P_LAUNCH_CHECK("qmm_tc_kernel");
   return B200P_OK;
 }
@@ -610,15 +664,15 @@ int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b
   EncodeTiledFn enc = get_encode();
   B200P_REQUIRE(enc != nullptr, B200P_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
   TcPlan pl = make_plan(M, N, K, bits, epi);
-  const int pkb = 64 * bits / 8;
+  B200P_REQUIRE(pl.in_stages >= 2, B200P_ERR_ARG, "shared memory too small for the tensor path");
   CUtensorMap tmw, tmx;
   {
     cuuint64_t dims[2] = {(cuuint64_t)(K * bits / 8), (cuuint64_t)N};
     cuuint64_t strides[1] = {(cuuint64_t)(K * bits / 8)};
-    cuuint32_t box[2] = {(cuuint32_t)pkb, 128u};
+    cuuint32_t box[2] = {128u, 128u};
     cuuint32_t estr[2] = {1u, 1u};
     CUresult r = enc(&tmw, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<uint32_t*>(w), dims, strides, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, bits == 4 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_64B,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                      CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     B200P_REQUIRE(r == CUDA_SUCCESS, B200P_ERR_CUDA, "cuTensorMapEncodeTiled(weights) failed: %d", (int)r);
   }
@@ -634,15 +688,16 @@ int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b
   }
   TcParams p;
   p.scales = s; p.biases = b; p.y = y;
-  size_t counters = ((size_t)pl.pairs * pl.tiles * sizeof(int) + 255) & ~(size_t)255;
-  p.ws_counter = reinterpret_cast<int*>(ws);
-  p.ws_partial = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + counters);
-  size_t need = counters + (pl.splits > 1 ? (size_t)pl.pairs * pl.tiles * pl.splits * 2 * pl.TN * 128 * sizeof(float) : 0);
+  const size_t counters = ws_counter_bytes(M, N);
+  const size_t need = counters + (size_t)pl.grid * 2 * pl.TN * 128 * sizeof(float);
   B200P_REQUIRE(ws_bytes >= need && aligned(ws, 16), B200P_ERR_ARG, "qmm workspace too small (%zu < %zu)", ws_bytes, need);
+  p.ws_counter = reinterpret_cast<int*>(ws);
+  p.ws_acc = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + counters);
   p.M_tok = (int)M; p.N = (int)N; p.K = (int)K; p.TN = pl.TN; p.ldy = ldy; p.epi = epi;
-  p.num_kb = (int)(K / 64); p.splits = pl.splits; p.kb_unit = pl.kb_unit; p.in_stages = pl.in_stages; p.in_stage_bytes = pl.in_stage_bytes;
-  p.tmem_cols = pl.tmem_cols;
-  p.tl = g_timeline;
+  p.num_kb = (int)(K / 64); p.pairs = pl.pairs; p.tiles_m = pl.tiles_m; p.U = pl.U;
+  p.num_st = (p.num_kb + (bits == 4 ? 4 : 2) - 1) / (bits == 4 ? 4 : 2);
+  p.vec_sb = (p.num_kb % 8 == 0) ? 1 : 0;
+  p.in_stages = pl.in_stages; p.in_stage_bytes = pl.in_stage_bytes;
   { const char* d = getenv("B200P_TC_DEBUG"); p.debug = d ? atoi(d) : 0; }
   if (dtype == B200P_F16) {
     return bits == 4 ? launch_tc<__half, 4>(tmw, tmx, p, pl, st) : launch_tc<__half, 8>(tmw, tmx, p, pl, st);

@@ -278,11 +278,13 @@ def test_qmm_tensor_path_matches_oracle(ops, M, N, K, bits, dtype, epi):
     assert rel_err(got, exp) < tol
 
 
-def test_qmm_tensor_path_is_deterministic_and_matches_gemv(ops):
+def test_qmm_tensor_path_is_repeatable_and_matches_gemv(ops):
+    # stream-K tiles shared by several CTAs are summed with fp32 L2 atomics in arrival order: two runs agree to
+    # fp32 rounding of the partial sums (not bit for bit), and both agree with the CUDA-core GEMV path
     a1, _ = qmm_case(ops, 64, 512, 4096, 4, "float16", 1, seed=3, path=2)
     a2, _ = qmm_case(ops, 64, 512, 4096, 4, "float16", 1, seed=3, path=2)
     g, _ = qmm_case(ops, 64, 512, 4096, 4, "float16", 1, seed=3, path=1)
-    assert np.array_equal(a1, a2)
+    assert rel_err(a1, a2) < 1e-5
     assert rel_err(a1, g) < 1e-3
 
 
