@@ -121,11 +121,17 @@ class OraclePagedKVCache:
 class OracleModel:
     """Holds MLX-layout weights (numpy) and evaluates the reference graph."""
 
-    def __init__(self, cfg: OracleConfig, weights: Dict[str, np.ndarray], numerics: str = "reference"):
+    def __init__(self, cfg: OracleConfig, weights: Dict[str, np.ndarray], numerics: str = "reference",
+                 tp_allreduce=None, tp_gather=None):
+        """``tp_allreduce(partial) -> sum over ranks`` / ``tp_gather(local_logits) -> full logits`` turn this
+        into ONE RANK of the tensor-parallel decomposition (mlx_parallm_b200/tp.py: weights are the rank's
+        shards, cfg its local head counts); used by the world_size-2 gloo tests.  "mirror" numerics only."""
         self.cfg = cfg
         self.w = weights
         assert numerics in ("reference", "mirror")
+        assert tp_allreduce is None or numerics == "mirror", "the TP decomposition is checked in mirror numerics"
         self.numerics = numerics
+        self.tp_allreduce, self.tp_gather = tp_allreduce, tp_gather
         self._deq_cache: Dict[str, np.ndarray] = {}
 
     # -- helpers ---------------------------------------------------------------------------
@@ -199,6 +205,8 @@ class OracleModel:
             o = ops.sdpa(q, kf, vf, D ** -0.5, mask, odt)
             o = o.transpose(0, 2, 1, 3).reshape(B, L, H * D)
             r = self._linear(p + "self_attn.o_proj", o, cur if self.numerics == "reference" else None)
+            if self.tp_allreduce is not None:
+                r = self.tp_allreduce(r)
             h = (h + r).astype(np.float32) if self.numerics == "mirror" else ops.round_to(h + r, cur)
             x = ops.rms_norm(h, self._f32(p + "post_attention_layernorm.weight"), c.rms_norm_eps,
                              cur if self.numerics == "reference" else T)
@@ -212,13 +220,18 @@ class OracleModel:
                 g = self._linear(p + "mlp.gate_proj", x, None)
                 u = self._linear(p + "mlp.up_proj", x, None)
                 a = ops.round_to(ops.silu(g) * u, T)
-                h = (h + self._linear(p + "mlp.down_proj", a, None)).astype(np.float32)
+                r = self._linear(p + "mlp.down_proj", a, None)
+                if self.tp_allreduce is not None:
+                    r = self.tp_allreduce(r)
+                h = (h + r).astype(np.float32)
         if last_only:
             h = h[:, -1:, :]
         x = ops.rms_norm(h, self._f32("model.norm.weight"), c.rms_norm_eps,
                          cur if self.numerics == "reference" else T)
         head = "model.embed_tokens" if c.tie_word_embeddings else "lm_head"   # llama.py:249-252
         logits = self._linear(head, x, cur if self.numerics == "reference" else None)
+        if self.tp_gather is not None and not c.tie_word_embeddings:
+            logits = self.tp_gather(logits)
         return logits.astype(np.float32)
 
 
