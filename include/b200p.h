@@ -50,11 +50,23 @@ enum {
                                  rows [0,N/2) of w are gate_proj, rows [N/2,N) up_proj   */
 };
 
+/* Activation-layout flags OR-ed into the `epilogue` argument of b200p_qmm, and passed as `flags` to the producer
+ * kernels (b200p_rmsnorm, b200p_attn).  PERM8: inside every aligned group of 8 consecutive elements of a row
+ * the values sit in the order [0,4,1,5,2,6,3,7] -- the order in which the nibbles of a 4-bit weight word unpack as
+ * packed 16-bit pairs -- so the tensor path skips the re-pairing PRMTs.  Purely internal to a chain of our kernels:
+ * a tensor written with Y_PERM8 / OUT_PERM8 must be consumed with X_PERM8. */
+#define B200P_X_PERM8   0x100   /* x of b200p_qmm is PERM8 (4-bit weights only)                          */
+#define B200P_Y_PERM8   0x200   /* 16-bit y of b200p_qmm (STORE, SILU_MUL) is written PERM8              */
+#define B200P_OUT_PERM8 0x1     /* flags of b200p_rmsnorm / b200p_attn: write the 16-bit output PERM8 */
+
 const char* b200p_version(void);
 const char* b200p_last_error(void);
 /* 0 iff the current device is compute capability 10.x */
 int b200p_arch_check(void);
 int b200p_sm_count(void);
+/* Programmatic dependent launch for every kernel of the library (default on): kernel N+1's prologue and weight
+ * prefetch overlap kernel N's tail; each kernel executes griddepcontrol.wait before touching its inputs. */
+int b200p_set_pdl(int enabled);
 
 /* mx.dequantize(w, scales, biases, group_size, bits)            [nn.QuantizedEmbedding.__call__,
  * models/llama.py:212, models/qwen3.py:166; bit-exactness target of the north star]
@@ -89,7 +101,7 @@ int b200p_qmm_set_path(int path);
 /* mx.fast.rms_norm(x, w, eps)                                      [nn.RMSNorm: models/llama.py:187,
  * 189,231]  x float [M,H] (the fp32 residual stream) -> y `dtype` [M,H]; w `dtype` [H]. */
 int b200p_rmsnorm(const float* x, const void* w, void* y, int64_t M, int64_t H, float eps,
-                  int dtype, void* stream);
+                  int dtype, int flags, void* stream);
 
 /* per-head q/k RMSNorm (qwen3 only) + mx.fast.rope at per-row offsets + cache append
  *                      [models/qwen3.py:65-70; models/llama.py:107-117; models/base.py:119-140]
@@ -113,7 +125,7 @@ int b200p_advance_lengths(int32_t* lengths, int64_t B, int32_t delta, void* stre
  * out `dtype` [B, L, Hq*D].  workspace: float, >= b200p_attn_workspace_bytes. */
 int b200p_attn(const void* q, const void* kcache, const void* vcache, const int32_t* lengths,
                void* out, int64_t B, int64_t L, int Hq, int Hkv, int D, int64_t Tcap,
-               float scale, int dtype, void* workspace, size_t workspace_bytes, void* stream);
+               float scale, int dtype, int flags, void* workspace, size_t workspace_bytes, void* stream);
 size_t b200p_attn_workspace_bytes(int64_t B, int64_t L, int Hq, int D);
 /* 0 = auto, 1 = generic CUDA-core kernel only, 2 = tensor (mma) split-K kernel only */
 int b200p_attn_set_path(int path);

@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libb200parallm.so")
 F32, F16, BF16 = 0, 1, 2
 DQ_F32_MULADD, DQ_FMA, DQ_T_MULADD = 0, 1, 2
 EPI_STORE, EPI_STORE_F32, EPI_ADD_RESIDUAL, EPI_SILU_MUL = 0, 1, 2, 3
+X_PERM8, Y_PERM8, OUT_PERM8 = 0x100, 0x200, 0x1      # activation-layout flags (include/b200p.h)
 
 _vp, _i64, _i32, _f32, _u64, _sz = C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_uint64, C.c_size_t
 
@@ -24,17 +25,18 @@ SIGNATURES = {
     "b200p_last_error": (C.c_char_p, []),
     "b200p_arch_check": (_i32, []),
     "b200p_sm_count": (_i32, []),
+    "b200p_set_pdl": (_i32, [_i32]),
     "b200p_dequantize": (_i32, [_vp, _vp, _vp, _vp, _i64, _i64, _i32, _i32, _i32, _i32, _vp]),
     "b200p_embed": (_i32, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _i32, _vp]),
     "b200p_qmm": (_i32, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _vp, _sz, _vp]),
     "b200p_qmm_workspace_bytes": (_sz, [_i64, _i64, _i64]),
     "b200p_qmm_tensor_supported": (_i32, [_i64, _i64, _i64, _i32, _i32, _i32, _i32]),
     "b200p_qmm_set_path": (_i32, [_i32]),
-    "b200p_rmsnorm": (_i32, [_vp, _vp, _vp, _i64, _i64, _f32, _i32, _vp]),
+    "b200p_rmsnorm": (_i32, [_vp, _vp, _vp, _i64, _i64, _f32, _i32, _i32, _vp]),
     "b200p_rope_kv_append": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i32, _i32, _i32, _i64,
                                     _f32, _f32, _f32, _i32, _vp]),
     "b200p_advance_lengths": (_i32, [_vp, _i64, _i32, _vp]),
-    "b200p_attn": (_i32, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i32, _i32, _i32, _i64, _f32, _i32, _vp, _sz, _vp]),
+    "b200p_attn": (_i32, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i32, _i32, _i32, _i64, _f32, _i32, _i32, _vp, _sz, _vp]),
     "b200p_attn_workspace_bytes": (_sz, [_i64, _i64, _i32, _i32]),
     "b200p_attn_set_path": (_i32, [_i32]),
     "b200p_argmax": (_i32, [_vp, _vp, _vp, _i64, _i64, _i64, _vp]),

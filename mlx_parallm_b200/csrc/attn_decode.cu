@@ -72,7 +72,7 @@ template <typename T>
 __global__ void __launch_bounds__(AD_THREADS, 1)
 attn_decode_kernel(const T* __restrict__ q, const T* __restrict__ kc, const T* __restrict__ vc,
                    const int32_t* __restrict__ lengths, T* __restrict__ out, float* __restrict__ ws, int Hq, int Hkv,
-                   int64_t Tcap, float scale_log2e, int splits) {
+                   int64_t Tcap, float scale_log2e, int splits, int out_perm) {
   extern __shared__ __align__(128) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int split = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
@@ -238,7 +238,7 @@ attn_decode_kernel(const T* __restrict__ q, const T* __restrict__ kc, const T* _
     }
     const int hq = kvh * G + row;
     if (splits == 1) {
-      out[((int64_t)b * Hq + hq) * AD_D + d] = Tr<T>::from_f(acc / Lsum);
+      out[((int64_t)b * Hq + hq) * AD_D + (out_perm ? perm8_pos(d) : d)] = Tr<T>::from_f(acc / Lsum);
     } else {
       float* rec = ws + (((int64_t)b * Hq + hq) * splits + split) * AD_REC;
       rec[4 + d] = acc;
@@ -250,7 +250,7 @@ attn_decode_kernel(const T* __restrict__ q, const T* __restrict__ kc, const T* _
 // merge the per-split partials: grid = B * Hq, block = 128 (one thread per head dim)
 template <typename T>
 __global__ void __launch_bounds__(AD_D)
-attn_reduce_kernel(const float* __restrict__ ws, T* __restrict__ out, int splits) {
+attn_reduce_kernel(const float* __restrict__ ws, T* __restrict__ out, int splits, int out_perm) {
   pdl_wait();
   const int64_t bh = blockIdx.x;
   const int d = threadIdx.x;
@@ -265,7 +265,7 @@ attn_reduce_kernel(const float* __restrict__ ws, T* __restrict__ out, int splits
     acc += base[s * AD_REC + 4 + d] * f;
   }
   pdl_launch_dependents();
-  out[bh * AD_D + d] = Tr<T>::from_f(acc / L);
+  out[bh * AD_D + (out_perm ? perm8_pos(d) : d)] = Tr<T>::from_f(acc / L);
 }
 
 // ------------------------------------------------------------------------------------------------ host
@@ -298,7 +298,7 @@ size_t attn_decode_workspace_bytes(int64_t B, int64_t L, int Hq, int D) {
 
 template <typename T>
 static int launch_attn_decode(const void* q, const void* kc, const void* vc, const int32_t* lengths, void* out, int64_t B,
-                              int Hq, int Hkv, int64_t Tcap, float scale, void* ws, cudaStream_t st) {
+                              int Hq, int Hkv, int64_t Tcap, float scale, int out_perm, void* ws, cudaStream_t st) {
   auto kern = attn_decode_kernel<T>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -310,25 +310,25 @@ static int launch_attn_decode(const void* q, const void* kc, const void* vc, con
   const int splits = pick_splits(B, Hkv, Tcap);
   dim3 grid((unsigned)splits, (unsigned)Hkv, (unsigned)B);
   kern<<<grid, AD_THREADS, AD_SMEM, st>>>((const T*)q, (const T*)kc, (const T*)vc, lengths, (T*)out, (float*)ws, Hq, Hkv,
-                                          Tcap, scale * 1.4426950408889634f, splits);
+                                          Tcap, scale * 1.4426950408889634f, splits, out_perm);
   B200P_LAUNCH_CHECK("attn_decode_kernel");
   if (splits > 1) {
-    attn_reduce_kernel<T><<<(unsigned)(B * Hq), AD_D, 0, st>>>((const float*)ws, (T*)out, splits);
+    attn_reduce_kernel<T><<<(unsigned)(B * Hq), AD_D, 0, st>>>((const float*)ws, (T*)out, splits, out_perm);
     B200P_LAUNCH_CHECK("attn_reduce_kernel");
   }
   return B200P_OK;
 }
 
 int attn_decode_launch(const void* q, const void* kc, const void* vc, const int32_t* lengths, void* out, int64_t B,
-                       int64_t L, int Hq, int Hkv, int D, int64_t Tcap, float scale, int dtype, void* ws, size_t ws_bytes,
-                       cudaStream_t st) {
+                       int64_t L, int Hq, int Hkv, int D, int64_t Tcap, float scale, int dtype, int out_perm, void* ws,
+                       size_t ws_bytes, cudaStream_t st) {
   B200P_REQUIRE(attn_decode_supported(L, Hq, Hkv, D, dtype), B200P_ERR_ARG, "tensor decode attention: unsupported shape");
   B200P_REQUIRE(B < 65536 && Hkv < 65536, B200P_ERR_ARG, "grid too large");
   B200P_REQUIRE(ws && ws_bytes >= attn_decode_workspace_bytes(B, L, Hq, D) && aligned(ws, 16), B200P_ERR_ARG,
                 "attention workspace too small");
   B200P_REQUIRE(aligned(q, 16) && aligned(kc, 16) && aligned(vc, 16), B200P_ERR_ALIGN, "q / caches must be 16-byte aligned");
-  if (dtype == B200P_F16) return launch_attn_decode<__half>(q, kc, vc, lengths, out, B, Hq, Hkv, Tcap, scale, ws, st);
-  return launch_attn_decode<__nv_bfloat16>(q, kc, vc, lengths, out, B, Hq, Hkv, Tcap, scale, ws, st);
+  if (dtype == B200P_F16) return launch_attn_decode<__half>(q, kc, vc, lengths, out, B, Hq, Hkv, Tcap, scale, out_perm, ws, st);
+  return launch_attn_decode<__nv_bfloat16>(q, kc, vc, lengths, out, B, Hq, Hkv, Tcap, scale, out_perm, ws, st);
 }
 
 }  // namespace b200p

@@ -24,7 +24,7 @@ template <typename T, int EPL>
 __global__ void __launch_bounds__(128)
 attn_generic_kernel(const T* __restrict__ q, const T* __restrict__ kc, const T* __restrict__ vc,
                     const int32_t* __restrict__ lengths, T* __restrict__ out, int L, int Hq, int Hkv, int D,
-                    int64_t Tcap, float scale) {
+                    int64_t Tcap, float scale, int out_perm) {
   __shared__ float sh_m[4], sh_l[4];
   __shared__ float sh_acc[4][32 * EPL];
   pdl_wait();
@@ -80,17 +80,18 @@ attn_generic_kernel(const T* __restrict__ q, const T* __restrict__ kc, const T* 
       for (int j = 0; j < EPL; ++j) o[j] += sh_acc[w][d0 + j] * f;
     }
     if (act) {
-      T* dst = out + ((int64_t)tok * Hq + h) * D + d0;
+      T* dst = out + ((int64_t)tok * Hq + h) * D;
       float inv = 1.0f / lt;
 #pragma unroll
-      for (int j = 0; j < EPL; ++j) dst[j] = Tr<T>::from_f(o[j] * inv);
+      for (int j = 0; j < EPL; ++j) dst[out_perm ? perm8_pos(d0 + j) : d0 + j] = Tr<T>::from_f(o[j] * inv);
     }
   }
 }
 
 int attn_generic_launch(const void* q, const void* kc, const void* vc, const int32_t* lengths, void* out,
                         int64_t B, int64_t L, int Hq, int Hkv, int D, int64_t Tcap, float scale, int dtype,
-                        cudaStream_t st) {
+                        int out_perm, cudaStream_t st) {
+  B200P_REQUIRE(!out_perm || D % 8 == 0, B200P_ERR_ARG, "B200P_OUT_PERM8 needs head_dim %% 8 == 0");
   B200P_REQUIRE(D >= 1 && D <= 256, B200P_ERR_ARG, "generic attention supports head_dim <= 256, got %d", D);
   int epl = (D + 31) / 32;
   if (epl == 3) epl = 4;
@@ -102,7 +103,7 @@ int attn_generic_launch(const void* q, const void* kc, const void* vc, const int
 #define GO(E_)                                                                                              \
   B200P_DISPATCH_DTYPE(dtype, T, (attn_generic_kernel<T, E_><<<(unsigned)nblk, 128, 0, st>>>(                \
                                      (const T*)q, (const T*)kc, (const T*)vc, lengths, (T*)out, (int)L, Hq, \
-                                     Hkv, D, Tcap, scale)))
+                                     Hkv, D, Tcap, scale, out_perm)))
   switch (epl) {
     case 1: GO(1); break;
     case 2: GO(2); break;

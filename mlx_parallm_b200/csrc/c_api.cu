@@ -21,23 +21,24 @@ int cuda_fail(cudaError_t e, const char* what) {
 
 // implemented in the kernel translation units
 int qmv_launch(const void* x, const uint32_t* w, const void* s, const void* b, void* y, int64_t M, int64_t N,
-               int64_t K, int64_t ldx, int64_t ldy, int gs, int bits, int dtype, int epi, cudaStream_t st);
+               int64_t K, int64_t ldx, int64_t ldy, int gs, int bits, int dtype, int epi, int flags, cudaStream_t st);
 bool qmm_tc_supported(int64_t M, int64_t N, int64_t K, int gs, int bits, int dtype, int epi);
 int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b, void* y, int64_t M, int64_t N,
-                  int64_t K, int64_t ldx, int64_t ldy, int bits, int dtype, int epi, void* ws, size_t ws_bytes,
+                  int64_t K, int64_t ldx, int64_t ldy, int bits, int dtype, int epi, int flags, void* ws, size_t ws_bytes,
                   cudaStream_t st);
 size_t qmm_tc_workspace_bytes(int64_t M, int64_t N, int64_t K);
 int attn_generic_launch(const void* q, const void* kc, const void* vc, const int32_t* lengths, void* out,
                         int64_t B, int64_t L, int Hq, int Hkv, int D, int64_t Tcap, float scale, int dtype,
-                        cudaStream_t st);
+                        int out_perm, cudaStream_t st);
 bool attn_decode_supported(int64_t L, int Hq, int Hkv, int D, int dtype);
 int attn_decode_launch(const void* q, const void* kc, const void* vc, const int32_t* lengths, void* out,
                        int64_t B, int64_t L, int Hq, int Hkv, int D, int64_t Tcap, float scale, int dtype,
-                       void* ws, size_t ws_bytes, cudaStream_t st);
+                       int out_perm, void* ws, size_t ws_bytes, cudaStream_t st);
 size_t attn_decode_workspace_bytes(int64_t B, int64_t L, int Hq, int D);
 
 static int g_qmm_path = 0;   // 0 auto, 1 gemv, 2 tensor
 static int g_attn_path = 0;  // 0 auto, 1 generic, 2 tensor
+static int g_pdl = 1;
 static int g_sm_count = -1;
 static int g_cc_major = -1;
 
@@ -53,6 +54,8 @@ static int query_device() {
   g_sm_count = p.multiProcessorCount;
   return B200P_OK;
 }
+
+bool pdl_enabled() { return g_pdl != 0; }
 
 int sm_count() {
   query_device();
@@ -79,6 +82,11 @@ extern "C" int b200p_sm_count(void) {
   return g_sm_count;
 }
 
+extern "C" int b200p_set_pdl(int enabled) {
+  g_pdl = enabled ? 1 : 0;
+  return B200P_OK;
+}
+
 extern "C" int b200p_qmm_set_path(int path) {
   B200P_REQUIRE(path >= 0 && path <= 2, B200P_ERR_ARG, "path must be 0..2");
   g_qmm_path = path;
@@ -102,7 +110,13 @@ extern "C" int b200p_qmm_tensor_supported(int64_t M, int64_t N, int64_t K, int g
 
 extern "C" int b200p_qmm(const void* x, const uint32_t* w, const void* scales, const void* biases, void* y,
                          int64_t M, int64_t N, int64_t K, int64_t ldx, int64_t ldy, int group_size, int bits,
-                         int dtype, int epilogue, void* workspace, size_t workspace_bytes, void* stream) {
+                         int dtype, int epilogue_flags, void* workspace, size_t workspace_bytes, void* stream) {
+  const int epilogue = epilogue_flags & 0xff, flags = epilogue_flags & ~0xff;
+  B200P_REQUIRE((flags & ~(B200P_X_PERM8 | B200P_Y_PERM8)) == 0, B200P_ERR_ARG, "unknown layout flags 0x%x", flags);
+  B200P_REQUIRE(!(flags & B200P_X_PERM8) || (bits == 4 && dtype != B200P_F32), B200P_ERR_ARG,
+                "B200P_X_PERM8 is the layout of 16-bit activations for 4-bit weights");
+  B200P_REQUIRE(!(flags & B200P_Y_PERM8) || ((epilogue == B200P_EPI_STORE || epilogue == B200P_EPI_SILU_MUL) && dtype != B200P_F32),
+                B200P_ERR_ARG, "B200P_Y_PERM8 applies to 16-bit outputs (STORE, SILU_MUL)");
   B200P_REQUIRE(x && w && scales && biases && y, B200P_ERR_ARG, "null pointer");
   B200P_REQUIRE(bits == 4 || bits == 8, B200P_ERR_ARG, "bits must be 4 or 8, got %d", bits);
   B200P_REQUIRE(M >= 0 && N > 0 && K > 0 && N % 2 == 0, B200P_ERR_ARG, "bad shape M=%lld N=%lld K=%lld (N must be even)",
@@ -126,10 +140,10 @@ extern "C" int b200p_qmm(const void* x, const uint32_t* w, const void* scales, c
   if (tc_ok && g_qmm_path != 1) {
     B200P_REQUIRE(workspace && workspace_bytes >= qmm_tc_workspace_bytes(M, N, K), B200P_ERR_ARG,
                   "tensor path needs a workspace of %zu bytes", qmm_tc_workspace_bytes(M, N, K));
-    return qmm_tc_launch(x, w, scales, biases, y, M, N, K, ldx, ldy, bits, dtype, epilogue, workspace,
+    return qmm_tc_launch(x, w, scales, biases, y, M, N, K, ldx, ldy, bits, dtype, epilogue, flags, workspace,
                          workspace_bytes, st);
   }
-  return qmv_launch(x, w, scales, biases, y, M, N, K, ldx, ldy, group_size, bits, dtype, epilogue, st);
+  return qmv_launch(x, w, scales, biases, y, M, N, K, ldx, ldy, group_size, bits, dtype, epilogue, flags, st);
 }
 
 extern "C" size_t b200p_attn_workspace_bytes(int64_t B, int64_t L, int Hq, int D) {
@@ -138,8 +152,11 @@ extern "C" size_t b200p_attn_workspace_bytes(int64_t B, int64_t L, int Hq, int D
 
 extern "C" int b200p_attn(const void* q, const void* kcache, const void* vcache, const int32_t* lengths, void* out,
                           int64_t B, int64_t L, int Hq, int Hkv, int D, int64_t Tcap, float scale, int dtype,
-                          void* workspace, size_t workspace_bytes, void* stream) {
+                          int flags, void* workspace, size_t workspace_bytes, void* stream) {
   B200P_REQUIRE(q && kcache && vcache && lengths && out, B200P_ERR_ARG, "null pointer");
+  B200P_REQUIRE((flags & ~B200P_OUT_PERM8) == 0, B200P_ERR_ARG, "unknown flags 0x%x", flags);
+  const int out_perm = (flags & B200P_OUT_PERM8) ? 1 : 0;
+  B200P_REQUIRE(!out_perm || dtype != B200P_F32, B200P_ERR_ARG, "B200P_OUT_PERM8 is a 16-bit layout");
   B200P_REQUIRE(Hq > 0 && Hkv > 0 && Hq % Hkv == 0, B200P_ERR_ARG, "bad head counts %d/%d", Hq, Hkv);
   B200P_REQUIRE(B >= 0 && L >= 0 && Tcap > 0, B200P_ERR_ARG, "bad shape");
   B200P_REQUIRE(dtype >= 0 && dtype <= 2, B200P_ERR_ARG, "bad dtype %d", dtype);
@@ -150,8 +167,8 @@ extern "C" int b200p_attn(const void* q, const void* kcache, const void* vcache,
   if (tc_ok && g_attn_path != 1) {
     B200P_REQUIRE(workspace && workspace_bytes >= attn_decode_workspace_bytes(B, L, Hq, D), B200P_ERR_ARG,
                   "attention needs a workspace of %zu bytes", attn_decode_workspace_bytes(B, L, Hq, D));
-    return attn_decode_launch(q, kcache, vcache, lengths, out, B, L, Hq, Hkv, D, Tcap, scale, dtype, workspace,
+    return attn_decode_launch(q, kcache, vcache, lengths, out, B, L, Hq, Hkv, D, Tcap, scale, dtype, out_perm, workspace,
                               workspace_bytes, st);
   }
-  return attn_generic_launch(q, kcache, vcache, lengths, out, B, L, Hq, Hkv, D, Tcap, scale, dtype, st);
+  return attn_generic_launch(q, kcache, vcache, lengths, out, B, L, Hq, Hkv, D, Tcap, scale, dtype, out_perm, st);
 }

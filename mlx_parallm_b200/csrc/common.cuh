@@ -81,6 +81,9 @@ __device__ __forceinline__ float u8_to_float(uint32_t q) {
   return __uint_as_float(0x4B000000u | q) - 8388608.0f;
 }
 
+// PERM8 activation layout (include/b200p.h): position of element n inside its aligned group of 8 ([0,4,1,5,2,6,3,7])
+__host__ __device__ __forceinline__ int perm8_pos(int n) { return (n & ~7) | (((n & 3) << 1) | ((n >> 2) & 1)); }
+
 // Programmatic dependent launch: wait for the producer grid's memory to be visible / allow the
 // consumer grid to start its prologue.  No-ops when the launch carries no PDL attribute.
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }

@@ -146,7 +146,7 @@ __device__ __forceinline__ float block_sum(float v, float* sh) {
 
 template <typename T>
 __global__ void __launch_bounds__(256)
-rmsnorm_kernel(const float* __restrict__ x, const T* __restrict__ w, T* __restrict__ y, int64_t H, float eps) {
+rmsnorm_kernel(const float* __restrict__ x, const T* __restrict__ w, T* __restrict__ y, int64_t H, float eps, int perm) {
   __shared__ float sh[33];
   pdl_wait();
   const float* xr = x + (int64_t)blockIdx.x * H;
@@ -161,6 +161,26 @@ rmsnorm_kernel(const float* __restrict__ x, const T* __restrict__ w, T* __restri
   ss = block_sum(ss, sh);
   float inv = 1.0f / sqrtf(ss / (float)H + eps);
   pdl_launch_dependents();
+  if (perm) {   // 16-bit output in the PERM8 order: one thread per aligned group of 8 (H % 8 == 0 checked by the host)
+    if constexpr (sizeof(T) == 2) {
+      for (int64_t i = threadIdx.x; i < H / 8; i += blockDim.x) {
+        const float4 a = reinterpret_cast<const float4*>(xr)[2 * i], b = reinterpret_cast<const float4*>(xr)[2 * i + 1];
+        const uint4 wv = reinterpret_cast<const uint4*>(w)[i];
+        const T* wp = reinterpret_cast<const T*>(&wv);
+        __align__(16) T o[8];
+        o[0] = Tr<T>::from_f(a.x * inv * Tr<T>::to_f(wp[0]));
+        o[2] = Tr<T>::from_f(a.y * inv * Tr<T>::to_f(wp[1]));
+        o[4] = Tr<T>::from_f(a.z * inv * Tr<T>::to_f(wp[2]));
+        o[6] = Tr<T>::from_f(a.w * inv * Tr<T>::to_f(wp[3]));
+        o[1] = Tr<T>::from_f(b.x * inv * Tr<T>::to_f(wp[4]));
+        o[3] = Tr<T>::from_f(b.y * inv * Tr<T>::to_f(wp[5]));
+        o[5] = Tr<T>::from_f(b.z * inv * Tr<T>::to_f(wp[6]));
+        o[7] = Tr<T>::from_f(b.w * inv * Tr<T>::to_f(wp[7]));
+        reinterpret_cast<uint4*>(yr)[i] = *reinterpret_cast<uint4*>(o);
+      }
+    }
+    return;
+  }
   for (int64_t i = threadIdx.x; i < H4; i += blockDim.x) {
     float4 v = reinterpret_cast<const float4*>(xr)[i];
     __align__(16) T o[4];
@@ -178,13 +198,17 @@ rmsnorm_kernel(const float* __restrict__ x, const T* __restrict__ w, T* __restri
 }  // namespace b200p
 
 extern "C" int b200p_rmsnorm(const float* x, const void* w, void* y, int64_t M, int64_t H, float eps,
-                             int dtype, void* stream) {
+                             int dtype, int flags, void* stream) {
   B200P_REQUIRE(x && w && y, B200P_ERR_ARG, "null pointer");
+  B200P_REQUIRE((flags & ~B200P_OUT_PERM8) == 0, B200P_ERR_ARG, "unknown flags 0x%x", flags);
+  const int perm = (flags & B200P_OUT_PERM8) ? 1 : 0;
+  B200P_REQUIRE(!perm || (dtype != B200P_F32 && H % 8 == 0 && aligned(w, 16)), B200P_ERR_ARG,
+                "B200P_OUT_PERM8 needs a 16-bit dtype, H %% 8 == 0 and a 16-byte aligned weight");
   B200P_REQUIRE(aligned(x, 16) && aligned(y, 16) && H % 4 == 0, B200P_ERR_ALIGN,
                 "rmsnorm needs 16-byte aligned rows (H %% 4 == 0)");
   if (M == 0) return B200P_OK;
   B200P_DISPATCH_DTYPE(dtype, T, (rmsnorm_kernel<T><<<(unsigned)M, 256, 0, (cudaStream_t)stream>>>(
-                                     x, (const T*)w, (T*)y, H, eps)));
+                                     x, (const T*)w, (T*)y, H, eps, perm)));
   B200P_LAUNCH_CHECK("rmsnorm_kernel");
   return B200P_OK;
 }

@@ -6,7 +6,8 @@
 //   A  = dequantised weights [128 x 64] 16-bit, written by the dequant warps STRAIGHT INTO TMEM with tcgen05.st
 //        (row m in lane m, k packed two per 32-bit column) -- no shared-memory round trip, no proxy fence;
 //   B  = X tile [TN x 64] 16-bit, TMA-loaded into shared memory with SWIZZLE_128B (K-major);
-//   D  = [128 x TN] fp32 in TMEM.
+//   D  = [128 x TN] fp32 in TMEM, double-buffered when TN <= 64 so the epilogue of one segment overlaps the
+//        main loop of the next.
 // A CTA owns a PAIR of 128-row weight blocks per output tile (they share the X tile; for SILU_MUL the pair is
 // gate block p / up block p).
 //
@@ -17,15 +18,24 @@
 // ADD_RESIDUAL, else into a per-boundary fp32 accumulator that the last-arriving CTA reads, applies the epilogue
 // to and re-zeroes.  Split tiles are therefore summed in arrival order (last-bit run-to-run differences).
 //
-// warp roles (576 threads): warps 0..15 = dequantisers (4 groups of 4 warps: group g handles block g&1 on
-// k-blocks of parity g>>1; a thread owns one weight row) and, at the end of each segment, the epilogue
-// (TMEM -> registers -> global, lanes along n so stores are coalesced); warp 16 = TMA producer; warp 17 = TMEM
-// owner + MMA issuer.  Both issue from a converged warp under elect.sync so the tcgen05 / TMA operands live in
-// uniform registers (under `lane == 0` ptxas wraps every UTCHMMA in a ~70-cycle uniformisation loop).
+// warp roles (704 threads):
+//   warps 0..15  dequantisers: 4 groups of 4 warps, group g handles weight block g&1 on k-blocks of parity g>>1;
+//                a thread owns one weight row: LDS packed codes -> 16-bit q*s+b -> tcgen05.st into the A ring;
+//   warps 16..19 epilogue: TMEM -> registers -> global (lanes along n: coalesced), stream-K fix-up;
+//   warp 20      TMA producer (weights, X tiles, scale/bias tiles);
+//   warp 21      TMEM owner + MMA issuer (elect.sync, operands in uniform registers).
 //
 // rings:  IN  (packed weights 2 x [128 rows x 128 B] + KPS X tiles [TN x 64]) in shared memory, SWIZZLE_128B,
-//             filled by TMA, freed by MMA completion (tcgen05.commit);
-//         A   (4 or 6 slots x 2 blocks x 32 TMEM columns), filled by the dequantisers, freed by MMA completion.
+//             filled by TMA (separate "weights landed" / "X landed" barriers), freed by MMA completion;
+//         SB  (scales + biases of 8 k-blocks for both blocks, [128 rows x 16 B] tiles) filled by TMA when the
+//             rows of the scale matrix are 16-byte multiples (K % 512 == 0), else the dequantisers read them
+//             from global memory; freed by the dequant warps as soon as the values are in registers;
+//         A   (4 slots x 2 blocks x 32 TMEM columns), filled by the dequantisers, freed by MMA completion.
+//
+// X layout: B200P_X_PERM8 says the 16-bit activations arrive with every aligned group of 8 k permuted to
+// [0,4,1,5,2,6,3,7] -- the order in which a 4-bit word's nibbles fall out of two masks as packed pairs -- which
+// removes the four PRMT per word from the dequant loop (the ALU pipe is the scarce resource there).  Our own
+// producer kernels (rmsnorm, attention, the SILU_MUL epilogue) write that layout on request.
 //
 // Algorithmic HBM bytes per launch: N*K*bits/8 + 2*N*(K/64)*2 (weights, scales, biases) -- X, Y and the
 // stream-K partials are L2 traffic.
@@ -39,6 +49,7 @@
 namespace b200p {
 
 int sm_count();
+bool pdl_enabled();
 
 // ------------------------------------------------------------------------------------------------ PTX
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -187,7 +198,9 @@ template <> struct H2<__nv_bfloat16> {
 
 // 8 consecutive codes (one word at 4 bits, two words at 8 bits) -> 8 dequantised 16-bit values, k order,
 // as four packed pairs (the layout of four consecutive TMEM columns of an A row).
-template <typename T, int BITS>
+// With XPERM (4 bits) the pairs are emitted as they fall out of the masks -- k order [0,4,1,5,2,6,3,7] -- and the
+// activations carry the same permutation (B200P_X_PERM8).
+template <typename T, int BITS, bool XPERM>
 __device__ __forceinline__ void dequant8(const uint32_t* pw, uint32_t s2, uint32_t b2, uint32_t* out) {
   typedef H2<T> H;
   if constexpr (BITS == 4) {
@@ -205,10 +218,14 @@ __device__ __forceinline__ void dequant8(const uint32_t* pw, uint32_t s2, uint32
       a26 = H::fma(H::q_lo(lop3_and_or(w >> 8, 0x000f000fu, H::MAGIC)), s2, b2);
       a37 = H::fma(H::q_lo(lop3_and_or(w >> 12, 0x000f000fu, H::MAGIC)), s2, b2);
     }
-    out[0] = prmt(a04, a15, 0x5410u);   // k0 k1
-    out[1] = prmt(a26, a37, 0x5410u);   // k2 k3
-    out[2] = prmt(a04, a15, 0x7632u);   // k4 k5
-    out[3] = prmt(a26, a37, 0x7632u);   // k6 k7
+    if constexpr (XPERM) {
+      out[0] = a04; out[1] = a15; out[2] = a26; out[3] = a37;
+    } else {
+      out[0] = prmt(a04, a15, 0x5410u);   // k0 k1
+      out[1] = prmt(a26, a37, 0x5410u);   // k2 k3
+      out[2] = prmt(a04, a15, 0x7632u);   // k4 k5
+      out[3] = prmt(a26, a37, 0x7632u);   // k6 k7
+    }
   } else {
     out[0] = H::fma(H::q_lo(prmt(pw[0], H::MAGIC_BYTES, 0x4140u)), s2, b2);
     out[1] = H::fma(H::q_lo(prmt(pw[0], H::MAGIC_BYTES, 0x4342u)), s2, b2);
@@ -227,10 +244,20 @@ __device__ __forceinline__ float silu_tc(float g) { return g / (1.0f + __expf(-g
 // ------------------------------------------------------------------------------------------------ kernel
 constexpr int DQ_WARPS = 16;
 constexpr int DQ_THREADS = DQ_WARPS * 32;
-constexpr int TC_THREADS = 64 + DQ_THREADS;     // + TMA warp + MMA warp
+constexpr int EPI_WARPS = 4;
+constexpr int EPI_THREADS = EPI_WARPS * 32;
+constexpr int WARP_TMA = DQ_WARPS + EPI_WARPS;
+constexpr int WARP_MMA = WARP_TMA + 1;
+constexpr int TC_THREADS = (WARP_MMA + 1) * 32;
 constexpr int TMEM_COLS = 512;
 constexpr int MAX_TN = 128;
 constexpr int W_TILE_BYTES = 128 * 128;          // one weight block of one stage: 128 rows x 128 packed bytes
+constexpr int NSLOT = 4;                         // A ring slots (each: 2 blocks x 32 TMEM columns)
+constexpr uint32_t A_COL0 = 256;                 // TMEM columns [0,256) hold D, [256,512) the A ring
+constexpr int NSB = 2;                           // scale/bias ring slots
+constexpr int SB_TILE_BYTES = 128 * 16;          // 128 rows x 8 k-blocks x 2 bytes
+constexpr int SB_SLOT_BYTES = 4 * SB_TILE_BYTES; // block 0 scales, block 0 biases, block 1 scales, block 1 biases
+constexpr int MAX_STAGES = 8;
 
 struct TcParams {
   const void* scales;
@@ -241,42 +268,46 @@ struct TcParams {
   int M_tok, N, K, TN;
   int64_t ldy;
   int epi;
+  int y_perm;          // 1: 16-bit outputs (STORE / SILU_MUL) are written in the PERM8 column order
   int num_kb;          // K / 64
   int num_st;          // stages along K = ceil(num_kb / KPS)
   int pairs, tiles_m;  // output tile t = pair * tiles_m + token tile
   long long U;         // total units = pairs * tiles_m * num_st
-  int vec_sb;          // 1: scales/biases rows allow aligned 128-bit loads (num_kb % 8 == 0)
+  int sb_tma;          // 1: scale/bias tiles come through TMA (num_kb % 8 == 0)
   int in_stages;
   int in_stage_bytes;
-  int debug;           // profiling only: 2 skip MMA issue, 4 skip epilogue + fix-up, 8 skip the TMEM store of A, 16 skip LDS + dequant math
 };
 
 // CTA that owns linear unit x when U units are dealt to G CTAs as [c*U/G, (c+1)*U/G)
 __device__ __forceinline__ int owner_of(long long x, long long U, int G) { return (int)(((x + 1) * G - 1) / U); }
 
-template <typename T, int BITS>
+template <typename T, int BITS, bool XPERM>
 __global__ void __launch_bounds__(TC_THREADS, 1)
-qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x, const TcParams p) {
+qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x,
+              const __grid_constant__ CUtensorMap tm_s, const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
   constexpr int PKB = 64 * BITS / 8;            // packed bytes per row per k-block
   constexpr int KPS = 128 / PKB;                // k-blocks per stage (a stage row is one 128-byte line)
-  constexpr int LKPS = (KPS == 4) ? 2 : 1;
+  constexpr int SPG = 8 / KPS;                  // stages per scale/bias group of 8 k-blocks
   constexpr int W_STAGE_BYTES = 2 * W_TILE_BYTES;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t in_ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t bar_base = in_ring + p.in_stages * p.in_stage_bytes;
   const int S = p.in_stages;
+  const uint32_t sb_ring = in_ring + S * p.in_stage_bytes;
+  const uint32_t bar_base = sb_ring + NSB * SB_SLOT_BYTES;
   const int TN = p.TN;
-  // TMEM columns: D block b at b*TN; A ring behind it: slot s, block b at a_col0 + s*64 + b*32
-  const int NSLOT = TN > 64 ? 4 : 6;
-  const uint32_t a_col0 = TN > 64 ? 256u : 128u;
-  auto full_in = [&](int s) { return bar_base + 8u * s; };
-  auto empty_in = [&](int s) { return bar_base + 8u * (S + s); };
-  auto full_a = [&](int s) { return bar_base + 8u * (2 * S + s); };
-  auto empty_a = [&](int s) { return bar_base + 8u * (2 * S + 8 + s); };
-  const uint32_t accum_full = bar_base + 8u * (2 * S + 16);
-  const uint32_t accum_empty = accum_full + 8u;
-  const uint32_t tmem_slot = accum_empty + 8u;
+  const int NBUF = TN > 64 ? 1 : 2;              // D buffers: buffer d, block b at columns d*128 + b*64 (TN <= 64) / b*128
+  auto full_w = [&](int s) { return bar_base + 8u * s; };
+  auto full_x = [&](int s) { return bar_base + 8u * (MAX_STAGES + s); };
+  auto empty_in = [&](int s) { return bar_base + 8u * (2 * MAX_STAGES + s); };
+  auto full_a = [&](int s) { return bar_base + 8u * (3 * MAX_STAGES + s); };
+  auto empty_a = [&](int s) { return bar_base + 8u * (3 * MAX_STAGES + NSLOT + s); };
+  auto sb_full = [&](int s) { return bar_base + 8u * (3 * MAX_STAGES + 2 * NSLOT + s); };
+  auto sb_empty = [&](int s) { return bar_base + 8u * (3 * MAX_STAGES + 2 * NSLOT + NSB + s); };
+  auto accum_full = [&](int d) { return bar_base + 8u * (3 * MAX_STAGES + 2 * NSLOT + 2 * NSB + d); };
+  auto accum_empty = [&](int d) { return bar_base + 8u * (3 * MAX_STAGES + 2 * NSLOT + 2 * NSB + 2 + d); };
+  const uint32_t tmem_slot = bar_base + 8u * (3 * MAX_STAGES + 2 * NSLOT + 2 * NSB + 4);
   const uint32_t flag_slot = tmem_slot + 4u;
+  auto d_col = [&](int d, int b) { return (uint32_t)(TN > 64 ? b * 128 : d * 128 + b * 64); };
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int G = (int)gridDim.x, cta = (int)blockIdx.x;
@@ -284,111 +315,242 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
   const bool silu = p.epi == B200P_EPI_SILU_MUL;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < S; ++s) { mbar_init(full_in(s), 1); mbar_init(empty_in(s), 1); }
+    for (int s = 0; s < S; ++s) { mbar_init(full_w(s), 1); mbar_init(full_x(s), 1); mbar_init(empty_in(s), 1); }
     for (int s = 0; s < NSLOT; ++s) { mbar_init(full_a(s), 8); mbar_init(empty_a(s), 1); }
-    mbar_init(accum_full, 1);
-    mbar_init(accum_empty, DQ_WARPS);
+    for (int s = 0; s < NSB; ++s) { mbar_init(sb_full(s), 1); mbar_init(sb_empty(s), DQ_WARPS); }
+    for (int d = 0; d < 2; ++d) { mbar_init(accum_full(d), 1); mbar_init(accum_empty(d), EPI_WARPS); }
     fence_barrier_init();
     tma_prefetch_desc(&tm_w);
     tma_prefetch_desc(&tm_x);
+    if (p.sb_tma) { tma_prefetch_desc(&tm_s); tma_prefetch_desc(&tm_b); }
   }
-  if (warp == DQ_WARPS + 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  if (warp == WARP_MMA) tmem_alloc(tmem_slot, TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
-  pdl_wait();   // X (and the residual) come from the previous kernel
-
-  if (warp == DQ_WARPS) {
+  if (warp == WARP_TMA) {
     // ===================================== TMA producer =====================================
+    // Weights and scale/bias tiles do not depend on the previous kernel: the first stages' worth is requested
+    // BEFORE griddepcontrol.wait, so under programmatic dependent launch the HBM stream of this kernel starts while
+    // the previous kernel drains.  X (and the residual the epilogue adds to) is only touched after the wait.
+    const uint32_t tx_w = (uint32_t)W_STAGE_BYTES, tx_x = (uint32_t)(KPS * TN * 128);
+    int si = 0, ph = 0, sbi = 0, sbph = 0;
+    // pre-wait pass: at most S stages and at most NSB scale/bias groups (nothing to wait for on fresh barriers)
+    long long u_pre = u_begin;
     {
-      const uint32_t tx = (uint32_t)(W_STAGE_BYTES + KPS * TN * 128);
-      int si = 0, ph = 0;
-      for (long long u = u_begin; u < u_end;) {
-        const int tile = (int)(u / p.num_st), s0 = (int)(u % p.num_st);
-        const int ns = (int)min((long long)(p.num_st - s0), u_end - u);
+      int groups = 0;
+      for (long long u = u_begin; u < u_end && (u - u_begin) < S; ++u) {
+        const int st = (int)(u % p.num_st);
+        const bool gstart = (u == u_begin) || st == 0 || (st % SPG) == 0;
+        if (p.sb_tma && gstart && groups == NSB) break;
+        if (gstart) ++groups;
+        u_pre = u + 1;
+      }
+    }
+    for (int pass = 0; pass < 2; ++pass) {
+      // pass 0: weights (+ scale/bias tiles) of units [u_begin, u_pre); then wait for the previous grid;
+      // pass 1: X tiles of those units, then everything of the remaining units
+      si = 0; ph = 0;
+      int sbi_l = pass == 0 ? 0 : sbi, sbph_l = pass == 0 ? 0 : sbph;
+      const long long u_stop = pass == 0 ? u_pre : u_end;
+      for (long long u = u_begin; u < u_stop; ++u) {
+        const int tile = (int)(u / p.num_st), st = (int)(u % p.num_st);
         const int pair = tile / p.tiles_m, tm = tile % p.tiles_m;
         const int rowA0 = silu ? pair * 128 : pair * 256;
         const int rowB0 = silu ? p.N / 2 + pair * 128 : pair * 256 + 128;
-        for (int st = s0; st < s0 + ns; ++st) {
-          mbar_wait(empty_in(si), ph ^ 1);
-          const uint32_t dst = in_ring + si * p.in_stage_bytes;
+        const bool early = u < u_pre;                       // weights of this unit were issued in pass 0
+        const bool do_w = pass == 0 || !early, do_x = pass == 1;
+        const bool gstart = (u == u_begin) || st == 0 || (st % SPG) == 0;
+        const uint32_t dst = in_ring + si * p.in_stage_bytes;
+        if (do_w && !early) mbar_wait(empty_in(si), ph ^ 1);
+        if (do_w && p.sb_tma && gstart) {
+          if (!early) mbar_wait(sb_empty(sbi_l), sbph_l ^ 1);
           if (elect_one()) {
-            mbar_arrive_expect_tx(full_in(si), tx);
-            tma_load_2d(dst, &tm_w, st * 128, rowA0, full_in(si));
-            tma_load_2d(dst + W_TILE_BYTES, &tm_w, st * 128, rowB0, full_in(si));
-#pragma unroll
-            for (int jj = 0; jj < KPS; ++jj)
-              tma_load_2d(dst + W_STAGE_BYTES + jj * TN * 128, &tm_x, (st * KPS + jj) * 64, tm * TN, full_in(si));
+            const uint32_t sdst = sb_ring + sbi_l * SB_SLOT_BYTES;
+            const int kb0 = (st / SPG) * 8;
+            mbar_arrive_expect_tx(sb_full(sbi_l), (uint32_t)SB_SLOT_BYTES);
+            tma_load_2d(sdst, &tm_s, kb0, rowA0, sb_full(sbi_l));
+            tma_load_2d(sdst + SB_TILE_BYTES, &tm_b, kb0, rowA0, sb_full(sbi_l));
+            tma_load_2d(sdst + 2 * SB_TILE_BYTES, &tm_s, kb0, rowB0, sb_full(sbi_l));
+            tma_load_2d(sdst + 3 * SB_TILE_BYTES, &tm_b, kb0, rowB0, sb_full(sbi_l));
           }
           __syncwarp();
-          if (++si == S) { si = 0; ph ^= 1; }
+          if (++sbi_l == NSB) { sbi_l = 0; sbph_l ^= 1; }
         }
-        u += ns;
+        if (elect_one()) {
+          if (do_w) {
+            mbar_arrive_expect_tx(full_w(si), tx_w);
+            tma_load_2d(dst, &tm_w, st * 128, rowA0, full_w(si));
+            tma_load_2d(dst + W_TILE_BYTES, &tm_w, st * 128, rowB0, full_w(si));
+          }
+          if (do_x) {
+            mbar_arrive_expect_tx(full_x(si), tx_x);
+#pragma unroll
+            for (int jj = 0; jj < KPS; ++jj)
+              tma_load_2d(dst + W_STAGE_BYTES + jj * TN * 128, &tm_x, (st * KPS + jj) * 64, tm * TN, full_x(si));
+          }
+        }
+        __syncwarp();
+        if (++si == S) { si = 0; ph ^= 1; }
+      }
+      if (pass == 0) {
+        sbi = sbi_l; sbph = sbph_l;
+        pdl_wait();
       }
     }
-  } else if (warp == DQ_WARPS + 1) {
+  } else if (warp == WARP_MMA) {
     // ===================================== MMA issuer =======================================
     // instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32 (1<<4), a/b format (0 f16, 1 bf16) at
     // bits 7/10, K-major A and B, N>>3 at bit 17, M>>4 at bit 24
     const uint32_t fmt = std::is_same<T, __nv_bfloat16>::value ? 1u : 0u;
     const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(TN >> 3) << 17) | ((128u >> 4) << 24);
-    int si = 0, ph = 0, slot = 0, pha = 0, seg = 0;
+    int si = 0, ph = 0, seg = 0;
+    uint32_t it = 0;
     for (long long u = u_begin; u < u_end; ++seg) {
       const int s0 = (int)(u % p.num_st);
       const int ns = (int)min((long long)(p.num_st - s0), u_end - u);
-      if (seg > 0) {                                  // the epilogue of the previous segment has drained D
-        mbar_wait(accum_empty, (uint32_t)((seg - 1) & 1));
+      const int buf = NBUF == 2 ? (seg & 1) : 0;
+      if (seg >= NBUF) {                               // the epilogue of the segment that last used this D buffer has drained it
+        mbar_wait(accum_empty(buf), (uint32_t)(((seg / NBUF) - 1) & 1));
         tc_fence_after();
       }
+      const uint32_t d0 = tmem_base + d_col(buf, 0), d1 = tmem_base + d_col(buf, 1);
       for (int j = 0; j < ns; ++j) {
-        mbar_wait(full_in(si), (uint32_t)ph);
+        mbar_wait(full_x(si), (uint32_t)ph);
         const uint32_t xs = in_ring + si * p.in_stage_bytes + W_STAGE_BYTES;
-        for (int jj = 0; jj < KPS; ++jj) {
-          mbar_wait(full_a(slot), (uint32_t)pha);
+#pragma unroll
+        for (int jj = 0; jj < KPS; ++jj, ++it) {
+          const uint32_t slot = it & (NSLOT - 1);
+          mbar_wait(full_a(slot), (it >> 2) & 1u);
           tc_fence_after();
           if (elect_one()) {
-            if (!(p.debug & 2)) {
 #pragma unroll
-              for (int blk = 0; blk < 2; ++blk) {
+            for (int blk = 0; blk < 2; ++blk) {
 #pragma unroll
-                for (int k4 = 0; k4 < 4; ++k4) {
-                  const uint32_t at = tmem_base + a_col0 + (uint32_t)(slot * 64 + blk * 32 + k4 * 8);
-                  umma_f16_ts(tmem_base + (uint32_t)(blk * TN), at, make_desc_sw128(xs + jj * TN * 128 + k4 * 32), idesc,
-                              (j > 0 || jj > 0 || k4 > 0) ? 1u : 0u);
-                }
+              for (int k4 = 0; k4 < 4; ++k4) {
+                const uint32_t at = tmem_base + A_COL0 + slot * 64 + (uint32_t)(blk * 32 + k4 * 8);
+                umma_f16_ts(blk ? d1 : d0, at, make_desc_sw128(xs + jj * TN * 128 + k4 * 32), idesc,
+                            (j > 0 || jj > 0 || k4 > 0) ? 1u : 0u);
               }
             }
             umma_commit(empty_a(slot));
             if (jj == KPS - 1) {
               umma_commit(empty_in(si));
-              if (j == ns - 1) umma_commit(accum_full);
+              if (j == ns - 1) umma_commit(accum_full(buf));
             }
           }
           __syncwarp();
-          if (++slot == NSLOT) { slot = 0; pha ^= 1; }
         }
         if (++si == S) { si = 0; ph ^= 1; }
       }
       u += ns;
     }
-  } else {
+  } else if (warp < DQ_WARPS) {
     // ===================================== dequantisers =====================================
     const int grp = warp >> 2;                         // 0..3
     const int blk = grp & 1, kpar = grp >> 1;
     const int q = warp & 3;                          // TMEM lane quarter this warp may touch
     const int r = q * 32 + lane;                     // weight row within the 128-row block
-    const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
+    const uint32_t a_dst = tmem_base + ((uint32_t)(q * 32) << 16) + A_COL0 + (uint32_t)(blk * 32);
     // SWIZZLE_128B tile [128 rows x 128 B]: row r at (r/8)*1024 + (r%8)*128, 16-byte chunk c at (c ^ (r%8))
     const uint32_t w_row_off = (uint32_t)(blk * W_TILE_BYTES + (r >> 3) * 1024 + (r & 7) * 128);
     const uint32_t w_xor = (uint32_t)(r & 7);
-    const int dq_tid = threadIdx.x;
+    const uint32_t sb_off = (uint32_t)(blk * 2 * SB_TILE_BYTES + r * 16);
+    const uint32_t half_sel = kpar ? 0x3232u : 0x1010u;   // which 16-bit half of a scale word is this thread's k-block
 
+    int si = 0, ph = 0, sbi = 0, sbph = 0;
+    uint32_t it = (uint32_t)kpar;                    // global k-block counter of this thread (slot = it % 4)
+    uint4 s8 = make_uint4(0u, 0u, 0u, 0u), b8 = s8;
+
+    // one k-block: 64 codes of row r -> 32 packed 16-bit pairs -> A ring slot
+    auto kblock = [&](uint32_t wsrc, int jj, uint32_t s2, uint32_t b2) {
+      uint32_t o[32];
+      uint4 pk[PKB / 16];
+#pragma unroll
+      for (int c = 0; c < PKB / 16; ++c) pk[c] = lds128(wsrc + ((((uint32_t)(jj * (PKB / 16) + c)) ^ w_xor) << 4));
+      const uint32_t* pw = reinterpret_cast<const uint32_t*>(pk);
+#pragma unroll
+      for (int c = 0; c < 8; ++c) dequant8<T, BITS, XPERM>(pw + c * (BITS / 4), s2, b2, o + 4 * c);
+      const uint32_t slot = it & (NSLOT - 1);
+      mbar_wait(empty_a(slot), ((it >> 2) & 1u) ^ 1u);
+      tc_fence_after();
+      tmem_st32(a_dst + slot * 64, o);
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(full_a(slot));
+      it += 2;
+    };
+
+    for (long long u = u_begin; u < u_end;) {
+      const int tile = (int)(u / p.num_st), s0 = (int)(u % p.num_st);
+      const int ns = (int)min((long long)(p.num_st - s0), u_end - u);
+      if (p.sb_tma) {
+        for (int st = s0; st < s0 + ns; ++st) {
+          if (st == s0 || (st % SPG) == 0) {             // next group of 8 k-blocks: scales / biases of this row
+            mbar_wait(sb_full(sbi), (uint32_t)sbph);
+            const uint32_t src = sb_ring + sbi * SB_SLOT_BYTES + sb_off;
+            s8 = lds128(src);
+            b8 = lds128(src + SB_TILE_BYTES);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sb_empty(sbi));
+            if (++sbi == NSB) { sbi = 0; sbph ^= 1; }
+          }
+          mbar_wait(full_w(si), (uint32_t)ph);
+          const uint32_t wsrc = in_ring + si * p.in_stage_bytes + w_row_off;
+          if constexpr (KPS == 4) {
+            // stage st holds k-blocks 4*(st&1) + {0..3} of the group: words 2*(st&1) + {0,1}
+            const bool hi = (st & 1) != 0;
+            const uint32_t sw0 = hi ? s8.z : s8.x, sw1 = hi ? s8.w : s8.y;
+            const uint32_t bw0 = hi ? b8.z : b8.x, bw1 = hi ? b8.w : b8.y;
+            kblock(wsrc, kpar, prmt(sw0, 0u, half_sel), prmt(bw0, 0u, half_sel));
+            kblock(wsrc, kpar + 2, prmt(sw1, 0u, half_sel), prmt(bw1, 0u, half_sel));
+          } else {
+            // stage st holds k-blocks 2*(st&3) + {0,1}: word st&3
+            const int wsel = st & 3;
+            const uint32_t sw = wsel == 0 ? s8.x : (wsel == 1 ? s8.y : (wsel == 2 ? s8.z : s8.w));
+            const uint32_t bw = wsel == 0 ? b8.x : (wsel == 1 ? b8.y : (wsel == 2 ? b8.z : b8.w));
+            kblock(wsrc, kpar, prmt(sw, 0u, half_sel), prmt(bw, 0u, half_sel));
+          }
+          if (++si == S) { si = 0; ph ^= 1; }
+        }
+      } else {
+        // scale rows are not 16-byte multiples (K % 512 != 0, e.g. a TP shard): read them from global memory
+        const int pair = tile / p.tiles_m;
+        const int grow = (blk ? (silu ? p.N / 2 + pair * 128 : pair * 256 + 128) : (silu ? pair * 128 : pair * 256)) + r;
+        const bool row_ok = grow < p.N;
+        const T* sp = reinterpret_cast<const T*>(p.scales) + (int64_t)(row_ok ? grow : 0) * p.num_kb;
+        const T* bp = reinterpret_cast<const T*>(p.biases) + (int64_t)(row_ok ? grow : 0) * p.num_kb;
+        const T zero = Tr<T>::from_f(0.f);
+        for (int st = s0; st < s0 + ns; ++st) {
+          T sv[KPS / 2], bv[KPS / 2];
+#pragma unroll
+          for (int j2 = 0; j2 < KPS / 2; ++j2) {
+            const int kb = st * KPS + kpar + 2 * j2;
+            const bool ok = row_ok && kb < p.num_kb;          // k-blocks past K are zero-filled by TMA: A = 0
+            sv[j2] = ok ? __ldg(sp + kb) : zero;
+            bv[j2] = ok ? __ldg(bp + kb) : zero;
+          }
+          mbar_wait(full_w(si), (uint32_t)ph);
+          const uint32_t wsrc = in_ring + si * p.in_stage_bytes + w_row_off;
+#pragma unroll
+          for (int j2 = 0; j2 < KPS / 2; ++j2) kblock(wsrc, kpar + 2 * j2, dup16(sv[j2]), dup16(bv[j2]));
+          if (++si == S) { si = 0; ph ^= 1; }
+        }
+      }
+      u += ns;
+    }
+  } else {
+    // ===================================== epilogue warps ===================================
+    const int e = warp - DQ_WARPS;                     // == warp % 4: the TMEM lane quarter this warp may read
+    const int r = e * 32 + lane;                     // output row (weight row) within the 128-row block
+    const uint32_t lane_base = tmem_base + ((uint32_t)(e * 32) << 16);
+    const int et = threadIdx.x - DQ_THREADS;         // 0..127
+    pdl_wait();                                      // y (residual) belongs to the previous kernels
     int seg = 0;
-    // position of the next k-block this thread handles: global k-block iteration, its stage ring slot, its A slot
-    int it_mine = kpar, st_mine = 0, si = 0, ph = 0, slot = kpar, pha = 0;
     for (long long u = u_begin; u < u_end; ++seg) {
       const int tile = (int)(u / p.num_st), s0 = (int)(u % p.num_st);
       const int ns = (int)min((long long)(p.num_st - s0), u_end - u);
@@ -396,77 +558,9 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
       const int rowA0 = silu ? pair * 128 : pair * 256;
       const int rowB0 = silu ? p.N / 2 + pair * 128 : pair * 256 + 128;
       const int tok0 = tm * TN;
-      const int grow = (blk ? rowB0 : rowA0) + r;
-      const bool row_ok = grow < p.N;
-      const T* sp = reinterpret_cast<const T*>(p.scales) + (int64_t)(row_ok ? grow : 0) * p.num_kb;
-      const T* bp = reinterpret_cast<const T*>(p.biases) + (int64_t)(row_ok ? grow : 0) * p.num_kb;
-      const int kb_lo = s0 * KPS, kb_hi = (s0 + ns) * KPS;     // k-blocks of this segment (the tail may pass num_kb)
-
-      auto process = [&](uint32_t s2, uint32_t b2) {
-        mbar_wait(full_in(si), (uint32_t)ph);
-        const int jj = it_mine & (KPS - 1);
-        const uint32_t wsrc = in_ring + si * p.in_stage_bytes + w_row_off;
-        uint32_t o[32];
-        if (!(p.debug & 16)) {
-          uint4 pk[PKB / 16];
-#pragma unroll
-          for (int c = 0; c < PKB / 16; ++c) pk[c] = lds128(wsrc + ((((uint32_t)(jj * (PKB / 16) + c)) ^ w_xor) << 4));
-          const uint32_t* pw = reinterpret_cast<const uint32_t*>(pk);
-#pragma unroll
-          for (int c = 0; c < 8; ++c) dequant8<T, BITS>(pw + c * (BITS / 4), s2, b2, o + 4 * c);
-        } else {
-#pragma unroll
-          for (int c = 0; c < 32; ++c) o[c] = s2;
-        }
-        mbar_wait(empty_a(slot), (uint32_t)(pha ^ 1));
-        tc_fence_after();
-        if (!(p.debug & 8)) {
-          tmem_st32(lane_base + a_col0 + (uint32_t)(slot * 64 + blk * 32), o);
-          tmem_st_wait();
-        }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(full_a(slot));
-        it_mine += 2;
-        const int st_new = it_mine >> LKPS;
-        if (st_new != st_mine) { st_mine = st_new; if (++si == S) { si = 0; ph ^= 1; } }
-        slot += 2;
-        if (slot >= NSLOT) { slot -= NSLOT; pha ^= 1; }
-      };
-
-      // this thread takes the k-blocks of parity kpar (stage starts are even, so global and local parity agree)
-      if (p.vec_sb) {
-        // scales / biases of 8 consecutive k-blocks per 128-bit load, prefetched one group ahead
-        const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
-        const uint4* sp4 = reinterpret_cast<const uint4*>(sp);
-        const uint4* bp4 = reinterpret_cast<const uint4*>(bp);
-        const int g_first = kb_lo >> 3, g_last = (kb_hi - 1) >> 3;
-        const uint32_t sel = kpar ? 0x3232u : 0x1010u;
-        uint4 sv_n = row_ok ? __ldg(sp4 + g_first) : z4;
-        uint4 bv_n = row_ok ? __ldg(bp4 + g_first) : z4;
-        for (int g8 = g_first; g8 <= g_last; ++g8) {
-          const uint4 sv = sv_n, bv = bv_n;
-          if (g8 < g_last && row_ok) { sv_n = __ldg(sp4 + g8 + 1); bv_n = __ldg(bp4 + g8 + 1); }
-          const uint32_t sw[4] = {sv.x, sv.y, sv.z, sv.w}, bw[4] = {bv.x, bv.y, bv.z, bv.w};
-#pragma unroll
-          for (int j2 = 0; j2 < 4; ++j2) {
-            const int kb = g8 * 8 + 2 * j2 + kpar;
-            if (kb >= kb_lo && kb < kb_hi) process(prmt(sw[j2], 0u, sel), prmt(bw[j2], 0u, sel));
-          }
-        }
-      } else {
-        const T zero = Tr<T>::from_f(0.f);
-        for (int kb = kb_lo + kpar; kb < kb_hi; kb += 2) {
-          const bool ok = row_ok && kb < p.num_kb;            // k-blocks past K are zero-filled by TMA: A = 0
-          const T sv = ok ? sp[kb] : zero, bv = ok ? bp[kb] : zero;
-          process(dup16(sv), dup16(bv));
-        }
-      }
-
-      // ===================================== epilogue of the segment =========================
-      mbar_wait(accum_full, (uint32_t)(seg & 1));
-      tc_fence_after();
+      const int buf = NBUF == 2 ? (seg & 1) : 0;
       const int n0 = rowA0 + r, n1 = rowB0 + r;        // output columns of this thread (block 0 / block 1)
+      const int c0 = p.y_perm ? perm8_pos(n0) : n0, c1 = p.y_perm ? perm8_pos(n1) : n1;
       const bool full = (s0 == 0 && ns == p.num_st);
       // a tile shared by several CTAs is summed with L2 atomics: straight into y for ADD_RESIDUAL, else into the
       // fp32 accumulator owned by the tile's first CTA; the last CTA to arrive applies the epilogue and re-zeroes it
@@ -479,8 +573,8 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
         if (tok >= p.M_tok) return;
         if (p.epi == B200P_EPI_STORE) {
           T* y = reinterpret_cast<T*>(p.y) + (int64_t)tok * p.ldy;
-          if (n0 < p.N) y[n0] = Tr<T>::from_f(a0);
-          if (n1 < p.N) y[n1] = Tr<T>::from_f(a1);
+          if (n0 < p.N) y[c0] = Tr<T>::from_f(a0);
+          if (n1 < p.N) y[c1] = Tr<T>::from_f(a1);
         } else if (p.epi == B200P_EPI_STORE_F32) {
           float* y = reinterpret_cast<float*>(p.y) + (int64_t)tok * p.ldy;
           if (n0 < p.N) y[n0] = a0;
@@ -496,15 +590,17 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
           }
         } else {
           T* y = reinterpret_cast<T*>(p.y) + (int64_t)tok * p.ldy;
-          if (n0 < p.N / 2) y[n0] = Tr<T>::from_f(silu_tc(a0) * a1);
+          if (n0 < p.N / 2) y[c0] = Tr<T>::from_f(silu_tc(a0) * a1);
         }
       };
 
-      // 8-token chunks are dealt round-robin to the four warp groups; every thread reads both blocks' rows
-      for (int t = grp * 8; t < TN && !(p.debug & 4); t += 32) {
+      mbar_wait(accum_full(buf), (uint32_t)((seg / NBUF) & 1));
+      tc_fence_after();
+      const uint32_t dA = lane_base + d_col(buf, 0), dB = lane_base + d_col(buf, 1);
+      for (int t = 0; t < TN; t += 8) {
         float v0[8], v1[8];
-        tmem_ld8(lane_base + (uint32_t)t, v0);
-        tmem_ld8(lane_base + (uint32_t)(TN + t), v1);
+        tmem_ld8(dA + (uint32_t)t, v0);
+        tmem_ld8(dB + (uint32_t)t, v1);
         tmem_ld_wait();
         if (!via_acc) {
 #pragma unroll
@@ -513,36 +609,31 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             if (tok0 + t + j < p.M_tok) {
-              if (p.debug & 32) {
-                acc[(int64_t)(t + j) * 128 + r] = v0[j];
-                acc[((int64_t)TN + t + j) * 128 + r] = v1[j];
-              } else {
-                atomicAdd(acc + (int64_t)(t + j) * 128 + r, v0[j]);
-                atomicAdd(acc + ((int64_t)TN + t + j) * 128 + r, v1[j]);
-              }
+              atomicAdd(acc + (int64_t)(t + j) * 128 + r, v0[j]);
+              atomicAdd(acc + ((int64_t)TN + t + j) * 128 + r, v1[j]);
             }
           }
         }
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(accum_empty);         // D may be overwritten by the next segment's MMAs
-      if (via_acc && !(p.debug & (4 | 64))) {
+      if (lane == 0) mbar_arrive(accum_empty(buf));    // this D buffer may be overwritten by a later segment's MMAs
+      if (via_acc) {
         const int nseg = owner_of((long long)tile * p.num_st + p.num_st - 1, p.U, G) - c_first + 1;
         __threadfence();
-        named_bar_sync(1, DQ_THREADS);
-        if (dq_tid == 0) {
+        named_bar_sync(1, EPI_THREADS);
+        if (et == 0) {
           const int old = atomicAdd(p.ws_counter + tile, 1);
           const int last = (old == nseg - 1);
           if (last) p.ws_counter[tile] = 0;            // self-cleaning for the next launch
           asm volatile("st.shared.u32 [%0], %1;" ::"r"(flag_slot), "r"(last) : "memory");
         }
-        named_bar_sync(1, DQ_THREADS);
+        named_bar_sync(1, EPI_THREADS);
         int last;
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(last) : "r"(flag_slot));
         if (last) {
           __threadfence();
-          for (int t = grp * 8; t < TN; t += 32) {
+          for (int t = 0; t < TN; t += 8) {
             float v0[8], v1[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) {               // 16 independent L2 loads in flight
@@ -557,7 +648,7 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
             }
           }
         }
-        named_bar_sync(1, DQ_THREADS);                 // flag_slot is reused by the next segment
+        named_bar_sync(1, EPI_THREADS);                // flag_slot is reused by the next segment
       }
       u += ns;
     }
@@ -565,7 +656,7 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
   pdl_launch_dependents();
   tc_fence_before();
   __syncthreads();
-  if (warp == DQ_WARPS + 1) {
+  if (warp == WARP_MMA) {
     tc_fence_after();
     tmem_dealloc(tmem_base, TMEM_COLS);
   }
@@ -588,6 +679,7 @@ static EncodeTiledFn get_encode() {
 }
 
 constexpr int SMEM_BUDGET = 227 * 1024;
+constexpr int SMEM_FIXED = 1024 /*align*/ + NSB * SB_SLOT_BYTES + 512 /*barriers*/;
 constexpr int MIN_TC_M = 5;        // below this the CUDA-core GEMV wins (weights read once either way)
 constexpr int MIN_UNITS_PER_CTA = 2;
 
@@ -609,11 +701,10 @@ static TcPlan make_plan(int64_t M, int64_t N, int64_t K, int bits, int epi) {
   const int sms = sm_count();
   pl.grid = (int)(g > sms ? sms : (g < 1 ? 1 : g));
   pl.in_stage_bytes = 2 * W_TILE_BYTES + kps * tn * 128;
-  const int avail = SMEM_BUDGET - 1024 /*align*/ - 512 /*barriers*/;
-  int st = avail / pl.in_stage_bytes;
-  if (st > 8) st = 8;
+  int st = (SMEM_BUDGET - SMEM_FIXED) / pl.in_stage_bytes;
+  if (st > MAX_STAGES) st = MAX_STAGES;
   pl.in_stages = st;
-  pl.smem_bytes = 1024 + st * pl.in_stage_bytes + 512;
+  pl.smem_bytes = SMEM_FIXED + st * pl.in_stage_bytes;
   return pl;
 }
 
@@ -644,47 +735,73 @@ size_t qmm_tc_workspace_bytes(int64_t M, int64_t N, int64_t K) {
   return ws_counter_bytes(M, N) + (size_t)sm_count() * 2 * tn * 128 * sizeof(float);
 }
 
-template <typename T, int BITS>
-static int launch_tc(const CUtensorMap& tmw, const CUtensorMap& tmx, const TcParams& p, const TcPlan& pl, cudaStream_t st) {
-  auto kern = qmm_tc_kernel<T, BITS>;
+template <typename T, int BITS, bool XPERM>
+static int launch_tc(const CUtensorMap* tms, const TcParams& p, const TcPlan& pl, cudaStream_t st) {
+  auto kern = qmm_tc_kernel<T, BITS, XPERM>;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(qmm_tc_kernel)");
     attr_set = true;
   }
-  kern<<<dim3((unsigned)pl.grid), TC_THREADS, pl.smem_bytes, st>>>(tmw, tmx, p);
-  B200P_LAUNCH_CHECK("qmm_tc_kernel");
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)pl.grid);
+  cfg.blockDim = dim3(TC_THREADS);
+  cfg.dynamicSmemBytes = (size_t)pl.smem_bytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tms[0], tms[1], tms[2], tms[3], p);
+  if (e != cudaSuccess) return cuda_fail(e, "qmm_tc_kernel launch");
+  return B200P_OK;
+}
+
+static int encode_2d(EncodeTiledFn enc, CUtensorMap* tm, CUtensorMapDataType dt, const void* base, uint64_t d0, uint64_t d1,
+                     uint64_t stride_bytes, uint32_t b0, uint32_t b1, CUtensorMapSwizzle sw, const char* what) {
+  cuuint64_t dims[2] = {(cuuint64_t)d0, (cuuint64_t)d1};
+  cuuint64_t strides[1] = {(cuuint64_t)stride_bytes};
+  cuuint32_t box[2] = {b0, b1};
+  cuuint32_t estr[2] = {1u, 1u};
+  CUresult r = enc(tm, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  B200P_REQUIRE(r == CUDA_SUCCESS, B200P_ERR_CUDA, "cuTensorMapEncodeTiled(%s) failed: %d", what, (int)r);
   return B200P_OK;
 }
 
 int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b, void* y, int64_t M, int64_t N,
-                  int64_t K, int64_t ldx, int64_t ldy, int bits, int dtype, int epi, void* ws, size_t ws_bytes,
+                  int64_t K, int64_t ldx, int64_t ldy, int bits, int dtype, int epi, int flags, void* ws, size_t ws_bytes,
                   cudaStream_t st) {
   EncodeTiledFn enc = get_encode();
   B200P_REQUIRE(enc != nullptr, B200P_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
   TcPlan pl = make_plan(M, N, K, bits, epi);
   B200P_REQUIRE(pl.in_stages >= 2, B200P_ERR_ARG, "shared memory too small for the tensor path");
-  CUtensorMap tmw, tmx;
-  {
-    cuuint64_t dims[2] = {(cuuint64_t)(K * bits / 8), (cuuint64_t)N};
-    cuuint64_t strides[1] = {(cuuint64_t)(K * bits / 8)};
-    cuuint32_t box[2] = {128u, 128u};
-    cuuint32_t estr[2] = {1u, 1u};
-    CUresult r = enc(&tmw, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<uint32_t*>(w), dims, strides, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                     CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    B200P_REQUIRE(r == CUDA_SUCCESS, B200P_ERR_CUDA, "cuTensorMapEncodeTiled(weights) failed: %d", (int)r);
-  }
-  {
-    cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)M};
-    cuuint64_t strides[1] = {(cuuint64_t)(ldx * 2)};
-    cuuint32_t box[2] = {64u, (cuuint32_t)pl.TN};
-    cuuint32_t estr[2] = {1u, 1u};
-    CUresult r = enc(&tmx, dtype == B200P_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
-                     const_cast<void*>(x), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    B200P_REQUIRE(r == CUDA_SUCCESS, B200P_ERR_CUDA, "cuTensorMapEncodeTiled(x) failed: %d", (int)r);
+  const bool x_perm = (flags & B200P_X_PERM8) != 0, y_perm = (flags & B200P_Y_PERM8) != 0;
+  B200P_REQUIRE(!x_perm || bits == 4, B200P_ERR_ARG, "B200P_X_PERM8 is the 4-bit activation layout");
+  B200P_REQUIRE(!y_perm || epi == B200P_EPI_STORE || epi == B200P_EPI_SILU_MUL, B200P_ERR_ARG,
+                "B200P_Y_PERM8 applies to 16-bit outputs only");
+  const int num_kb = (int)(K / 64);
+  const bool sb_tma = (num_kb % 8) == 0 && aligned(s, 16) && aligned(b, 16);
+  const CUtensorMapDataType dt16 = dtype == B200P_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  CUtensorMap tms[4];
+  int rc = encode_2d(enc, &tms[0], CU_TENSOR_MAP_DATA_TYPE_UINT8, w, (uint64_t)(K * bits / 8), (uint64_t)N,
+                     (uint64_t)(K * bits / 8), 128u, 128u, CU_TENSOR_MAP_SWIZZLE_128B, "weights");
+  if (rc) return rc;
+  rc = encode_2d(enc, &tms[1], dt16, x, (uint64_t)K, (uint64_t)M, (uint64_t)(ldx * 2), 64u, (uint32_t)pl.TN,
+                 CU_TENSOR_MAP_SWIZZLE_128B, "x");
+  if (rc) return rc;
+  if (sb_tma) {
+    rc = encode_2d(enc, &tms[2], dt16, s, (uint64_t)num_kb, (uint64_t)N, (uint64_t)num_kb * 2, 8u, 128u,
+                   CU_TENSOR_MAP_SWIZZLE_NONE, "scales");
+    if (rc) return rc;
+    rc = encode_2d(enc, &tms[3], dt16, b, (uint64_t)num_kb, (uint64_t)N, (uint64_t)num_kb * 2, 8u, 128u,
+                   CU_TENSOR_MAP_SWIZZLE_NONE, "biases");
+    if (rc) return rc;
+  } else {
+    tms[2] = tms[0];
+    tms[3] = tms[0];
   }
   TcParams p;
   p.scales = s; p.biases = b; p.y = y;
@@ -693,17 +810,17 @@ int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b
   B200P_REQUIRE(ws_bytes >= need && aligned(ws, 16), B200P_ERR_ARG, "qmm workspace too small (%zu < %zu)", ws_bytes, need);
   p.ws_counter = reinterpret_cast<int*>(ws);
   p.ws_acc = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + counters);
-  p.M_tok = (int)M; p.N = (int)N; p.K = (int)K; p.TN = pl.TN; p.ldy = ldy; p.epi = epi;
-  p.num_kb = (int)(K / 64); p.pairs = pl.pairs; p.tiles_m = pl.tiles_m; p.U = pl.U;
+  p.M_tok = (int)M; p.N = (int)N; p.K = (int)K; p.TN = pl.TN; p.ldy = ldy; p.epi = epi; p.y_perm = y_perm ? 1 : 0;
+  p.num_kb = num_kb; p.pairs = pl.pairs; p.tiles_m = pl.tiles_m; p.U = pl.U;
   p.num_st = (p.num_kb + (bits == 4 ? 4 : 2) - 1) / (bits == 4 ? 4 : 2);
-  p.vec_sb = (p.num_kb % 8 == 0) ? 1 : 0;
+  p.sb_tma = sb_tma ? 1 : 0;
   p.in_stages = pl.in_stages; p.in_stage_bytes = pl.in_stage_bytes;
-  { const char* d = getenv("B200P_TC_DEBUG"); p.debug = d ? atoi(d) : 0; }
   if (dtype == B200P_F16) {
-    return bits == 4 ? launch_tc<__half, 4>(tmw, tmx, p, pl, st) : launch_tc<__half, 8>(tmw, tmx, p, pl, st);
+    if (bits == 8) return launch_tc<__half, 8, false>(tms, p, pl, st);
+    return x_perm ? launch_tc<__half, 4, true>(tms, p, pl, st) : launch_tc<__half, 4, false>(tms, p, pl, st);
   } else {
     B200P_REQUIRE(bits == 4, B200P_ERR_ARG, "bf16 8-bit is not on the tensor path");
-    return launch_tc<__nv_bfloat16, 4>(tmw, tmx, p, pl, st);
+    return x_perm ? launch_tc<__nv_bfloat16, 4, true>(tms, p, pl, st) : launch_tc<__nv_bfloat16, 4, false>(tms, p, pl, st);
   }
 }
 

@@ -39,7 +39,7 @@ template <typename T, int BITS, int MB, int EPI>
 __global__ void __launch_bounds__(128)
 qmv_kernel(const T* __restrict__ x, const uint32_t* __restrict__ w, const T* __restrict__ scales,
            const T* __restrict__ biases, void* __restrict__ yv, int m_valid, int64_t N, int64_t K,
-           int64_t ldx, int64_t ldy, int gs) {
+           int64_t ldx, int64_t ldy, int gs, int flags) {
   constexpr int WPL = (32 / BITS) * 4;  // weights per lane per 128-bit load
   const int lane = threadIdx.x & 31;
   const int64_t pair = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
@@ -87,6 +87,10 @@ qmv_kernel(const T* __restrict__ x, const uint32_t* __restrict__ w, const T* __r
         if (m < m_valid) {
           float xv[8];
           XVec<T>::load(x + (int64_t)m * ldx + k + 8 * c, xv);
+          if (flags & B200P_X_PERM8) {   // stored order [0,4,1,5,2,6,3,7] -> natural
+            const float t1 = xv[1], t2 = xv[2], t3 = xv[3], t4 = xv[4], t5 = xv[5], t6 = xv[6];
+            xv[4] = t1; xv[1] = t2; xv[5] = t3; xv[2] = t4; xv[6] = t5; xv[3] = t6;
+          }
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             acc0[m] = fmaf(xv[j], wa[j], acc0[m]);
@@ -103,13 +107,16 @@ qmv_kernel(const T* __restrict__ x, const uint32_t* __restrict__ w, const T* __r
     acc1[m] = warp_sum(acc1[m]);
   }
   if (lane == 0) {
+    const bool yp = (flags & B200P_Y_PERM8) != 0;   // 16-bit outputs in the PERM8 column order
+    const int64_t c0 = yp ? ((r0 & ~7ll) | (((r0 & 3) << 1) | ((r0 >> 2) & 1))) : r0;
+    const int64_t c1 = yp ? ((r1 & ~7ll) | (((r1 & 3) << 1) | ((r1 >> 2) & 1))) : r1;
 #pragma unroll
     for (int m = 0; m < MB; ++m) {
       if (m >= m_valid) break;
       if (EPI == B200P_EPI_STORE) {
         T* y = reinterpret_cast<T*>(yv) + (int64_t)m * ldy;
-        y[r0] = Tr<T>::from_f(acc0[m]);
-        y[r1] = Tr<T>::from_f(acc1[m]);
+        y[c0] = Tr<T>::from_f(acc0[m]);
+        y[c1] = Tr<T>::from_f(acc1[m]);
       } else if (EPI == B200P_EPI_STORE_F32) {
         float* y = reinterpret_cast<float*>(yv) + (int64_t)m * ldy;
         y[r0] = acc0[m];
@@ -120,7 +127,7 @@ qmv_kernel(const T* __restrict__ x, const uint32_t* __restrict__ w, const T* __r
         y[r1] += acc1[m];
       } else {
         T* y = reinterpret_cast<T*>(yv) + (int64_t)m * ldy;
-        y[r0] = Tr<T>::from_f(silu_f(acc0[m]) * acc1[m]);
+        y[c0] = Tr<T>::from_f(silu_f(acc0[m]) * acc1[m]);
       }
     }
   }
@@ -128,16 +135,16 @@ qmv_kernel(const T* __restrict__ x, const uint32_t* __restrict__ w, const T* __r
 
 template <typename T, int BITS, int EPI>
 static int launch_qmv_mb(const T* x, const uint32_t* w, const T* s, const T* b, void* y, int64_t M, int64_t N,
-                         int64_t K, int64_t ldx, int64_t ldy, int gs, cudaStream_t st) {
+                         int64_t K, int64_t ldx, int64_t ldy, int gs, int flags, cudaStream_t st) {
   const size_t ysz = (EPI == B200P_EPI_STORE_F32 || EPI == B200P_EPI_ADD_RESIDUAL) ? sizeof(float) : sizeof(T);
   dim3 grid((unsigned)((N / 2 + 3) / 4)), block(128);
   for (int64_t m0 = 0; m0 < M; m0 += 4) {
     int mv = (int)((M - m0) < 4 ? (M - m0) : 4);
     const T* xp = x + m0 * ldx;
     void* yp = reinterpret_cast<char*>(y) + m0 * ldy * ysz;
-    if (mv == 1) qmv_kernel<T, BITS, 1, EPI><<<grid, block, 0, st>>>(xp, w, s, b, yp, mv, N, K, ldx, ldy, gs);
-    else if (mv == 2) qmv_kernel<T, BITS, 2, EPI><<<grid, block, 0, st>>>(xp, w, s, b, yp, mv, N, K, ldx, ldy, gs);
-    else qmv_kernel<T, BITS, 4, EPI><<<grid, block, 0, st>>>(xp, w, s, b, yp, mv, N, K, ldx, ldy, gs);
+    if (mv == 1) qmv_kernel<T, BITS, 1, EPI><<<grid, block, 0, st>>>(xp, w, s, b, yp, mv, N, K, ldx, ldy, gs, flags);
+    else if (mv == 2) qmv_kernel<T, BITS, 2, EPI><<<grid, block, 0, st>>>(xp, w, s, b, yp, mv, N, K, ldx, ldy, gs, flags);
+    else qmv_kernel<T, BITS, 4, EPI><<<grid, block, 0, st>>>(xp, w, s, b, yp, mv, N, K, ldx, ldy, gs, flags);
   }
   B200P_LAUNCH_CHECK("qmv_kernel");
   return B200P_OK;
@@ -145,8 +152,8 @@ static int launch_qmv_mb(const T* x, const uint32_t* w, const T* s, const T* b, 
 
 template <typename T>
 static int launch_qmv_t(const void* x, const uint32_t* w, const void* s, const void* b, void* y, int64_t M,
-                        int64_t N, int64_t K, int64_t ldx, int64_t ldy, int gs, int bits, int epi, cudaStream_t st) {
-#define GO(B_, E_) return launch_qmv_mb<T, B_, E_>((const T*)x, w, (const T*)s, (const T*)b, y, M, N, K, ldx, ldy, gs, st)
+                        int64_t N, int64_t K, int64_t ldx, int64_t ldy, int gs, int bits, int epi, int flags, cudaStream_t st) {
+#define GO(B_, E_) return launch_qmv_mb<T, B_, E_>((const T*)x, w, (const T*)s, (const T*)b, y, M, N, K, ldx, ldy, gs, flags, st)
   if (bits == 4) {
     switch (epi) { case 0: GO(4, 0); case 1: GO(4, 1); case 2: GO(4, 2); case 3: GO(4, 3); }
   } else {
@@ -158,8 +165,8 @@ static int launch_qmv_t(const void* x, const uint32_t* w, const void* s, const v
 }
 
 int qmv_launch(const void* x, const uint32_t* w, const void* s, const void* b, void* y, int64_t M, int64_t N,
-               int64_t K, int64_t ldx, int64_t ldy, int gs, int bits, int dtype, int epi, cudaStream_t st) {
-  B200P_DISPATCH_DTYPE(dtype, T, return (launch_qmv_t<T>(x, w, s, b, y, M, N, K, ldx, ldy, gs, bits, epi, st)));
+               int64_t K, int64_t ldx, int64_t ldy, int gs, int bits, int dtype, int epi, int flags, cudaStream_t st) {
+  B200P_DISPATCH_DTYPE(dtype, T, return (launch_qmv_t<T>(x, w, s, b, y, M, N, K, ldx, ldy, gs, bits, epi, flags, st)));
   return B200P_OK;
 }
 

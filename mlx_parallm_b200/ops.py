@@ -88,8 +88,11 @@ def qmm_workspace_bytes(M, N, K) -> int:
     return int(lib().b200p_qmm_workspace_bytes(M, N, K))
 
 
-def qmm(x, w, scales, biases, group_size=64, bits=4, epilogue=EPI_STORE, out=None, workspace=None):
+def qmm(x, w, scales, biases, group_size=64, bits=4, epilogue=EPI_STORE, out=None, workspace=None,
+        x_perm=False, y_perm=False):
     """quantized_matmul(x, w, scales, biases, transpose=True) with a fused epilogue.
+
+    ``x_perm`` / ``y_perm``: x arrives / the 16-bit y leaves in the PERM8 column order (include/b200p.h).
 
     x [M, K] (row stride = x.stride(0)); out per epilogue:
       EPI_STORE -> [M, N] x.dtype; EPI_STORE_F32 -> [M, N] float32; EPI_ADD_RESIDUAL -> out (float32
@@ -108,11 +111,14 @@ def qmm(x, w, scales, biases, group_size=64, bits=4, epilogue=EPI_STORE, out=Non
             out = torch.empty((M, N // 2), dtype=x.dtype, device=x.device)
         else:
             raise ValueError("EPI_ADD_RESIDUAL needs the residual tensor as `out`")
+    epi_flags = epilogue | (_lib.X_PERM8 if x_perm else 0) | (_lib.Y_PERM8 if y_perm else 0)
     if M > DENSE_INTERIM_MIN_M and not lib().b200p_qmm_tensor_supported(M, N, K, group_size, bits, dtype_code(x.dtype), epilogue):
+        if x_perm or y_perm:
+            raise _lib.B200PError("PERM8 layouts are not available on the interim dense path")
         return _qmm_dense_interim(x, w, scales, biases, group_size, bits, epilogue, out)
     ws_ptr, ws_bytes = (0, 0) if workspace is None else (workspace.data_ptr(), workspace.numel() * workspace.element_size())
     _call(("b200p_qmm", N, K), lambda: lib().b200p_qmm(_p(x), _p(w), _p(scales), _p(biases), _p(out), M, N, K, x.stride(0), out.stride(0),
-                          group_size, bits, dtype_code(x.dtype), epilogue, ws_ptr, ws_bytes, _stream()))
+                          group_size, bits, dtype_code(x.dtype), epi_flags, ws_ptr, ws_bytes, _stream()))
     return out
 
 
@@ -140,14 +146,15 @@ def _qmm_dense_interim(x, w, scales, biases, group_size, bits, epilogue, out):
     return out
 
 
-def rmsnorm(x, w, eps, out=None):
-    """mx.fast.rms_norm on the float32 residual stream -> w.dtype."""
+def rmsnorm(x, w, eps, out=None, out_perm=False):
+    """mx.fast.rms_norm on the float32 residual stream -> w.dtype (``out_perm``: PERM8 column order for a 4-bit qmm)."""
     _dev(x, w, out)
     assert x.dtype == torch.float32 and x.is_contiguous()
     M, H = x.shape
     if out is None:
         out = torch.empty((M, H), dtype=w.dtype, device=x.device)
-    _call("b200p_rmsnorm", lambda: lib().b200p_rmsnorm(_p(x), _p(w), _p(out), M, H, float(eps), dtype_code(w.dtype), _stream()))
+    _call("b200p_rmsnorm", lambda: lib().b200p_rmsnorm(_p(x), _p(w), _p(out), M, H, float(eps), dtype_code(w.dtype),
+                                                      _lib.OUT_PERM8 if out_perm else 0, _stream()))
     return out
 
 
@@ -170,12 +177,12 @@ def attn_workspace_bytes(B, L, Hq, D) -> int:
     return int(lib().b200p_attn_workspace_bytes(B, L, Hq, D))
 
 
-def attn(q, kcache, vcache, lengths, out, B, L, Hq, Hkv, D, scale, workspace=None):
+def attn(q, kcache, vcache, lengths, out, B, L, Hq, Hkv, D, scale, workspace=None, out_perm=False):
     _dev(q, kcache, vcache, lengths, out)
     Tcap = kcache.shape[2]
     ws_ptr, ws_bytes = (0, 0) if workspace is None else (workspace.data_ptr(), workspace.numel() * workspace.element_size())
     _call("b200p_attn", lambda: lib().b200p_attn(_p(q), _p(kcache), _p(vcache), _p(lengths), _p(out), B, L, Hq, Hkv, D, Tcap, float(scale),
-                           dtype_code(q.dtype), ws_ptr, ws_bytes, _stream()))
+                           dtype_code(q.dtype), _lib.OUT_PERM8 if out_perm else 0, ws_ptr, ws_bytes, _stream()))
     return out
 
 

@@ -17,12 +17,8 @@ x = torch.randn((M, K), device="cuda").to(dt)
 ws = torch.zeros((max(ops.qmm_workspace_bytes(M, N, K), 16),), dtype=torch.uint8, device="cuda")
 out = torch.zeros((M, N if epi != 3 else N // 2), device="cuda", dtype=torch.float32 if epi in (1, 2) else dt)
 _lib.check(L.b200p_qmm_set_path(2))
-import ctypes
-tl = torch.zeros((16 * 16 + 64,), dtype=torch.int64, device="cuda")
 evs = []
 for i in range(8):
-    if i == 7:
-        L.b200p_debug_set_timeline(ctypes.c_void_p(tl.data_ptr()))
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     ops.qmm(x, *mats[i % 4], 64, 4, epi, out=out, workspace=ws)
@@ -30,14 +26,4 @@ for i in range(8):
     evs.append((e0, e1))
 torch.cuda.synchronize()
 print("event us per launch:", [round(a.elapsed_time(b) * 1e3, 1) for a, b in evs])
-t2 = tl.cpu()[256:].view(4, 16)
-t = tl.cpu()[:256].view(16, 16)
-b0 = int(t2[0, 0])
-lab = ['dq_top','dq_fullin','dq_lds','dq_emptya','dq_math','dq_arrived','','','mma_top','mma_fullin','mma_fulla','mma_issued','prod_top','prod_emptyin']
-for it in range(4):
-    print('iter', 16 + it, ' '.join(f'{lab[k]}={int(t2[it, k]) - b0}' for k in range(14) if lab[k]))
-names = ["start", "setup_done", "prod_first_tma", "prod_last_tma", "mma_first", "mma_last", "dq_first_full_in", "dq_first_done", "dq_last_done", "accum_full", "epi_done", "end", "dq_i8", "dq_i16"]
-for c in (0, 1, 5):
-    base = int(t[c, 0])
-    print("CTA", c, " ".join(f"{n}={int(t[c, j]) - base}" for j, n in enumerate(names) if int(t[c, j])))
 print("done")
