@@ -18,15 +18,19 @@
 // ADD_RESIDUAL, else into a per-boundary fp32 accumulator that the last-arriving CTA reads, applies the epilogue
 // to and re-zeroes.  Split tiles are therefore summed in arrival order (last-bit run-to-run differences).
 //
-// warp roles (704 threads):
+// warp roles (736 threads):
 //   warps 0..15  dequantisers: 4 groups of 4 warps, group g handles weight block g&1 on k-blocks of parity g>>1;
 //                a thread owns one weight row: LDS packed codes -> 16-bit q*s+b -> tcgen05.st into the A ring;
 //   warps 16..19 epilogue: TMEM -> registers -> global (lanes along n: coalesced), stream-K fix-up;
-//   warp 20      TMA producer (weights, X tiles, scale/bias tiles);
-//   warp 21      TMEM owner + MMA issuer (elect.sync, operands in uniform registers).
+//   warp 20      TMA producer of weights and scale/bias tiles (independent of the previous kernel: starts at once);
+//   warp 21      TMA producer of X tiles (after griddepcontrol.wait);
+//   warp 22      TMEM owner + MMA issuer (elect.sync, operands in uniform registers).
 //
-// rings:  IN  (packed weights 2 x [128 rows x 128 B] + KPS X tiles [TN x 64]) in shared memory, SWIZZLE_128B,
-//             filled by TMA (separate "weights landed" / "X landed" barriers), freed by MMA completion;
+// rings:  W   (packed weights, 2 x [128 rows x 128 B] per stage) in shared memory, SWIZZLE_128B, filled by TMA and
+//             handed back as soon as the dequant warps hold the codes in registers, so the HBM stream never waits
+//             for dequant math or MMAs;
+//         X   (one [TN x 64] activation tile per k-block, 8 slots) SWIZZLE_128B, filled by TMA, freed by MMA
+//             completion (tcgen05.commit);
 //         SB  (scales + biases of 8 k-blocks for both blocks, [128 rows x 16 B] tiles) filled by TMA when the
 //             rows of the scale matrix are 16-byte multiples (K % 512 == 0), else the dequantisers read them
 //             from global memory; freed by the dequant warps as soon as the values are in registers;
@@ -246,18 +250,21 @@ constexpr int DQ_WARPS = 16;
 constexpr int DQ_THREADS = DQ_WARPS * 32;
 constexpr int EPI_WARPS = 4;
 constexpr int EPI_THREADS = EPI_WARPS * 32;
-constexpr int WARP_TMA = DQ_WARPS + EPI_WARPS;
-constexpr int WARP_MMA = WARP_TMA + 1;
+constexpr int WARP_W = DQ_WARPS + EPI_WARPS;     // TMA producer: weights + scale/bias tiles (never waits for the previous grid)
+constexpr int WARP_X = WARP_W + 1;               // TMA producer: activation tiles (after griddepcontrol.wait)
+constexpr int WARP_MMA = WARP_X + 1;
 constexpr int TC_THREADS = (WARP_MMA + 1) * 32;
 constexpr int TMEM_COLS = 512;
 constexpr int MAX_TN = 128;
 constexpr int W_TILE_BYTES = 128 * 128;          // one weight block of one stage: 128 rows x 128 packed bytes
+constexpr int W_STAGE_BYTES = 2 * W_TILE_BYTES;
 constexpr int NSLOT = 4;                         // A ring slots (each: 2 blocks x 32 TMEM columns)
 constexpr uint32_t A_COL0 = 256;                 // TMEM columns [0,256) hold D, [256,512) the A ring
 constexpr int NSB = 2;                           // scale/bias ring slots
 constexpr int SB_TILE_BYTES = 128 * 16;          // 128 rows x 8 k-blocks x 2 bytes
 constexpr int SB_SLOT_BYTES = 4 * SB_TILE_BYTES; // block 0 scales, block 0 biases, block 1 scales, block 1 biases
-constexpr int MAX_STAGES = 8;
+constexpr int MAX_STAGES = 8;                    // weight ring stages / X ring slots (upper bounds)
+constexpr int X_RING_BYTES = 64 * 1024;
 
 struct TcParams {
   const void* scales;
@@ -274,8 +281,9 @@ struct TcParams {
   int pairs, tiles_m;  // output tile t = pair * tiles_m + token tile
   long long U;         // total units = pairs * tiles_m * num_st
   int sb_tma;          // 1: scale/bias tiles come through TMA (num_kb % 8 == 0)
-  int in_stages;
-  int in_stage_bytes;
+  int w_stages;        // weight ring depth
+  int x_slots;         // X ring depth (4 or 8; one slot = the [TN x 64] tile of one k-block)
+  int debug;           // B200P_TC_DEBUG (profiling only): 1 no X loads, 2 no MMA issue, 4 no epilogue stores, 8 no A stores
 };
 
 // CTA that owns linear unit x when U units are dealt to G CTAs as [c*U/G, (c+1)*U/G)
@@ -288,24 +296,28 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
   constexpr int PKB = 64 * BITS / 8;            // packed bytes per row per k-block
   constexpr int KPS = 128 / PKB;                // k-blocks per stage (a stage row is one 128-byte line)
   constexpr int SPG = 8 / KPS;                  // stages per scale/bias group of 8 k-blocks
-  constexpr int W_STAGE_BYTES = 2 * W_TILE_BYTES;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  const uint32_t in_ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const int S = p.in_stages;
-  const uint32_t sb_ring = in_ring + S * p.in_stage_bytes;
-  const uint32_t bar_base = sb_ring + NSB * SB_SLOT_BYTES;
+  const uint32_t w_ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int S = p.w_stages;
   const int TN = p.TN;
+  const uint32_t x_ring = w_ring + S * W_STAGE_BYTES;
+  const uint32_t x_slot_bytes = (uint32_t)(TN * 128);
+  const uint32_t x_mask = (uint32_t)(p.x_slots - 1);
+  const int x_shift = p.x_slots == 8 ? 3 : 2;
+  const uint32_t sb_ring = x_ring + p.x_slots * x_slot_bytes;
+  const uint32_t bar_base = sb_ring + NSB * SB_SLOT_BYTES;
   const int NBUF = TN > 64 ? 1 : 2;              // D buffers: buffer d, block b at columns d*128 + b*64 (TN <= 64) / b*128
   auto full_w = [&](int s) { return bar_base + 8u * s; };
-  auto full_x = [&](int s) { return bar_base + 8u * (MAX_STAGES + s); };
-  auto empty_in = [&](int s) { return bar_base + 8u * (2 * MAX_STAGES + s); };
-  auto full_a = [&](int s) { return bar_base + 8u * (3 * MAX_STAGES + s); };
-  auto empty_a = [&](int s) { return bar_base + 8u * (3 * MAX_STAGES + NSLOT + s); };
-  auto sb_full = [&](int s) { return bar_base + 8u * (3 * MAX_STAGES + 2 * NSLOT + s); };
-  auto sb_empty = [&](int s) { return bar_base + 8u * (3 * MAX_STAGES + 2 * NSLOT + NSB + s); };
-  auto accum_full = [&](int d) { return bar_base + 8u * (3 * MAX_STAGES + 2 * NSLOT + 2 * NSB + d); };
-  auto accum_empty = [&](int d) { return bar_base + 8u * (3 * MAX_STAGES + 2 * NSLOT + 2 * NSB + 2 + d); };
-  const uint32_t tmem_slot = bar_base + 8u * (3 * MAX_STAGES + 2 * NSLOT + 2 * NSB + 4);
+  auto empty_w = [&](int s) { return bar_base + 8u * (MAX_STAGES + s); };
+  auto full_x = [&](int s) { return bar_base + 8u * (2 * MAX_STAGES + s); };
+  auto empty_x = [&](int s) { return bar_base + 8u * (3 * MAX_STAGES + s); };
+  auto full_a = [&](int s) { return bar_base + 8u * (4 * MAX_STAGES + s); };
+  auto empty_a = [&](int s) { return bar_base + 8u * (4 * MAX_STAGES + NSLOT + s); };
+  auto sb_full = [&](int s) { return bar_base + 8u * (4 * MAX_STAGES + 2 * NSLOT + s); };
+  auto sb_empty = [&](int s) { return bar_base + 8u * (4 * MAX_STAGES + 2 * NSLOT + NSB + s); };
+  auto accum_full = [&](int d) { return bar_base + 8u * (4 * MAX_STAGES + 2 * NSLOT + 2 * NSB + d); };
+  auto accum_empty = [&](int d) { return bar_base + 8u * (4 * MAX_STAGES + 2 * NSLOT + 2 * NSB + 2 + d); };
+  const uint32_t tmem_slot = bar_base + 8u * (4 * MAX_STAGES + 2 * NSLOT + 2 * NSB + 4);
   const uint32_t flag_slot = tmem_slot + 4u;
   auto d_col = [&](int d, int b) { return (uint32_t)(TN > 64 ? b * 128 : d * 128 + b * 64); };
 
@@ -315,7 +327,8 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
   const bool silu = p.epi == B200P_EPI_SILU_MUL;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < S; ++s) { mbar_init(full_w(s), 1); mbar_init(full_x(s), 1); mbar_init(empty_in(s), 1); }
+    for (int s = 0; s < S; ++s) { mbar_init(full_w(s), 1); mbar_init(empty_w(s), DQ_WARPS); }
+    for (int s = 0; s < p.x_slots; ++s) { mbar_init(full_x(s), 1); mbar_init(empty_x(s), 1); }
     for (int s = 0; s < NSLOT; ++s) { mbar_init(full_a(s), 8); mbar_init(empty_a(s), 1); }
     for (int s = 0; s < NSB; ++s) { mbar_init(sb_full(s), 1); mbar_init(sb_empty(s), DQ_WARPS); }
     for (int d = 0; d < 2; ++d) { mbar_init(accum_full(d), 1); mbar_init(accum_empty(d), EPI_WARPS); }
@@ -330,75 +343,62 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+  pdl_launch_dependents();   // the next kernel may be scheduled as SMs free up; it waits for our completion itself
 
-  if (warp == WARP_TMA) {
-    // ===================================== TMA producer =====================================
-    // Weights and scale/bias tiles do not depend on the previous kernel: the first stages' worth is requested
-    // BEFORE griddepcontrol.wait, so under programmatic dependent launch the HBM stream of this kernel starts while
-    // the previous kernel drains.  X (and the residual the epilogue adds to) is only touched after the wait.
-    const uint32_t tx_w = (uint32_t)W_STAGE_BYTES, tx_x = (uint32_t)(KPS * TN * 128);
+  if (warp == WARP_W) {
+    // ===================================== weight producer ==================================
+    // Weights and scale/bias tiles do not depend on the previous kernel: no griddepcontrol.wait here, so under
+    // programmatic dependent launch the HBM stream of this kernel starts while the previous kernel drains.
     int si = 0, ph = 0, sbi = 0, sbph = 0;
-    // pre-wait pass: at most S stages and at most NSB scale/bias groups (nothing to wait for on fresh barriers)
-    long long u_pre = u_begin;
-    {
-      int groups = 0;
-      for (long long u = u_begin; u < u_end && (u - u_begin) < S; ++u) {
-        const int st = (int)(u % p.num_st);
-        const bool gstart = (u == u_begin) || st == 0 || (st % SPG) == 0;
-        if (p.sb_tma && gstart && groups == NSB) break;
-        if (gstart) ++groups;
-        u_pre = u + 1;
-      }
-    }
-    for (int pass = 0; pass < 2; ++pass) {
-      // pass 0: weights (+ scale/bias tiles) of units [u_begin, u_pre); then wait for the previous grid;
-      // pass 1: X tiles of those units, then everything of the remaining units
-      si = 0; ph = 0;
-      int sbi_l = pass == 0 ? 0 : sbi, sbph_l = pass == 0 ? 0 : sbph;
-      const long long u_stop = pass == 0 ? u_pre : u_end;
-      for (long long u = u_begin; u < u_stop; ++u) {
-        const int tile = (int)(u / p.num_st), st = (int)(u % p.num_st);
-        const int pair = tile / p.tiles_m, tm = tile % p.tiles_m;
-        const int rowA0 = silu ? pair * 128 : pair * 256;
-        const int rowB0 = silu ? p.N / 2 + pair * 128 : pair * 256 + 128;
-        const bool early = u < u_pre;                       // weights of this unit were issued in pass 0
-        const bool do_w = pass == 0 || !early, do_x = pass == 1;
-        const bool gstart = (u == u_begin) || st == 0 || (st % SPG) == 0;
-        const uint32_t dst = in_ring + si * p.in_stage_bytes;
-        if (do_w && !early) mbar_wait(empty_in(si), ph ^ 1);
-        if (do_w && p.sb_tma && gstart) {
-          if (!early) mbar_wait(sb_empty(sbi_l), sbph_l ^ 1);
-          if (elect_one()) {
-            const uint32_t sdst = sb_ring + sbi_l * SB_SLOT_BYTES;
-            const int kb0 = (st / SPG) * 8;
-            mbar_arrive_expect_tx(sb_full(sbi_l), (uint32_t)SB_SLOT_BYTES);
-            tma_load_2d(sdst, &tm_s, kb0, rowA0, sb_full(sbi_l));
-            tma_load_2d(sdst + SB_TILE_BYTES, &tm_b, kb0, rowA0, sb_full(sbi_l));
-            tma_load_2d(sdst + 2 * SB_TILE_BYTES, &tm_s, kb0, rowB0, sb_full(sbi_l));
-            tma_load_2d(sdst + 3 * SB_TILE_BYTES, &tm_b, kb0, rowB0, sb_full(sbi_l));
-          }
-          __syncwarp();
-          if (++sbi_l == NSB) { sbi_l = 0; sbph_l ^= 1; }
-        }
+    for (long long u = u_begin; u < u_end; ++u) {
+      const int tile = (int)(u / p.num_st), st = (int)(u % p.num_st);
+      const int pair = tile / p.tiles_m;
+      const int rowA0 = silu ? pair * 128 : pair * 256;
+      const int rowB0 = silu ? p.N / 2 + pair * 128 : pair * 256 + 128;
+      if (p.sb_tma && (u == u_begin || (st % SPG) == 0)) {     // a new group of 8 k-blocks starts with this stage
+        mbar_wait(sb_empty(sbi), sbph ^ 1);
         if (elect_one()) {
-          if (do_w) {
-            mbar_arrive_expect_tx(full_w(si), tx_w);
-            tma_load_2d(dst, &tm_w, st * 128, rowA0, full_w(si));
-            tma_load_2d(dst + W_TILE_BYTES, &tm_w, st * 128, rowB0, full_w(si));
-          }
-          if (do_x) {
-            mbar_arrive_expect_tx(full_x(si), tx_x);
+          const uint32_t sdst = sb_ring + sbi * SB_SLOT_BYTES;
+          const int kb0 = (st / SPG) * 8;
+          mbar_arrive_expect_tx(sb_full(sbi), (uint32_t)SB_SLOT_BYTES);
+          tma_load_2d(sdst, &tm_s, kb0, rowA0, sb_full(sbi));
+          tma_load_2d(sdst + SB_TILE_BYTES, &tm_b, kb0, rowA0, sb_full(sbi));
+          tma_load_2d(sdst + 2 * SB_TILE_BYTES, &tm_s, kb0, rowB0, sb_full(sbi));
+          tma_load_2d(sdst + 3 * SB_TILE_BYTES, &tm_b, kb0, rowB0, sb_full(sbi));
+        }
+        __syncwarp();
+        if (++sbi == NSB) { sbi = 0; sbph ^= 1; }
+      }
+      mbar_wait(empty_w(si), ph ^ 1);
+      if (elect_one()) {
+        const uint32_t dst = w_ring + si * W_STAGE_BYTES;
+        mbar_arrive_expect_tx(full_w(si), (uint32_t)W_STAGE_BYTES);
+        tma_load_2d(dst, &tm_w, st * 128, rowA0, full_w(si));
+        tma_load_2d(dst + W_TILE_BYTES, &tm_w, st * 128, rowB0, full_w(si));
+      }
+      __syncwarp();
+      if (++si == S) { si = 0; ph ^= 1; }
+    }
+  } else if (warp == WARP_X) {
+    // ===================================== activation producer ==============================
+    pdl_wait();                                      // X is the previous kernel's output
+    uint32_t it = 0;
+    for (long long u = u_begin; u < u_end; ++u) {
+      const int tile = (int)(u / p.num_st), st = (int)(u % p.num_st);
+      const int tm = tile % p.tiles_m;
 #pragma unroll
-            for (int jj = 0; jj < KPS; ++jj)
-              tma_load_2d(dst + W_STAGE_BYTES + jj * TN * 128, &tm_x, (st * KPS + jj) * 64, tm * TN, full_x(si));
+      for (int jj = 0; jj < KPS; ++jj, ++it) {
+        const uint32_t xs = it & x_mask;
+        mbar_wait(empty_x(xs), ((it >> x_shift) & 1u) ^ 1u);
+        if (elect_one()) {
+          if (p.debug & 1) {
+            mbar_arrive(full_x(xs));
+          } else {
+            mbar_arrive_expect_tx(full_x(xs), x_slot_bytes);
+            tma_load_2d(x_ring + xs * x_slot_bytes, &tm_x, (st * KPS + jj) * 64, tm * TN, full_x(xs));
           }
         }
         __syncwarp();
-        if (++si == S) { si = 0; ph ^= 1; }
-      }
-      if (pass == 0) {
-        sbi = sbi_l; sbph = sbph_l;
-        pdl_wait();
       }
     }
   } else if (warp == WARP_MMA) {
@@ -407,7 +407,7 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     // bits 7/10, K-major A and B, N>>3 at bit 17, M>>4 at bit 24
     const uint32_t fmt = std::is_same<T, __nv_bfloat16>::value ? 1u : 0u;
     const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(TN >> 3) << 17) | ((128u >> 4) << 24);
-    int si = 0, ph = 0, seg = 0;
+    int seg = 0;
     uint32_t it = 0;
     for (long long u = u_begin; u < u_end; ++seg) {
       const int s0 = (int)(u % p.num_st);
@@ -418,33 +418,28 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
         tc_fence_after();
       }
       const uint32_t d0 = tmem_base + d_col(buf, 0), d1 = tmem_base + d_col(buf, 1);
-      for (int j = 0; j < ns; ++j) {
-        mbar_wait(full_x(si), (uint32_t)ph);
-        const uint32_t xs = in_ring + si * p.in_stage_bytes + W_STAGE_BYTES;
+      const int nkb = ns * KPS;
+      for (int j = 0; j < nkb; ++j, ++it) {
+        const uint32_t slot = it & (NSLOT - 1), xs = it & x_mask;
+        mbar_wait(full_x(xs), (it >> x_shift) & 1u);
+        mbar_wait(full_a(slot), (it >> 2) & 1u);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t xsm = x_ring + xs * x_slot_bytes;
+          if (!(p.debug & 2))
 #pragma unroll
-        for (int jj = 0; jj < KPS; ++jj, ++it) {
-          const uint32_t slot = it & (NSLOT - 1);
-          mbar_wait(full_a(slot), (it >> 2) & 1u);
-          tc_fence_after();
-          if (elect_one()) {
+          for (int blk = 0; blk < 2; ++blk) {
 #pragma unroll
-            for (int blk = 0; blk < 2; ++blk) {
-#pragma unroll
-              for (int k4 = 0; k4 < 4; ++k4) {
-                const uint32_t at = tmem_base + A_COL0 + slot * 64 + (uint32_t)(blk * 32 + k4 * 8);
-                umma_f16_ts(blk ? d1 : d0, at, make_desc_sw128(xs + jj * TN * 128 + k4 * 32), idesc,
-                            (j > 0 || jj > 0 || k4 > 0) ? 1u : 0u);
-              }
-            }
-            umma_commit(empty_a(slot));
-            if (jj == KPS - 1) {
-              umma_commit(empty_in(si));
-              if (j == ns - 1) umma_commit(accum_full(buf));
+            for (int k4 = 0; k4 < 4; ++k4) {
+              const uint32_t at = tmem_base + A_COL0 + slot * 64 + (uint32_t)(blk * 32 + k4 * 8);
+              umma_f16_ts(blk ? d1 : d0, at, make_desc_sw128(xsm + k4 * 32), idesc, (j > 0 || k4 > 0) ? 1u : 0u);
             }
           }
-          __syncwarp();
+          umma_commit(empty_a(slot));
+          umma_commit(empty_x(xs));
+          if (j == nkb - 1) umma_commit(accum_full(buf));
         }
-        if (++si == S) { si = 0; ph ^= 1; }
+        __syncwarp();
       }
       u += ns;
     }
@@ -465,20 +460,36 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     uint32_t it = (uint32_t)kpar;                    // global k-block counter of this thread (slot = it % 4)
     uint4 s8 = make_uint4(0u, 0u, 0u, 0u), b8 = s8;
 
-    // one k-block: 64 codes of row r -> 32 packed 16-bit pairs -> A ring slot
-    auto kblock = [&](uint32_t wsrc, int jj, uint32_t s2, uint32_t b2) {
-      uint32_t o[32];
-      uint4 pk[PKB / 16];
+    constexpr int CPK = PKB / 16;                    // 16-byte chunks of packed codes per k-block
+    constexpr int KPT = KPS / 2;                     // k-blocks per thread per stage
+    uint4 pk[KPT * CPK];
+    // wait for the stage's weights, pull this thread's codes into registers and hand the slot straight back to the
+    // producer: the HBM stream then only waits for LDS, not for the dequant math or the MMAs
+    auto fetch_stage = [&]() {
+      mbar_wait(full_w(si), (uint32_t)ph);
+      const uint32_t wsrc = w_ring + si * W_STAGE_BYTES + w_row_off;
 #pragma unroll
-      for (int c = 0; c < PKB / 16; ++c) pk[c] = lds128(wsrc + ((((uint32_t)(jj * (PKB / 16) + c)) ^ w_xor) << 4));
-      const uint32_t* pw = reinterpret_cast<const uint32_t*>(pk);
+      for (int j2 = 0; j2 < KPT; ++j2)
+#pragma unroll
+        for (int c = 0; c < CPK; ++c)
+          pk[j2 * CPK + c] = lds128(wsrc + ((((uint32_t)((kpar + 2 * j2) * CPK + c)) ^ w_xor) << 4));
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty_w(si));
+      if (++si == S) { si = 0; ph ^= 1; }
+    };
+    // one k-block: 64 codes of row r -> 32 packed 16-bit pairs -> A ring slot
+    auto kblock = [&](int j2, uint32_t s2, uint32_t b2) {
+      uint32_t o[32];
+      const uint32_t* pw = reinterpret_cast<const uint32_t*>(pk + j2 * CPK);
 #pragma unroll
       for (int c = 0; c < 8; ++c) dequant8<T, BITS, XPERM>(pw + c * (BITS / 4), s2, b2, o + 4 * c);
       const uint32_t slot = it & (NSLOT - 1);
       mbar_wait(empty_a(slot), ((it >> 2) & 1u) ^ 1u);
       tc_fence_after();
-      tmem_st32(a_dst + slot * 64, o);
-      tmem_st_wait();
+      if (!(p.debug & 8)) {
+        tmem_st32(a_dst + slot * 64, o);
+        tmem_st_wait();
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(full_a(slot));
@@ -499,23 +510,21 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
             if (lane == 0) mbar_arrive(sb_empty(sbi));
             if (++sbi == NSB) { sbi = 0; sbph ^= 1; }
           }
-          mbar_wait(full_w(si), (uint32_t)ph);
-          const uint32_t wsrc = in_ring + si * p.in_stage_bytes + w_row_off;
+          fetch_stage();
           if constexpr (KPS == 4) {
             // stage st holds k-blocks 4*(st&1) + {0..3} of the group: words 2*(st&1) + {0,1}
             const bool hi = (st & 1) != 0;
             const uint32_t sw0 = hi ? s8.z : s8.x, sw1 = hi ? s8.w : s8.y;
             const uint32_t bw0 = hi ? b8.z : b8.x, bw1 = hi ? b8.w : b8.y;
-            kblock(wsrc, kpar, prmt(sw0, 0u, half_sel), prmt(bw0, 0u, half_sel));
-            kblock(wsrc, kpar + 2, prmt(sw1, 0u, half_sel), prmt(bw1, 0u, half_sel));
+            kblock(0, prmt(sw0, 0u, half_sel), prmt(bw0, 0u, half_sel));
+            kblock(1, prmt(sw1, 0u, half_sel), prmt(bw1, 0u, half_sel));
           } else {
             // stage st holds k-blocks 2*(st&3) + {0,1}: word st&3
             const int wsel = st & 3;
             const uint32_t sw = wsel == 0 ? s8.x : (wsel == 1 ? s8.y : (wsel == 2 ? s8.z : s8.w));
             const uint32_t bw = wsel == 0 ? b8.x : (wsel == 1 ? b8.y : (wsel == 2 ? b8.z : b8.w));
-            kblock(wsrc, kpar, prmt(sw, 0u, half_sel), prmt(bw, 0u, half_sel));
+            kblock(0, prmt(sw, 0u, half_sel), prmt(bw, 0u, half_sel));
           }
-          if (++si == S) { si = 0; ph ^= 1; }
         }
       } else {
         // scale rows are not 16-byte multiples (K % 512 != 0, e.g. a TP shard): read them from global memory
@@ -534,11 +543,9 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
             sv[j2] = ok ? __ldg(sp + kb) : zero;
             bv[j2] = ok ? __ldg(bp + kb) : zero;
           }
-          mbar_wait(full_w(si), (uint32_t)ph);
-          const uint32_t wsrc = in_ring + si * p.in_stage_bytes + w_row_off;
+          fetch_stage();
 #pragma unroll
-          for (int j2 = 0; j2 < KPS / 2; ++j2) kblock(wsrc, kpar + 2 * j2, dup16(sv[j2]), dup16(bv[j2]));
-          if (++si == S) { si = 0; ph ^= 1; }
+          for (int j2 = 0; j2 < KPS / 2; ++j2) kblock(j2, dup16(sv[j2]), dup16(bv[j2]));
         }
       }
       u += ns;
@@ -597,7 +604,7 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
       mbar_wait(accum_full(buf), (uint32_t)((seg / NBUF) & 1));
       tc_fence_after();
       const uint32_t dA = lane_base + d_col(buf, 0), dB = lane_base + d_col(buf, 1);
-      for (int t = 0; t < TN; t += 8) {
+      for (int t = 0; t < TN && !(p.debug & 4); t += 8) {
         float v0[8], v1[8];
         tmem_ld8(dA + (uint32_t)t, v0);
         tmem_ld8(dB + (uint32_t)t, v1);
@@ -618,7 +625,7 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(accum_empty(buf));    // this D buffer may be overwritten by a later segment's MMAs
-      if (via_acc) {
+      if (via_acc && !(p.debug & 4)) {
         const int nseg = owner_of((long long)tile * p.num_st + p.num_st - 1, p.U, G) - c_first + 1;
         __threadfence();
         named_bar_sync(1, EPI_THREADS);
@@ -680,11 +687,12 @@ static EncodeTiledFn get_encode() {
 
 constexpr int SMEM_BUDGET = 227 * 1024;
 constexpr int SMEM_FIXED = 1024 /*align*/ + NSB * SB_SLOT_BYTES + 512 /*barriers*/;
+static_assert(8 * (4 * MAX_STAGES + 2 * NSLOT + 2 * NSB + 4) + 8 <= 512, "barrier block overflows its slot");
 constexpr int MIN_TC_M = 5;        // below this the CUDA-core GEMV wins (weights read once either way)
 constexpr int MIN_UNITS_PER_CTA = 2;
 
 struct TcPlan {
-  int TN, tiles_m, pairs, grid, in_stages, in_stage_bytes, smem_bytes;
+  int TN, tiles_m, pairs, grid, w_stages, x_slots, smem_bytes;
   long long U;
 };
 
@@ -700,11 +708,13 @@ static TcPlan make_plan(int64_t M, int64_t N, int64_t K, int bits, int epi) {
   long long g = (pl.U + MIN_UNITS_PER_CTA - 1) / MIN_UNITS_PER_CTA;
   const int sms = sm_count();
   pl.grid = (int)(g > sms ? sms : (g < 1 ? 1 : g));
-  pl.in_stage_bytes = 2 * W_TILE_BYTES + kps * tn * 128;
-  int st = (SMEM_BUDGET - SMEM_FIXED) / pl.in_stage_bytes;
+  // X ring: one [TN x 64] tile per k-block, 8 slots (4 at TN = 128) -- about 1 us of MMA work in flight, enough to
+  // cover the L2 latency of the tile loads; the weight ring gets the rest of shared memory
+  pl.x_slots = tn * 128 * 8 <= X_RING_BYTES ? 8 : 4;
+  int st = (SMEM_BUDGET - SMEM_FIXED - pl.x_slots * tn * 128) / W_STAGE_BYTES;
   if (st > MAX_STAGES) st = MAX_STAGES;
-  pl.in_stages = st;
-  pl.smem_bytes = SMEM_FIXED + st * pl.in_stage_bytes;
+  pl.w_stages = st;
+  pl.smem_bytes = SMEM_FIXED + pl.x_slots * tn * 128 + st * W_STAGE_BYTES;
   return pl;
 }
 
@@ -777,7 +787,7 @@ int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b
   EncodeTiledFn enc = get_encode();
   B200P_REQUIRE(enc != nullptr, B200P_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
   TcPlan pl = make_plan(M, N, K, bits, epi);
-  B200P_REQUIRE(pl.in_stages >= 2, B200P_ERR_ARG, "shared memory too small for the tensor path");
+  B200P_REQUIRE(pl.w_stages >= 2, B200P_ERR_ARG, "shared memory too small for the tensor path");
   const bool x_perm = (flags & B200P_X_PERM8) != 0, y_perm = (flags & B200P_Y_PERM8) != 0;
   B200P_REQUIRE(!x_perm || bits == 4, B200P_ERR_ARG, "B200P_X_PERM8 is the 4-bit activation layout");
   B200P_REQUIRE(!y_perm || epi == B200P_EPI_STORE || epi == B200P_EPI_SILU_MUL, B200P_ERR_ARG,
@@ -814,7 +824,8 @@ int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b
   p.num_kb = num_kb; p.pairs = pl.pairs; p.tiles_m = pl.tiles_m; p.U = pl.U;
   p.num_st = (p.num_kb + (bits == 4 ? 4 : 2) - 1) / (bits == 4 ? 4 : 2);
   p.sb_tma = sb_tma ? 1 : 0;
-  p.in_stages = pl.in_stages; p.in_stage_bytes = pl.in_stage_bytes;
+  p.w_stages = pl.w_stages; p.x_slots = pl.x_slots;
+  { const char* d = getenv("B200P_TC_DEBUG"); p.debug = d ? atoi(d) : 0; }
   if (dtype == B200P_F16) {
     if (bits == 8) return launch_tc<__half, 8, false>(tms, p, pl, st);
     return x_perm ? launch_tc<__half, 4, true>(tms, p, pl, st) : launch_tc<__half, 4, false>(tms, p, pl, st);
