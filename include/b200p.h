@@ -108,12 +108,21 @@ int b200p_rmsnorm(const float* x, const void* w, void* y, int64_t M, int64_t H, 
  * qkv `dtype` [B*L, (Hq+2*Hkv)*D] (q heads, then k heads, then v heads);
  * q_out `dtype` [B, L, Hq, D]; kcache/vcache `dtype` [B, Hkv, Tcap, D];
  * lengths int32 [B] = tokens already in the cache per row (position of token l is lengths[b]+l);
- * q_norm_w / k_norm_w `dtype` [D] or NULL.  Does NOT advance lengths. */
-int b200p_rope_kv_append(const void* qkv, void* q_out, void* kcache, void* vcache,
+ * q_norm_w / k_norm_w `dtype` [D] or NULL.  Does NOT advance lengths.
+ * qkv_f32 = 1: qkv is instead the float accumulation buffer of the fused projection (b200p_qmm with
+ * B200P_EPI_ADD_RESIDUAL into a zeroed buffer); values are rounded to `dtype` on read and the buffer is re-zeroed. */
+int b200p_rope_kv_append(void* qkv, void* q_out, void* kcache, void* vcache,
                          const int32_t* lengths, const void* q_norm_w, const void* k_norm_w,
                          int64_t B, int64_t L, int Hq, int Hkv, int D, int64_t Tcap,
                          float rope_base, float rope_scale, float norm_eps, int dtype,
-                         void* stream);
+                         int qkv_f32, void* stream);
+/* nn.silu(gate) * up                                                  [models/llama.py:165]
+ * gu float [M, 2*I] (ldg floats between rows): columns [0,I) = gate_proj, [I,2I) = up_proj sums, as accumulated by
+ * b200p_qmm(..., B200P_EPI_ADD_RESIDUAL) of the fused gate|up matrix into a ZEROED buffer (stream-K partial tiles
+ * then need no second pass); out `dtype` [M, I] (ldo), optionally PERM8 (flags = B200P_OUT_PERM8).
+ * The kernel re-zeroes gu behind its read, so the buffer is ready for the next step. */
+int b200p_silu_mul(float* gu, void* out, int64_t M, int64_t I, int64_t ldg, int64_t ldo, int dtype, int flags,
+                   void* stream);
 /* lengths[b] += delta (device side, keeps the decode graph replayable) */
 int b200p_advance_lengths(int32_t* lengths, int64_t B, int32_t delta, void* stream);
 

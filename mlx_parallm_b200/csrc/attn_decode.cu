@@ -309,11 +309,11 @@ static int launch_attn_decode(const void* q, const void* kc, const void* vc, con
   // the split count depends on capacity, not on the (device-side) lengths, so a captured graph stays valid
   const int splits = pick_splits(B, Hkv, Tcap);
   dim3 grid((unsigned)splits, (unsigned)Hkv, (unsigned)B);
-  kern<<<grid, AD_THREADS, AD_SMEM, st>>>((const T*)q, (const T*)kc, (const T*)vc, lengths, (T*)out, (float*)ws, Hq, Hkv,
+  launch_pdl(kern, grid, AD_THREADS, AD_SMEM, st, (const T*)q, (const T*)kc, (const T*)vc, lengths, (T*)out, (float*)ws, Hq, Hkv,
                                           Tcap, scale * 1.4426950408889634f, splits, out_perm);
   B200P_LAUNCH_CHECK("attn_decode_kernel");
   if (splits > 1) {
-    attn_reduce_kernel<T><<<(unsigned)(B * Hq), AD_D, 0, st>>>((const float*)ws, (T*)out, splits, out_perm);
+    launch_pdl(attn_reduce_kernel<T>, (unsigned)(B * Hq), AD_D, 0, st, (const float*)ws, (T*)out, splits, out_perm);
     B200P_LAUNCH_CHECK("attn_reduce_kernel");
   }
   return B200P_OK;

@@ -101,7 +101,7 @@ int attn_generic_launch(const void* q, const void* kc, const void* vc, const int
   B200P_REQUIRE(nblk < (1ll << 31), B200P_ERR_ARG, "grid too large");
   if (nblk == 0) return B200P_OK;
 #define GO(E_)                                                                                              \
-  B200P_DISPATCH_DTYPE(dtype, T, (attn_generic_kernel<T, E_><<<(unsigned)nblk, 128, 0, st>>>(                \
+  B200P_DISPATCH_DTYPE(dtype, T, (launch_pdl(attn_generic_kernel<T, E_>, (unsigned)nblk, 128, 0, st,                 \
                                      (const T*)q, (const T*)kc, (const T*)vc, lengths, (T*)out, (int)L, Hq, \
                                      Hkv, D, Tcap, scale, out_perm)))
   switch (epl) {

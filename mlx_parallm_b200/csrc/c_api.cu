@@ -1,5 +1,6 @@
 // C-ABI glue: error plumbing, device checks and the path dispatchers of b200p_qmm / b200p_attn.
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -38,7 +39,8 @@ size_t attn_decode_workspace_bytes(int64_t B, int64_t L, int Hq, int D);
 
 static int g_qmm_path = 0;   // 0 auto, 1 gemv, 2 tensor
 static int g_attn_path = 0;  // 0 auto, 1 generic, 2 tensor
-static int g_pdl = 1;
+// 0 off, 1 every kernel, 2 only the tensor-path GEMM (B200P_PDL overrides the default at load time)
+static int g_pdl = [] { const char* e = getenv("B200P_PDL"); return e ? atoi(e) : 2; }();
 static int g_sm_count = -1;
 static int g_cc_major = -1;
 
@@ -55,7 +57,8 @@ static int query_device() {
   return B200P_OK;
 }
 
-bool pdl_enabled() { return g_pdl != 0; }
+bool pdl_enabled() { return g_pdl == 1; }
+bool pdl_enabled_gemm() { return g_pdl != 0; }
 
 int sm_count() {
   query_device();
@@ -83,7 +86,7 @@ extern "C" int b200p_sm_count(void) {
 }
 
 extern "C" int b200p_set_pdl(int enabled) {
-  g_pdl = enabled ? 1 : 0;
+  g_pdl = enabled;
   return B200P_OK;
 }
 

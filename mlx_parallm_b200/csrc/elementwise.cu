@@ -1,5 +1,7 @@
 // dequantize / embedding gather / RMSNorm / RoPE + KV append / argmax.
 // All HBM- or latency-bound byte work: one pass, 128-bit accesses, no tensor cores.
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace b200p {
@@ -30,6 +32,7 @@ dequant_kernel(const uint32_t* __restrict__ w, const T* __restrict__ scales,
   const int64_t words_per_row = K / PER;
   int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= n_rows * words_per_row) return;
+  pdl_wait();   // `rows` (token ids) and `out` belong to the previous kernels
   int64_t r = idx / words_per_row;
   int64_t wi = idx - r * words_per_row;
   int64_t src = rows ? (int64_t)rows[r] : r;
@@ -67,7 +70,7 @@ static int launch_dequant(const uint32_t* w, const void* scales, const void* bia
   if (total == 0) return B200P_OK;
   dim3 grid((unsigned)((total + 255) / 256)), block(256);
 #define L(B_, M_)                                                                                   \
-  dequant_kernel<T, B_, M_, OUT><<<grid, block, 0, st>>>(w, (const T*)scales, (const T*)biases,      \
+  launch_pdl(dequant_kernel<T, B_, M_, OUT>, grid, block, 0, st, w, (const T*)scales, (const T*)biases,      \
                                                          (OUT*)out, rows, n_rows, V, K, gs)
   if (bits == 4) {
     if (mode == 0) L(4, 0); else if (mode == 1) L(4, 1); else L(4, 2);
@@ -207,7 +210,7 @@ extern "C" int b200p_rmsnorm(const float* x, const void* w, void* y, int64_t M, 
   B200P_REQUIRE(aligned(x, 16) && aligned(y, 16) && H % 4 == 0, B200P_ERR_ALIGN,
                 "rmsnorm needs 16-byte aligned rows (H %% 4 == 0)");
   if (M == 0) return B200P_OK;
-  B200P_DISPATCH_DTYPE(dtype, T, (rmsnorm_kernel<T><<<(unsigned)M, 256, 0, (cudaStream_t)stream>>>(
+  B200P_DISPATCH_DTYPE(dtype, T, (launch_pdl(rmsnorm_kernel<T>, (unsigned)M, 256, 0, (cudaStream_t)stream, 
                                      x, (const T*)w, (T*)y, H, eps, perm)));
   B200P_LAUNCH_CHECK("rmsnorm_kernel");
   return B200P_OK;
@@ -219,8 +222,11 @@ extern "C" int b200p_rmsnorm(const float* x, const void* w, void* y, int64_t M, 
 // ------------------------------------------------------------------------------------------------
 namespace b200p {
 
-template <typename T>
-__global__ void rope_kv_append_kernel(const T* __restrict__ qkv, T* __restrict__ q_out, T* __restrict__ kc,
+// TIN = T: qkv is the projection's 16-bit output.  TIN = float: qkv is the fp32 split-K accumulation buffer of the
+// projection (b200p_qmm with ADD_RESIDUAL into a zeroed buffer): values are rounded to T first (the rounding the
+// reference's projection output has) and the buffer is re-zeroed behind the read, ready for the next step.
+template <typename T, typename TIN>
+__global__ void rope_kv_append_kernel(TIN* __restrict__ qkv, T* __restrict__ q_out, T* __restrict__ kc,
                                       T* __restrict__ vc, const int32_t* __restrict__ lengths,
                                       const T* __restrict__ qn_w, const T* __restrict__ kn_w, int L, int Hq,
                                       int Hkv, int D, int64_t Tcap, float log2_base, float rope_scale,
@@ -233,17 +239,29 @@ __global__ void rope_kv_append_kernel(const T* __restrict__ qkv, T* __restrict__
   const int half = D >> 1;
   const int i = threadIdx.x;
   const int64_t row_stride = (int64_t)(Hq + 2 * Hkv) * D;
-  const T* src = qkv + (int64_t)tok * row_stride + (int64_t)head * D;
+  TIN* src = qkv + (int64_t)tok * row_stride + (int64_t)head * D;
   const int pos_i = lengths[b] + l;
   const bool act = i < half;  // block is padded to whole warps
-  float x1 = act ? Tr<T>::to_f(src[i]) : 0.f;
-  float x2 = act ? Tr<T>::to_f(src[i + half]) : 0.f;
+  constexpr bool F32IN = sizeof(TIN) != sizeof(T) || std::is_same<TIN, float>::value;
+  float x1 = 0.f, x2 = 0.f;
+  if (act) {
+    if constexpr (std::is_same<TIN, float>::value && !std::is_same<T, float>::value) {
+      x1 = Tr<T>::to_f(Tr<T>::from_f(src[i]));
+      x2 = Tr<T>::to_f(Tr<T>::from_f(src[i + half]));
+      src[i] = 0.f;
+      src[i + half] = 0.f;
+    } else {
+      x1 = Tr<TIN>::to_f(src[i]);
+      x2 = Tr<TIN>::to_f(src[i + half]);
+    }
+  }
+  (void)F32IN;
   if (head >= Hq + Hkv) {  // V head: plain append
     int hv = head - Hq - Hkv;
     if (pos_i < Tcap && act) {
       T* dst = vc + (((int64_t)b * Hkv + hv) * Tcap + pos_i) * D;
-      dst[i] = src[i];
-      dst[i + half] = src[i + half];
+      dst[i] = Tr<T>::from_f(x1);
+      dst[i + half] = Tr<T>::from_f(x2);
     }
     return;
   }
@@ -277,36 +295,90 @@ __global__ void rope_kv_append_kernel(const T* __restrict__ qkv, T* __restrict__
   }
 }
 
+// act[m, i] = silu(gu[m, i]) * gu[m, I + i] from the fp32 accumulation buffer of the fused gate|up projection
+// (models/llama.py:165); the buffer is re-zeroed behind the read.  One thread per aligned group of 8 outputs.
+template <typename T>
+__global__ void __launch_bounds__(256)
+silu_mul_kernel(float* __restrict__ gu, T* __restrict__ out, int64_t M, int64_t I, int64_t ldg, int64_t ldo, int perm) {
+  pdl_wait();
+  const int64_t groups = I / 8;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= M * groups) return;
+  const int64_t m = idx / groups, g8 = idx - m * groups;
+  float4* gp = reinterpret_cast<float4*>(gu + m * ldg + g8 * 8);
+  float4* up = reinterpret_cast<float4*>(gu + m * ldg + I + g8 * 8);
+  const float4 g0 = gp[0], g1 = gp[1], u0 = up[0], u1 = up[1];
+  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+  gp[0] = z; gp[1] = z; up[0] = z; up[1] = z;
+  pdl_launch_dependents();
+  const float gv[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+  const float uv[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+  __align__(16) T o[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float a = gv[j] / (1.0f + __expf(-gv[j])) * uv[j];
+    o[perm ? perm8_pos(j) : j] = Tr<T>::from_f(a);
+  }
+  *reinterpret_cast<uint4*>(out + m * ldo + g8 * 8) = *reinterpret_cast<uint4*>(o);
+}
+
 __global__ void advance_lengths_kernel(int32_t* lengths, int64_t B, int32_t delta) {
+  pdl_wait();
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < B) lengths[i] += delta;
 }
 
 }  // namespace b200p
 
-extern "C" int b200p_rope_kv_append(const void* qkv, void* q_out, void* kcache, void* vcache,
+extern "C" int b200p_rope_kv_append(void* qkv, void* q_out, void* kcache, void* vcache,
                                     const int32_t* lengths, const void* q_norm_w, const void* k_norm_w,
                                     int64_t B, int64_t L, int Hq, int Hkv, int D, int64_t Tcap,
                                     float rope_base, float rope_scale, float norm_eps, int dtype,
-                                    void* stream) {
+                                    int qkv_f32, void* stream) {
   B200P_REQUIRE(qkv && q_out && kcache && vcache && lengths, B200P_ERR_ARG, "null pointer");
+  B200P_REQUIRE(!qkv_f32 || dtype != B200P_F32, B200P_ERR_ARG, "qkv_f32 is the accumulation-buffer input of 16-bit models");
   B200P_REQUIRE(D >= 2 && D % 2 == 0 && D <= 2048, B200P_ERR_ARG, "head_dim %d unsupported", D);
   B200P_REQUIRE(Hq > 0 && Hkv > 0 && Hq % Hkv == 0, B200P_ERR_ARG, "bad head counts %d/%d", Hq, Hkv);
   B200P_REQUIRE(B * L < (1ll << 31) && Hq + 2 * Hkv < 65536, B200P_ERR_ARG, "grid too large");
   if (B * L == 0) return B200P_OK;
   dim3 grid((unsigned)(B * L), (unsigned)(Hq + 2 * Hkv)), block(((D / 2 + 31) / 32) * 32);
-  B200P_DISPATCH_DTYPE(dtype, T, (rope_kv_append_kernel<T><<<grid, block, 0, (cudaStream_t)stream>>>(
-                                     (const T*)qkv, (T*)q_out, (T*)kcache, (T*)vcache, lengths,
-                                     (const T*)q_norm_w, (const T*)k_norm_w, (int)L, Hq, Hkv, D, Tcap,
-                                     log2f(rope_base), rope_scale, norm_eps)));
+  if (qkv_f32) {
+    B200P_DISPATCH_DTYPE(dtype, T, (launch_pdl(rope_kv_append_kernel<T, float>, grid, block, 0, (cudaStream_t)stream, 
+                                       (float*)qkv, (T*)q_out, (T*)kcache, (T*)vcache, lengths,
+                                       (const T*)q_norm_w, (const T*)k_norm_w, (int)L, Hq, Hkv, D, Tcap,
+                                       log2f(rope_base), rope_scale, norm_eps)));
+  } else {
+    B200P_DISPATCH_DTYPE(dtype, T, (launch_pdl(rope_kv_append_kernel<T, T>, grid, block, 0, (cudaStream_t)stream, 
+                                       (T*)qkv, (T*)q_out, (T*)kcache, (T*)vcache, lengths,
+                                       (const T*)q_norm_w, (const T*)k_norm_w, (int)L, Hq, Hkv, D, Tcap,
+                                       log2f(rope_base), rope_scale, norm_eps)));
+  }
   B200P_LAUNCH_CHECK("rope_kv_append_kernel");
+  return B200P_OK;
+}
+
+extern "C" int b200p_silu_mul(float* gu, void* out, int64_t M, int64_t I, int64_t ldg, int64_t ldo, int dtype, int flags,
+                              void* stream) {
+  B200P_REQUIRE(gu && out, B200P_ERR_ARG, "null pointer");
+  B200P_REQUIRE(dtype == B200P_F16 || dtype == B200P_BF16, B200P_ERR_ARG, "silu_mul writes a 16-bit activation");
+  B200P_REQUIRE((flags & ~B200P_OUT_PERM8) == 0, B200P_ERR_ARG, "unknown flags 0x%x", flags);
+  B200P_REQUIRE(I % 8 == 0 && ldg % 4 == 0 && ldo % 8 == 0 && ldg >= 2 * I && ldo >= I && aligned(gu, 16) && aligned(out, 16),
+                B200P_ERR_ALIGN, "silu_mul needs I %% 8 == 0 and 16-byte aligned rows");
+  if (M * I == 0) return B200P_OK;
+  const int64_t n = M * (I / 8);
+  const int perm = (flags & B200P_OUT_PERM8) ? 1 : 0;
+  if (dtype == B200P_F16)
+    launch_pdl(silu_mul_kernel<__half>, (unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream, gu, (__half*)out, M, I, ldg, ldo, perm);
+  else
+    launch_pdl(silu_mul_kernel<__nv_bfloat16>, (unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream, gu, (__nv_bfloat16*)out, M, I, ldg, ldo, perm);
+  B200P_LAUNCH_CHECK("silu_mul_kernel");
   return B200P_OK;
 }
 
 extern "C" int b200p_advance_lengths(int32_t* lengths, int64_t B, int32_t delta, void* stream) {
   B200P_REQUIRE(lengths, B200P_ERR_ARG, "null lengths");
   if (B == 0) return B200P_OK;
-  advance_lengths_kernel<<<(unsigned)((B + 255) / 256), 256, 0, (cudaStream_t)stream>>>(lengths, B, delta);
+  launch_pdl(advance_lengths_kernel, (unsigned)((B + 255) / 256), 256, 0, (cudaStream_t)stream, lengths, B, delta);
   B200P_LAUNCH_CHECK("advance_lengths_kernel");
   return B200P_OK;
 }

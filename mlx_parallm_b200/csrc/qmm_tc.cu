@@ -53,7 +53,7 @@
 namespace b200p {
 
 int sm_count();
-bool pdl_enabled();
+bool pdl_enabled_gemm();
 
 // ------------------------------------------------------------------------------------------------ PTX
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -136,7 +136,36 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, float (&v)[8]) {
 #pragma unroll
   for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[i]);
 }
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
+  uint32_t r[16];
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+                 "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+               : "r"(taddr));
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
+template <typename T> __device__ __forceinline__ void sts16(uint32_t addr, T v) {
+  asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"(*reinterpret_cast<uint16_t*>(&v)) : "memory");
+}
+// generic-proxy writes to shared memory -> visible to the async proxy (TMA store / reduce reads them)
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+// shared-memory tile -> global tensor (rows / columns outside the tensor are clipped by the TMA unit)
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, int c0, int c1, uint32_t src) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];" ::"l"(map), "r"(c0), "r"(c1), "r"(src)
+               : "memory");
+}
+// the same with an element-wise atomic add performed at the destination (fp32 tensor map)
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* map, int c0, int c1, uint32_t src) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%1, %2}], [%3];" ::"l"(map), "r"(c0),
+               "r"(c1), "r"(src)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 // each lane writes 32 consecutive 32-bit columns of ITS TMEM lane (= 64 consecutive 16-bit k of one A row)
 __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
   asm volatile(
@@ -265,6 +294,9 @@ constexpr int SB_TILE_BYTES = 128 * 16;          // 128 rows x 8 k-blocks x 2 by
 constexpr int SB_SLOT_BYTES = 4 * SB_TILE_BYTES; // block 0 scales, block 0 biases, block 1 scales, block 1 biases
 constexpr int MAX_STAGES = 8;                    // weight ring stages / X ring slots (upper bounds)
 constexpr int X_RING_BYTES = 64 * 1024;
+constexpr int EPI_TOK = 16;                      // tokens per epilogue staging tile
+constexpr int EPI_NBUF = 2;
+constexpr int EPI_BUF_BYTES = EPI_TOK * 128 * 4; // [16 tokens x 128 rows] fp32 (16-bit tiles use the first half)
 
 struct TcParams {
   const void* scales;
@@ -283,7 +315,7 @@ struct TcParams {
   int sb_tma;          // 1: scale/bias tiles come through TMA (num_kb % 8 == 0)
   int w_stages;        // weight ring depth
   int x_slots;         // X ring depth (4 or 8; one slot = the [TN x 64] tile of one k-block)
-  int debug;           // B200P_TC_DEBUG (profiling only): 1 no X loads, 2 no MMA issue, 4 no epilogue stores, 8 no A stores
+  int debug;           // B200P_TC_DEBUG (profiling only): 1 no X loads, 2 no MMA issue, 4 no epilogue, 8 no A stores, 16 no TMA stores
 };
 
 // CTA that owns linear unit x when U units are dealt to G CTAs as [c*U/G, (c+1)*U/G)
@@ -292,7 +324,8 @@ __device__ __forceinline__ int owner_of(long long x, long long U, int G) { retur
 template <typename T, int BITS, bool XPERM>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x,
-              const __grid_constant__ CUtensorMap tm_s, const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
+              const __grid_constant__ CUtensorMap tm_s, const __grid_constant__ CUtensorMap tm_b,
+              const __grid_constant__ CUtensorMap tm_y, const __grid_constant__ CUtensorMap tm_acc, const TcParams p) {
   constexpr int PKB = 64 * BITS / 8;            // packed bytes per row per k-block
   constexpr int KPS = 128 / PKB;                // k-blocks per stage (a stage row is one 128-byte line)
   constexpr int SPG = 8 / KPS;                  // stages per scale/bias group of 8 k-blocks
@@ -305,7 +338,8 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
   const uint32_t x_mask = (uint32_t)(p.x_slots - 1);
   const int x_shift = p.x_slots == 8 ? 3 : 2;
   const uint32_t sb_ring = x_ring + p.x_slots * x_slot_bytes;
-  const uint32_t bar_base = sb_ring + NSB * SB_SLOT_BYTES;
+  const uint32_t epi_ring = sb_ring + NSB * SB_SLOT_BYTES;
+  const uint32_t bar_base = epi_ring + EPI_NBUF * EPI_BUF_BYTES;
   const int NBUF = TN > 64 ? 1 : 2;              // D buffers: buffer d, block b at columns d*128 + b*64 (TN <= 64) / b*128
   auto full_w = [&](int s) { return bar_base + 8u * s; };
   auto empty_w = [&](int s) { return bar_base + 8u * (MAX_STAGES + s); };
@@ -336,6 +370,8 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     tma_prefetch_desc(&tm_w);
     tma_prefetch_desc(&tm_x);
     if (p.sb_tma) { tma_prefetch_desc(&tm_s); tma_prefetch_desc(&tm_b); }
+    tma_prefetch_desc(&tm_y);
+    tma_prefetch_desc(&tm_acc);
   }
   if (warp == WARP_MMA) tmem_alloc(tmem_slot, TMEM_COLS);
   tc_fence_before();
@@ -360,11 +396,15 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
         if (elect_one()) {
           const uint32_t sdst = sb_ring + sbi * SB_SLOT_BYTES;
           const int kb0 = (st / SPG) * 8;
-          mbar_arrive_expect_tx(sb_full(sbi), (uint32_t)SB_SLOT_BYTES);
-          tma_load_2d(sdst, &tm_s, kb0, rowA0, sb_full(sbi));
-          tma_load_2d(sdst + SB_TILE_BYTES, &tm_b, kb0, rowA0, sb_full(sbi));
-          tma_load_2d(sdst + 2 * SB_TILE_BYTES, &tm_s, kb0, rowB0, sb_full(sbi));
-          tma_load_2d(sdst + 3 * SB_TILE_BYTES, &tm_b, kb0, rowB0, sb_full(sbi));
+          if (p.debug & 32) {
+            mbar_arrive(sb_full(sbi));
+          } else {
+            mbar_arrive_expect_tx(sb_full(sbi), (uint32_t)SB_SLOT_BYTES);
+            tma_load_2d(sdst, &tm_s, kb0, rowA0, sb_full(sbi));
+            tma_load_2d(sdst + SB_TILE_BYTES, &tm_b, kb0, rowA0, sb_full(sbi));
+            tma_load_2d(sdst + 2 * SB_TILE_BYTES, &tm_s, kb0, rowB0, sb_full(sbi));
+            tma_load_2d(sdst + 3 * SB_TILE_BYTES, &tm_b, kb0, rowB0, sb_full(sbi));
+          }
         }
         __syncwarp();
         if (++sbi == NSB) { sbi = 0; sbph ^= 1; }
@@ -552,12 +592,36 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     }
   } else {
     // ===================================== epilogue warps ===================================
+    // TMEM -> registers -> a [16 tokens x 128 rows] staging tile in shared memory (the transpose is free: thread = row
+    // writes column r of every token line, bank = lane) -> ONE TMA tensor store / reduce-add per tile.  Stream-K
+    // partial tiles are summed by the TMA unit (cp.reduce.async.bulk .add.f32) instead of 16K scalar atomics per
+    // segment, which kept the LSU busy for ~10 us.
     const int e = warp - DQ_WARPS;                     // == warp % 4: the TMEM lane quarter this warp may read
     const int r = e * 32 + lane;                     // output row (weight row) within the 128-row block
     const uint32_t lane_base = tmem_base + ((uint32_t)(e * 32) << 16);
     const int et = threadIdx.x - DQ_THREADS;         // 0..127
+    const bool out16 = p.epi == B200P_EPI_STORE || p.epi == B200P_EPI_SILU_MUL;
+    const int rp = p.y_perm ? perm8_pos(r) : r;      // column inside a 16-bit staging line
     pdl_wait();                                      // y (residual) belongs to the previous kernels
     int seg = 0;
+    uint32_t nchunk = 0;
+    // claim staging buffer (nchunk & 1): the bulk group that last read it must be done with shared memory
+    auto stage_begin = [&]() -> uint32_t {
+      if (et == 0) bulk_wait_read<EPI_NBUF - 1>();
+      named_bar_sync(1, EPI_THREADS);
+      return epi_ring + (nchunk & (EPI_NBUF - 1)) * EPI_BUF_BYTES;
+    };
+    // the tile is written: hand it to the TMA unit
+    auto stage_end = [&](uint32_t buf, const CUtensorMap* tm, int cx, int cy, bool reduce) {
+      fence_proxy_async_smem();
+      named_bar_sync(2, EPI_THREADS);
+      if (et == 0 && !(p.debug & 16)) {
+        if (reduce) tma_reduce_add_2d(tm, cx, cy, buf);
+        else tma_store_2d(tm, cx, cy, buf);
+        bulk_commit();
+      }
+      ++nchunk;
+    };
     for (long long u = u_begin; u < u_end; ++seg) {
       const int tile = (int)(u / p.num_st), s0 = (int)(u % p.num_st);
       const int ns = (int)min((long long)(p.num_st - s0), u_end - u);
@@ -566,59 +630,49 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
       const int rowB0 = silu ? p.N / 2 + pair * 128 : pair * 256 + 128;
       const int tok0 = tm * TN;
       const int buf = NBUF == 2 ? (seg & 1) : 0;
-      const int n0 = rowA0 + r, n1 = rowB0 + r;        // output columns of this thread (block 0 / block 1)
-      const int c0 = p.y_perm ? perm8_pos(n0) : n0, c1 = p.y_perm ? perm8_pos(n1) : n1;
       const bool full = (s0 == 0 && ns == p.num_st);
-      // a tile shared by several CTAs is summed with L2 atomics: straight into y for ADD_RESIDUAL, else into the
-      // fp32 accumulator owned by the tile's first CTA; the last CTA to arrive applies the epilogue and re-zeroes it
+      // a tile shared by several CTAs is summed in L2: straight into y for ADD_RESIDUAL, else into the fp32
+      // accumulator owned by the tile's first CTA; the last CTA to arrive applies the epilogue and re-zeroes it
       const bool via_acc = !full && p.epi != B200P_EPI_ADD_RESIDUAL;
       const int c_first = via_acc ? owner_of((long long)tile * p.num_st, p.U, G) : cta;
-      float* acc = p.ws_acc + (int64_t)c_first * (2 * (int64_t)TN * 128);
-
-      auto finish = [&](int t, float a0, float a1) {   // final epilogue for token t (tile-local), rows n0 / n1
-        const int tok = tok0 + t;
-        if (tok >= p.M_tok) return;
-        if (p.epi == B200P_EPI_STORE) {
-          T* y = reinterpret_cast<T*>(p.y) + (int64_t)tok * p.ldy;
-          if (n0 < p.N) y[c0] = Tr<T>::from_f(a0);
-          if (n1 < p.N) y[c1] = Tr<T>::from_f(a1);
-        } else if (p.epi == B200P_EPI_STORE_F32) {
-          float* y = reinterpret_cast<float*>(p.y) + (int64_t)tok * p.ldy;
-          if (n0 < p.N) y[n0] = a0;
-          if (n1 < p.N) y[n1] = a1;
-        } else if (p.epi == B200P_EPI_ADD_RESIDUAL) {
-          float* y = reinterpret_cast<float*>(p.y) + (int64_t)tok * p.ldy;
-          if (full) {
-            if (n0 < p.N) y[n0] += a0;
-            if (n1 < p.N) y[n1] += a1;
-          } else {
-            if (n0 < p.N) atomicAdd(y + n0, a0);
-            if (n1 < p.N) atomicAdd(y + n1, a1);
-          }
-        } else {
-          T* y = reinterpret_cast<T*>(p.y) + (int64_t)tok * p.ldy;
-          if (n0 < p.N / 2) y[c0] = Tr<T>::from_f(silu_tc(a0) * a1);
-        }
-      };
+      const int acc_row0 = c_first * 2 * TN;           // first line of this boundary's accumulator in tm_acc
 
       mbar_wait(accum_full(buf), (uint32_t)((seg / NBUF) & 1));
       tc_fence_after();
       const uint32_t dA = lane_base + d_col(buf, 0), dB = lane_base + d_col(buf, 1);
-      for (int t = 0; t < TN && !(p.debug & 4); t += 8) {
-        float v0[8], v1[8];
-        tmem_ld8(dA + (uint32_t)t, v0);
-        tmem_ld8(dB + (uint32_t)t, v1);
-        tmem_ld_wait();
-        if (!via_acc) {
+      for (int t0 = 0; t0 < TN && !(p.debug & 4); t0 += EPI_TOK) {
+        if (via_acc || !out16) {
+          // fp32 tiles, one per block: reduce-add (split tile / residual) or plain store (whole STORE_F32 tile)
 #pragma unroll
-          for (int j = 0; j < 8; ++j) finish(t + j, v0[j], v1[j]);
+          for (int blk = 0; blk < 2; ++blk) {
+            float v[EPI_TOK];
+            tmem_ld16((blk ? dB : dA) + (uint32_t)t0, v);
+            tmem_ld_wait();
+            const uint32_t sb = stage_begin();
+#pragma unroll
+            for (int j = 0; j < EPI_TOK; ++j) sts32(sb + (uint32_t)(j * 128 + r) * 4u, __float_as_uint(v[j]));
+            if (via_acc) stage_end(sb, &tm_acc, 0, acc_row0 + blk * TN + t0, true);
+            else stage_end(sb, &tm_y, blk ? rowB0 : rowA0, tok0 + t0, p.epi == B200P_EPI_ADD_RESIDUAL);
+          }
+        } else if (silu) {
+          float g[EPI_TOK], uu[EPI_TOK];
+          tmem_ld16(dA + (uint32_t)t0, g);
+          tmem_ld16(dB + (uint32_t)t0, uu);
+          tmem_ld_wait();
+          const uint32_t sb = stage_begin();
+#pragma unroll
+          for (int j = 0; j < EPI_TOK; ++j) sts16(sb + (uint32_t)(j * 128 + rp) * 2u, Tr<T>::from_f(silu_tc(g[j]) * uu[j]));
+          stage_end(sb, &tm_y, rowA0, tok0 + t0, false);
         } else {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            if (tok0 + t + j < p.M_tok) {
-              atomicAdd(acc + (int64_t)(t + j) * 128 + r, v0[j]);
-              atomicAdd(acc + ((int64_t)TN + t + j) * 128 + r, v1[j]);
-            }
+          for (int blk = 0; blk < 2; ++blk) {
+            float v[EPI_TOK];
+            tmem_ld16((blk ? dB : dA) + (uint32_t)t0, v);
+            tmem_ld_wait();
+            const uint32_t sb = stage_begin();
+#pragma unroll
+            for (int j = 0; j < EPI_TOK; ++j) sts16(sb + (uint32_t)(j * 128 + rp) * 2u, Tr<T>::from_f(v[j]));
+            stage_end(sb, &tm_y, blk ? rowB0 : rowA0, tok0 + t0, false);
           }
         }
       }
@@ -627,9 +681,12 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
       if (lane == 0) mbar_arrive(accum_empty(buf));    // this D buffer may be overwritten by a later segment's MMAs
       if (via_acc && !(p.debug & 4)) {
         const int nseg = owner_of((long long)tile * p.num_st + p.num_st - 1, p.U, G) - c_first + 1;
-        __threadfence();
-        named_bar_sync(1, EPI_THREADS);
+        float* acc = p.ws_acc + (int64_t)acc_row0 * 128;
+        const int n0 = rowA0 + r, n1 = rowB0 + r;      // output columns of this thread (block 0 / block 1)
+        const int c0 = p.y_perm ? perm8_pos(n0) : n0, c1 = p.y_perm ? perm8_pos(n1) : n1;
         if (et == 0) {
+          bulk_wait_all();                             // our reduce-adds have been performed ...
+          __threadfence();                             // ... and are visible before the arrival is counted
           const int old = atomicAdd(p.ws_counter + tile, 1);
           const int last = (old == nseg - 1);
           if (last) p.ws_counter[tile] = 0;            // self-cleaning for the next launch
@@ -649,18 +706,32 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
             }
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-              finish(t + j, v0[j], v1[j]);
+              const int tok = tok0 + t + j;
+              if (tok < p.M_tok) {
+                if (p.epi == B200P_EPI_STORE) {
+                  T* y = reinterpret_cast<T*>(p.y) + (int64_t)tok * p.ldy;
+                  if (n0 < p.N) y[c0] = Tr<T>::from_f(v0[j]);
+                  if (n1 < p.N) y[c1] = Tr<T>::from_f(v1[j]);
+                } else if (p.epi == B200P_EPI_STORE_F32) {
+                  float* y = reinterpret_cast<float*>(p.y) + (int64_t)tok * p.ldy;
+                  if (n0 < p.N) y[n0] = v0[j];
+                  if (n1 < p.N) y[n1] = v1[j];
+                } else {
+                  T* y = reinterpret_cast<T*>(p.y) + (int64_t)tok * p.ldy;
+                  if (n0 < p.N / 2) y[c0] = Tr<T>::from_f(silu_tc(v0[j]) * v1[j]);
+                }
+              }
               __stcg(acc + (int64_t)(t + j) * 128 + r, 0.f);
               __stcg(acc + ((int64_t)TN + t + j) * 128 + r, 0.f);
             }
           }
         }
-        named_bar_sync(1, EPI_THREADS);                // flag_slot is reused by the next segment
+        named_bar_sync(2, EPI_THREADS);                // flag_slot is reused by the next segment
       }
       u += ns;
     }
+    if (et == 0) bulk_wait_all();                      // staging memory and outputs are settled before the CTA retires
   }
-  pdl_launch_dependents();
   tc_fence_before();
   __syncthreads();
   if (warp == WARP_MMA) {
@@ -686,7 +757,7 @@ static EncodeTiledFn get_encode() {
 }
 
 constexpr int SMEM_BUDGET = 227 * 1024;
-constexpr int SMEM_FIXED = 1024 /*align*/ + NSB * SB_SLOT_BYTES + 512 /*barriers*/;
+constexpr int SMEM_FIXED = 1024 /*align*/ + NSB * SB_SLOT_BYTES + EPI_NBUF * EPI_BUF_BYTES + 512 /*barriers*/;
 static_assert(8 * (4 * MAX_STAGES + 2 * NSLOT + 2 * NSB + 4) + 8 <= 512, "barrier block overflows its slot");
 constexpr int MIN_TC_M = 5;        // below this the CUDA-core GEMV wins (weights read once either way)
 constexpr int MIN_UNITS_PER_CTA = 2;
@@ -763,8 +834,8 @@ static int launch_tc(const CUtensorMap* tms, const TcParams& p, const TcPlan& pl
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tms[0], tms[1], tms[2], tms[3], p);
+  cfg.numAttrs = pdl_enabled_gemm() ? 1 : 0;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tms[0], tms[1], tms[2], tms[3], tms[4], tms[5], p);
   if (e != cudaSuccess) return cuda_fail(e, "qmm_tc_kernel launch");
   return B200P_OK;
 }
@@ -795,7 +866,7 @@ int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b
   const int num_kb = (int)(K / 64);
   const bool sb_tma = (num_kb % 8) == 0 && aligned(s, 16) && aligned(b, 16);
   const CUtensorMapDataType dt16 = dtype == B200P_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
-  CUtensorMap tms[4];
+  CUtensorMap tms[6];
   int rc = encode_2d(enc, &tms[0], CU_TENSOR_MAP_DATA_TYPE_UINT8, w, (uint64_t)(K * bits / 8), (uint64_t)N,
                      (uint64_t)(K * bits / 8), 128u, 128u, CU_TENSOR_MAP_SWIZZLE_128B, "weights");
   if (rc) return rc;
@@ -818,6 +889,21 @@ int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b
   const size_t counters = ws_counter_bytes(M, N);
   const size_t need = counters + (size_t)pl.grid * 2 * pl.TN * 128 * sizeof(float);
   B200P_REQUIRE(ws_bytes >= need && aligned(ws, 16), B200P_ERR_ARG, "qmm workspace too small (%zu < %zu)", ws_bytes, need);
+  {
+    // output tensor: [M tokens x n_out columns]; staging tiles are [16 tokens x 128 columns]
+    const bool f32out = epi == B200P_EPI_STORE_F32 || epi == B200P_EPI_ADD_RESIDUAL;
+    const uint64_t n_out = (uint64_t)(epi == B200P_EPI_SILU_MUL ? N / 2 : N);
+    const size_t esz = f32out ? 4 : 2;
+    B200P_REQUIRE(aligned(y, 16) && (ldy * esz) % 16 == 0, B200P_ERR_ALIGN, "y rows must be 16-byte aligned for the tensor path (ldy=%lld)",
+                  (long long)ldy);
+    rc = encode_2d(enc, &tms[4], f32out ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : dt16, y, n_out, (uint64_t)M, (uint64_t)ldy * esz, 128u,
+                   (uint32_t)EPI_TOK, CU_TENSOR_MAP_SWIZZLE_NONE, "y");
+    if (rc) return rc;
+    // stream-K accumulators: one fp32 [2*TN x 128] block per CTA boundary
+    rc = encode_2d(enc, &tms[5], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, reinterpret_cast<char*>(ws) + counters, 128u,
+                   (uint64_t)pl.grid * 2 * pl.TN, 512u, 128u, (uint32_t)EPI_TOK, CU_TENSOR_MAP_SWIZZLE_NONE, "acc");
+    if (rc) return rc;
+  }
   p.ws_counter = reinterpret_cast<int*>(ws);
   p.ws_acc = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + counters);
   p.M_tok = (int)M; p.N = (int)N; p.K = (int)K; p.TN = pl.TN; p.ldy = ldy; p.epi = epi; p.y_perm = y_perm ? 1 : 0;

@@ -142,9 +142,9 @@ static int launch_qmv_mb(const T* x, const uint32_t* w, const T* s, const T* b, 
     int mv = (int)((M - m0) < 4 ? (M - m0) : 4);
     const T* xp = x + m0 * ldx;
     void* yp = reinterpret_cast<char*>(y) + m0 * ldy * ysz;
-    if (mv == 1) qmv_kernel<T, BITS, 1, EPI><<<grid, block, 0, st>>>(xp, w, s, b, yp, mv, N, K, ldx, ldy, gs, flags);
-    else if (mv == 2) qmv_kernel<T, BITS, 2, EPI><<<grid, block, 0, st>>>(xp, w, s, b, yp, mv, N, K, ldx, ldy, gs, flags);
-    else qmv_kernel<T, BITS, 4, EPI><<<grid, block, 0, st>>>(xp, w, s, b, yp, mv, N, K, ldx, ldy, gs, flags);
+    if (mv == 1) launch_pdl(qmv_kernel<T, BITS, 1, EPI>, grid, block, 0, st, xp, w, s, b, yp, mv, N, K, ldx, ldy, gs, flags);
+    else if (mv == 2) launch_pdl(qmv_kernel<T, BITS, 2, EPI>, grid, block, 0, st, xp, w, s, b, yp, mv, N, K, ldx, ldy, gs, flags);
+    else launch_pdl(qmv_kernel<T, BITS, 4, EPI>, grid, block, 0, st, xp, w, s, b, yp, mv, N, K, ldx, ldy, gs, flags);
   }
   B200P_LAUNCH_CHECK("qmv_kernel");
   return B200P_OK;

@@ -319,7 +319,7 @@ extern "C" int b200p_argmax(const float* logits, int32_t* tokens, float* probs_o
   B200P_REQUIRE(logits && tokens, B200P_ERR_ARG, "null pointer");
   B200P_REQUIRE(V > 0 && V < (1ll << 31) && ldl >= V, B200P_ERR_ARG, "bad V/ldl");
   if (B == 0) return B200P_OK;
-  argmax_kernel<<<(unsigned)B, SAMP_THREADS, 0, (cudaStream_t)stream>>>(logits, tokens, probs_out, V, ldl, nullptr, 0);
+  launch_pdl(argmax_kernel, (unsigned)B, SAMP_THREADS, 0, (cudaStream_t)stream, logits, tokens, probs_out, V, ldl, nullptr, 0);
   B200P_LAUNCH_CHECK("argmax_kernel");
   return B200P_OK;
 }
@@ -330,7 +330,7 @@ extern "C" int b200p_argmax_partial(const float* logits, float* rec_out, int64_t
   B200P_REQUIRE(V > 0 && V < (1ll << 31) && ldl >= V && vocab_offset >= 0, B200P_ERR_ARG, "bad V/ldl/offset");
   B200P_REQUIRE(aligned(rec_out, 16), B200P_ERR_ALIGN, "rec_out must be 16-byte aligned");
   if (B == 0) return B200P_OK;
-  argmax_kernel<<<(unsigned)B, SAMP_THREADS, 0, (cudaStream_t)stream>>>(logits, nullptr, nullptr, V, ldl,
+  launch_pdl(argmax_kernel, (unsigned)B, SAMP_THREADS, 0, (cudaStream_t)stream, logits, nullptr, nullptr, V, ldl,
                                                                        reinterpret_cast<float4*>(rec_out), vocab_offset);
   B200P_LAUNCH_CHECK("argmax_kernel(partial)");
   return B200P_OK;
@@ -341,7 +341,7 @@ extern "C" int b200p_argmax_merge(const float* recs, int32_t* tokens, float* pro
   B200P_REQUIRE(recs && tokens, B200P_ERR_ARG, "null pointer");
   B200P_REQUIRE(W > 0 && aligned(recs, 16), B200P_ERR_ARG, "bad shard count / alignment");
   if (B == 0) return B200P_OK;
-  argmax_merge_kernel<<<(unsigned)((B + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+  launch_pdl(argmax_merge_kernel, (unsigned)((B + 127) / 128), 128, 0, (cudaStream_t)stream, 
       reinterpret_cast<const float4*>(recs), tokens, probs_out, W, B);
   B200P_LAUNCH_CHECK("argmax_merge_kernel");
   return B200P_OK;
@@ -355,7 +355,7 @@ extern "C" int b200p_sample_top_p(const float* logits, int32_t* tokens, float* p
   B200P_REQUIRE(temperature > 0.f, B200P_ERR_ARG, "temperature must be > 0 (use b200p_argmax for greedy)");
   if (B == 0) return B200P_OK;
   if (!(top_p > 0.f)) top_p = 1.0f;
-  top_p_kernel<<<(unsigned)B, SAMP_THREADS, 0, (cudaStream_t)stream>>>(logits, tokens, probs_out, V, ldl,
+  launch_pdl(top_p_kernel, (unsigned)B, SAMP_THREADS, 0, (cudaStream_t)stream, logits, tokens, probs_out, V, ldl,
                                                                       1.0f / temperature, top_p, seed, offset);
   B200P_LAUNCH_CHECK("top_p_kernel");
   return B200P_OK;

@@ -31,6 +31,7 @@ from .._lib import EPI_ADD_RESIDUAL, EPI_SILU_MUL, EPI_STORE, EPI_STORE_F32
 from .base import BatchedKVCache, PagedKVCache
 
 MAX_TOKENS_PER_FORWARD = 8192     # chunk size (B*L) of one prefill pass through the layers
+USE_PERM8 = True                  # 4-bit 16-bit models: GEMM inputs in the PERM8 column order (include/b200p.h)
 
 
 class QuantizedLinear:
@@ -46,10 +47,10 @@ class QuantizedLinear:
         self.out_features = weight.shape[0]
         self.in_features = weight.shape[1] * 32 // self.bits
 
-    def __call__(self, x, epilogue=EPI_STORE, out=None, workspace=None):
+    def __call__(self, x, epilogue=EPI_STORE, out=None, workspace=None, x_perm=False):
         lead = x.shape[:-1]
         y = ops.qmm(x.reshape(-1, x.shape[-1]), self.weight, self.scales, self.biases, self.group_size,
-                    self.bits, epilogue, out, workspace)
+                    self.bits, epilogue, out, workspace, x_perm=x_perm)
         return y if out is not None else y.reshape(*lead, -1)
 
 
@@ -217,6 +218,11 @@ class DecoderModel:
             raise TypeError(f"scales must share one dtype, got {dts}")
         self.dtype = dts.pop()
         self.device = device
+        a0 = self.args
+        self._fast16 = self.dtype in (torch.float16, torch.bfloat16)
+        # PERM8 needs every GEMM input row to be made of aligned groups of 8 (hidden, heads*head_dim, intermediate)
+        self._perm8 = (self._fast16 and a0._bits == 4 and a0.hidden_size % 8 == 0 and self._hd % 8 == 0
+                       and a0.intermediate_size % 8 == 0 and USE_PERM8)
 
         def put(t):
             if t.dtype == torch.uint32:
@@ -292,6 +298,10 @@ class DecoderModel:
                 h=torch.empty((M, args.hidden_size), dtype=torch.float32, device=dev),
                 x=torch.empty((M, args.hidden_size), dtype=dt, device=dev),
                 qkv=torch.empty((M, nqkv), dtype=dt, device=dev),
+                # fp32 split-K accumulation buffers of the fused q|k|v and gate|up projections (16-bit models): zero
+                # once, the consumer kernels (rope_kv_append, silu_mul) re-zero them behind their reads
+                qkv32=torch.zeros((M, nqkv), dtype=torch.float32, device=dev) if self._fast16 else None,
+                gu32=torch.zeros((M, 2 * inter_local), dtype=torch.float32, device=dev) if self._fast16 else None,
                 q=torch.empty((M, att.n_heads * att.head_dim), dtype=dt, device=dev),
                 att=torch.empty((M, att.n_heads * att.head_dim), dtype=dt, device=dev),
                 act=torch.empty((M, inter_local), dtype=dt, device=dev),
@@ -311,27 +321,40 @@ class DecoderModel:
         args = self.args
         self.model.embed_tokens.embed(ids_i32, out=a["h"])
         tp = self.tp_world > 1
+        # 16-bit models: (i) the fused projections accumulate in fp32 (stream-K partial tiles are summed by TMA
+        # reduce-adds, no second pass) and the consumer kernel rounds to the storage type; (ii) with 4-bit weights the
+        # GEMM inputs travel in the PERM8 column order the tensor path unpacks nibbles in.
+        f16 = self._fast16
+        pm = self._perm8
         for layer, c in zip(self.model.layers, cache):
             at, mlp = layer.self_attn, layer.mlp
             lengths = c.lengths(self.device)
-            ops.rmsnorm(a["h"], layer.input_layernorm.weight, layer.input_layernorm.eps, out=a["x"])
-            at.qkv_proj(a["x"], EPI_STORE, out=a["qkv"], workspace=a["ws"])
-            ops.rope_kv_append(a["qkv"], a["q"], c.keys, c.values, lengths, B, L, at.n_heads, at.n_kv_heads,
-                               at.head_dim, args.rope_theta, self.rope_scale,
+            ops.rmsnorm(a["h"], layer.input_layernorm.weight, layer.input_layernorm.eps, out=a["x"], out_perm=pm)
+            if f16:
+                at.qkv_proj(a["x"], EPI_ADD_RESIDUAL, out=a["qkv32"], workspace=a["ws"], x_perm=pm)
+            else:
+                at.qkv_proj(a["x"], EPI_STORE, out=a["qkv"], workspace=a["ws"])
+            ops.rope_kv_append(a["qkv32"] if f16 else a["qkv"], a["q"], c.keys, c.values, lengths, B, L, at.n_heads,
+                               at.n_kv_heads, at.head_dim, args.rope_theta, self.rope_scale,
                                at.q_norm.weight if at.q_norm else None, at.k_norm.weight if at.k_norm else None,
                                args.rms_norm_eps)
             ops.attn(a["q"], c.keys, c.values, lengths, a["att"], B, L, at.n_heads, at.n_kv_heads, at.head_dim,
-                     at.scale, workspace=a["ws_attn"])
+                     at.scale, workspace=a["ws_attn"], out_perm=pm)
             if tp and self.tp_rank != 0:
                 a["h"].zero_()
-            at.o_proj(a["att"], EPI_ADD_RESIDUAL, out=a["h"], workspace=a["ws"])
+            at.o_proj(a["att"], EPI_ADD_RESIDUAL, out=a["h"], workspace=a["ws"], x_perm=pm)
             if tp:
                 self._allreduce(a["h"])
-            ops.rmsnorm(a["h"], layer.post_attention_layernorm.weight, layer.post_attention_layernorm.eps, out=a["x"])
-            mlp.gate_up_proj(a["x"], EPI_SILU_MUL, out=a["act"], workspace=a["ws"])
+            ops.rmsnorm(a["h"], layer.post_attention_layernorm.weight, layer.post_attention_layernorm.eps, out=a["x"],
+                        out_perm=pm)
+            if f16:
+                mlp.gate_up_proj(a["x"], EPI_ADD_RESIDUAL, out=a["gu32"], workspace=a["ws"], x_perm=pm)
+                ops.silu_mul(a["gu32"], a["act"], out_perm=pm)
+            else:
+                mlp.gate_up_proj(a["x"], EPI_SILU_MUL, out=a["act"], workspace=a["ws"])
             if tp and self.tp_rank != 0:
                 a["h"].zero_()
-            mlp.down_proj(a["act"], EPI_ADD_RESIDUAL, out=a["h"], workspace=a["ws"])
+            mlp.down_proj(a["act"], EPI_ADD_RESIDUAL, out=a["h"], workspace=a["ws"], x_perm=pm)
             if tp:
                 self._allreduce(a["h"])
 
@@ -339,9 +362,9 @@ class DecoderModel:
         """final RMSNorm + lm_head / tied embed_tokens.as_linear (llama.py:231,249-252) -> float32 logits."""
         n = self.model.norm
         rows = h_rows.shape[0]
-        x = ops.rmsnorm(h_rows, n.weight, n.eps, out=a["xl"][:rows])
+        x = ops.rmsnorm(h_rows, n.weight, n.eps, out=a["xl"][:rows], out_perm=self._perm8)
         head = self.lm_head if self.lm_head is not None else self.model.embed_tokens
-        return QuantizedLinear.__call__(head, x, EPI_STORE_F32, out=logits_out, workspace=a["ws"])
+        return QuantizedLinear.__call__(head, x, EPI_STORE_F32, out=logits_out, workspace=a["ws"], x_perm=self._perm8)
 
     def __call__(self, inputs, cache: Optional[List[BatchedKVCache]] = None, last_only: bool = False):
         """inputs int [B, L] -> logits float32 [B, L, V] (or [B, 1, V] with last_only, the only rows

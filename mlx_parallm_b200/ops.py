@@ -165,7 +165,18 @@ def rope_kv_append(qkv, q_out, kcache, vcache, lengths, B, L, Hq, Hkv, D, rope_b
     Tcap = kcache.shape[2]
     _call("b200p_rope_kv_append", lambda: lib().b200p_rope_kv_append(_p(qkv), _p(q_out), _p(kcache), _p(vcache), _p(lengths), _p(q_norm_w),
                                      _p(k_norm_w), B, L, Hq, Hkv, D, Tcap, float(rope_base), float(rope_scale),
-                                     float(norm_eps), dtype_code(qkv.dtype), _stream()))
+                                     float(norm_eps), dtype_code(kcache.dtype), 1 if qkv.dtype == torch.float32 and kcache.dtype != torch.float32 else 0,
+                                     _stream()))
+
+
+def silu_mul(gu, out, out_perm=False):
+    """silu(gate) * up from the fp32 accumulation buffer gu [M, 2*I] of the fused gate|up projection; re-zeroes gu."""
+    _dev(gu, out)
+    assert gu.dtype == torch.float32 and gu.stride(1) == 1 and out.stride(1) == 1
+    M, I = out.shape
+    _call("b200p_silu_mul", lambda: lib().b200p_silu_mul(_p(gu), _p(out), M, I, gu.stride(0), out.stride(0), dtype_code(out.dtype),
+                                                         _lib.OUT_PERM8 if out_perm else 0, _stream()))
+    return out
 
 
 def advance_lengths(lengths, delta: int):

@@ -33,12 +33,12 @@ def bench(M, N, K, epi, rotate, reps=20):
     ws.zero_()
     return e0.elapsed_time(e1) / reps * 1e3
 
-shapes = [(64, 28672, 4096, 3), (8, 28672, 4096, 3), (64, 4096, 4096, 2)]
+shapes = [(64, 28672, 4096, 2), (64, 4096, 14336, 2), (64, 4096, 4096, 2), (16, 28672, 4096, 2)]
 if len(sys.argv) > 1 and sys.argv[1] == "all":
     shapes += [(64, 4096, 4096, 2), (64, 4096, 14336, 2), (64, 6144, 4096, 0)]
 # bits: 2 no MMA, 4 no epilogue, 8 no TMEM store of A, 16 no LDS + dequant math
 # bits: 1 no X loads, 2 no MMA issue, 4 no epilogue stores, 8 no A stores
-modes = [("full", 0), ("-x", 1), ("-mma", 2), ("-epi", 4), ("-sttm", 8), ("-x-mma", 3), ("-x-mma-epi", 7), ("-all", 15)]
+modes = [("full", 0), ("-sb", 32), ("-x-mma-epi", 7), ("-x-mma-epi-sb", 39), ("-all", 47)]
 for (M, N, K, epi) in shapes:
     byts = N * K / 2 + 2 * N * (K // 64) * 2
     row = []
