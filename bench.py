@@ -301,6 +301,13 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries exactly ONE line (the JSON); anything libraries print (NCCL's version banner, warnings) goes to stderr
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(line: dict):
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     cfg_name, B, T = WORKLOADS[args.workload]
 
     if args.impl == "reference":
@@ -314,7 +321,7 @@ def main():
                            "note": "reference arithmetic lives in mlx==0.25.2 (not installable offline); this is the numpy port of the same step"},
                 "cpu_baseline": cb,
                 "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line))
+        emit(line)
         return
 
     import torch
@@ -378,7 +385,7 @@ def main():
                 "clocks": clocks, "sweep": sweep}
         if cb is not None:
             line["cpu_baseline"] = cb
-        print(json.dumps(line))
+        emit(line)
     if dist is not None:
         dist.destroy_process_group()
 

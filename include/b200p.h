@@ -164,6 +164,41 @@ int b200p_sample_top_p(const float* logits, int32_t* tokens, float* probs_out, i
                        int64_t V, int64_t ldl, float temperature, float top_p, uint64_t seed,
                        uint64_t offset, void* stream);
 
+/* ---- tensor-parallel exchange over NVLink peer memory (new; the reference is single-device) -----------------
+ * Setup calls (host side, synchronous, NOT graph-capturable; the only entry points that allocate):
+ *   b200p_symm_alloc   cudaMalloc + zero a buffer peers may map;   b200p_symm_free releases it
+ *   b200p_ipc_export   64-byte cudaIpcMemHandle of such a buffer (ship it to the peers with any host transport)
+ *   b200p_ipc_import   map a peer's buffer into this process (peer access enabled lazily); b200p_ipc_close unmaps it
+ * Each rank owns one flag array of b200p_allreduce_flag_bytes() bytes (zeroed) mapped by every peer. */
+#define B200P_AR_MAX_CTAS 1024
+int b200p_symm_alloc(void** ptr, size_t bytes);
+int b200p_symm_free(void* ptr);
+int b200p_ipc_export(void* ptr, void* handle64);
+int b200p_ipc_import(const void* handle64, void** ptr);
+int b200p_ipc_close(void* ptr);
+size_t b200p_allreduce_flag_bytes(void);
+/* cap on the exchange grid (0 = auto: the number of CTAs the device can hold at once); tests / tuning */
+int b200p_allreduce_set_max_ctas(int n);
+
+/* One-shot all-reduce of the row-parallel partial sums + residual add + the next RMSNorm, one kernel per rank
+ *                      [replaces, under TP, the residual adds of models/llama.py:188,190 and the nn.RMSNorm that follows
+ *                       (models/llama.py:187,189,231) around a sum over ranks the single-device reference does not need]
+ * peer_partial[p] / peer_flags[p]: HOST arrays of `world` device pointers -- rank p's fp32 partial buffer [M, ld_partial]
+ * and flag array as mapped in this process (entry `rank` is the local buffer).  h float [M,H] += sum_p partial_p (rank
+ * order: bit-identical on all ranks); y `dtype` [M,H] = rms_norm(h, norm_w, eps) (both NULL to skip), optionally PERM8
+ * (flags = B200P_OUT_PERM8); zero_buf (local fp32 [M, ld_partial], may be NULL) is zeroed behind the handshake: pass the
+ * OTHER partial buffer of a two-buffer rotation (see csrc/allreduce.cu for the protocol and why two buffers suffice).
+ * Every rank must issue the same sequence of exchange calls with the same M. */
+int b200p_allreduce_residual_rmsnorm(const void* const* peer_partial, void* const* peer_flags, int world, int rank,
+                                     float* h, const void* norm_w, void* y, float* zero_buf, int64_t M, int64_t H,
+                                     int64_t ld_partial, float eps, int dtype, int flags, void* stream);
+/* dst[p * bytes_per_rank ...] = peer p's src block, through peer memory (vocab-parallel greedy head: the W records of
+ * b200p_argmax_partial, then b200p_argmax_merge).  bytes_per_rank % 16 == 0. */
+int b200p_peer_allgather(const void* const* peer_src, void* const* peer_flags, int world, int rank, void* dst,
+                         int64_t bytes_per_rank, void* stream);
+/* host_out[0] = 1 if a handshake of this rank ever timed out (a peer stopped), else 0; synchronises `stream` */
+int b200p_peer_status(const void* flags_local, uint32_t* host_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

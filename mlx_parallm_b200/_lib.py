@@ -44,6 +44,16 @@ SIGNATURES = {
     "b200p_argmax_partial": (_i32, [_vp, _vp, _i64, _i64, _i64, _i32, _vp]),
     "b200p_argmax_merge": (_i32, [_vp, _vp, _vp, _i32, _i64, _vp]),
     "b200p_sample_top_p": (_i32, [_vp, _vp, _vp, _i64, _i64, _i64, _f32, _f32, _u64, _u64, _vp]),
+    "b200p_symm_alloc": (_i32, [C.POINTER(_vp), _sz]),
+    "b200p_symm_free": (_i32, [_vp]),
+    "b200p_ipc_export": (_i32, [_vp, _vp]),
+    "b200p_ipc_import": (_i32, [_vp, C.POINTER(_vp)]),
+    "b200p_ipc_close": (_i32, [_vp]),
+    "b200p_allreduce_flag_bytes": (_sz, []),
+    "b200p_allreduce_set_max_ctas": (_i32, [_i32]),
+    "b200p_allreduce_residual_rmsnorm": (_i32, [_vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _f32, _i32, _i32, _vp]),
+    "b200p_peer_allgather": (_i32, [_vp, _vp, _i32, _i32, _vp, _i64, _vp]),
+    "b200p_peer_status": (_i32, [_vp, _vp, _vp]),
 }
 
 _lib = None

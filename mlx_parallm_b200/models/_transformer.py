@@ -326,10 +326,14 @@ class DecoderModel:
         # GEMM inputs travel in the PERM8 column order the tensor path unpacks nibbles in.
         f16 = self._fast16
         pm = self._perm8
-        for layer, c in zip(self.model.layers, cache):
+        fx = getattr(self, "_tp_fused", None) if tp else None      # peer-memory exchange (tp.PeerExchange) or NCCL
+        layers = self.model.layers
+        M = a["h"].shape[0]
+        for li, (layer, c) in enumerate(zip(layers, cache)):
             at, mlp = layer.self_attn, layer.mlp
             lengths = c.lengths(self.device)
-            ops.rmsnorm(a["h"], layer.input_layernorm.weight, layer.input_layernorm.eps, out=a["x"], out_perm=pm)
+            if fx is None or li == 0:      # with the fused exchange the previous layer's down_proj exchange wrote x
+                ops.rmsnorm(a["h"], layer.input_layernorm.weight, layer.input_layernorm.eps, out=a["x"], out_perm=pm)
             if f16:
                 at.qkv_proj(a["x"], EPI_ADD_RESIDUAL, out=a["qkv32"], workspace=a["ws"], x_perm=pm)
             else:
@@ -340,23 +344,36 @@ class DecoderModel:
                                args.rms_norm_eps)
             ops.attn(a["q"], c.keys, c.values, lengths, a["att"], B, L, at.n_heads, at.n_kv_heads, at.head_dim,
                      at.scale, workspace=a["ws_attn"], out_perm=pm)
-            if tp and self.tp_rank != 0:
-                a["h"].zero_()
-            at.o_proj(a["att"], EPI_ADD_RESIDUAL, out=a["h"], workspace=a["ws"], x_perm=pm)
-            if tp:
-                self._allreduce(a["h"])
-            ops.rmsnorm(a["h"], layer.post_attention_layernorm.weight, layer.post_attention_layernorm.eps, out=a["x"],
-                        out_perm=pm)
+            if fx is not None:
+                # row-parallel partial sums accumulate into the peer-mapped buffer; ONE kernel then does the
+                # all-reduce over NVLink + residual add + post-attention RMSNorm (and re-zeroes the other buffer)
+                at.o_proj(a["att"], EPI_ADD_RESIDUAL, out=fx.partial(0, M), workspace=a["ws"], x_perm=pm)
+                n2 = layer.post_attention_layernorm
+                fx.exchange(0, a["h"], n2.weight, a["x"], n2.eps, out_perm=pm)
+            else:
+                if tp and self.tp_rank != 0:
+                    a["h"].zero_()
+                at.o_proj(a["att"], EPI_ADD_RESIDUAL, out=a["h"], workspace=a["ws"], x_perm=pm)
+                if tp:
+                    self._allreduce(a["h"])
+                ops.rmsnorm(a["h"], layer.post_attention_layernorm.weight, layer.post_attention_layernorm.eps, out=a["x"],
+                            out_perm=pm)
             if f16:
                 mlp.gate_up_proj(a["x"], EPI_ADD_RESIDUAL, out=a["gu32"], workspace=a["ws"], x_perm=pm)
                 ops.silu_mul(a["gu32"], a["act"], out_perm=pm)
             else:
                 mlp.gate_up_proj(a["x"], EPI_SILU_MUL, out=a["act"], workspace=a["ws"])
-            if tp and self.tp_rank != 0:
-                a["h"].zero_()
-            mlp.down_proj(a["act"], EPI_ADD_RESIDUAL, out=a["h"], workspace=a["ws"], x_perm=pm)
-            if tp:
-                self._allreduce(a["h"])
+            if fx is not None:
+                mlp.down_proj(a["act"], EPI_ADD_RESIDUAL, out=fx.partial(1, M), workspace=a["ws"], x_perm=pm)
+                nxt = layers[li + 1].input_layernorm if li + 1 < len(layers) else None
+                fx.exchange(1, a["h"], nxt.weight if nxt else None, a["x"] if nxt else None,
+                            nxt.eps if nxt else 0.0, out_perm=pm)
+            else:
+                if tp and self.tp_rank != 0:
+                    a["h"].zero_()
+                mlp.down_proj(a["act"], EPI_ADD_RESIDUAL, out=a["h"], workspace=a["ws"], x_perm=pm)
+                if tp:
+                    self._allreduce(a["h"])
 
     def _head(self, h_rows: torch.Tensor, a: dict, logits_out: Optional[torch.Tensor] = None):
         """final RMSNorm + lm_head / tied embed_tokens.as_linear (llama.py:231,249-252) -> float32 logits."""

@@ -121,8 +121,13 @@ class TensorParallelHead:
             self._rec[B] = (torch.empty((B, 4), dtype=torch.float32, device=dev),
                             torch.empty((self.world, B, 4), dtype=torch.float32, device=dev))
         mine, allr = self._rec[B]
-        ops.argmax_partial(logits, self.v0, mine)
-        self.dist.all_gather_into_tensor(allr.view(-1), mine.view(-1), group=self.group)
+        fx = getattr(self.model, "_tp_fused", None)
+        if fx is not None and B <= fx.REC_ROWS:
+            ops.argmax_partial(logits, self.v0, fx.records[:B])       # peer-visible records, gathered over NVLink
+            fx.allgather_records(B, allr)
+        else:
+            ops.argmax_partial(logits, self.v0, mine)
+            self.dist.all_gather_into_tensor(allr.view(-1), mine.view(-1), group=self.group)
         ops.argmax_merge(allr, tok_out, probs_out)
 
     def sample(self, logits, temp, top_p, seed, offset, tok_out, probs_out=None):
@@ -140,13 +145,127 @@ class TensorParallelHead:
         ops.sample_top_p(full, temp, top_p, seed, offset, out=tok_out, probs_out=probs_out)
 
 
-def attach(model, dist, rank: int, world: int, group=None, allreduce: Optional[Callable] = None):
+class _RawCuda:
+    """__cuda_array_interface__ carrier so torch can view memory this library allocated (b200p_symm_alloc)."""
+
+    def __init__(self, ptr: int, shape, typestr: str):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 3,
+                                         "strides": None}
+
+
+class PeerExchange:
+    """This rank's peer-mapped buffers and the fused exchange launches (csrc/allreduce.cu).
+
+    One device allocation per rank, mapped by every peer through cudaIpc handles shipped with
+    ``dist.all_gather_object`` (host plumbing, once, at attach time):
+
+        [ partial A : max_rows x hidden f32 | partial B : same | records : 4096 x 16 B | flags ]
+
+    ``partial(i, M)`` is the tensor a row-parallel projection accumulates into (``EPI_ADD_RESIDUAL``);
+    ``exchange(i, ...)`` sums the W partials over NVLink in rank order, adds the residual stream, applies the next
+    RMSNorm and zeroes partial ``1 - i`` -- one kernel per rank instead of memset + ncclAllReduce + rmsnorm."""
+
+    REC_ROWS = 4096
+
+    def __init__(self, dist, group, rank: int, world: int, device, max_rows: int, hidden: int):
+        import ctypes as C
+        from ._lib import check, lib
+        self.rank, self.world, self.hidden, self.max_rows = rank, world, hidden, max_rows
+        self.device = torch.device(device)
+        L = lib()
+        part = max_rows * hidden * 4
+        rec = self.REC_ROWS * 16
+        flag_bytes = int(L.b200p_allreduce_flag_bytes())
+        self._off = (0, part, 2 * part, 2 * part + rec)
+        total = 2 * part + rec + flag_bytes
+        with torch.cuda.device(self.device):
+            base = C.c_void_p()
+            check(L.b200p_symm_alloc(C.byref(base), total), "b200p_symm_alloc")
+            self._base = base.value
+            handle = (C.c_char * 64)()
+            check(L.b200p_ipc_export(self._base, handle), "b200p_ipc_export")
+            handles = [None] * world
+            dist.all_gather_object(handles, bytes(handle.raw), group=group)
+            self._peer_base = []
+            for p in range(world):
+                if p == rank:
+                    self._peer_base.append(self._base)
+                else:
+                    ptr = C.c_void_p()
+                    check(L.b200p_ipc_import(handles[p], C.byref(ptr)), "b200p_ipc_import")
+                    self._peer_base.append(ptr.value)
+        arr = C.c_void_p * world
+        self._tab = [arr(*[b + off for b in self._peer_base]) for off in self._off]      # A, B, records, flags
+        self._local = [torch.as_tensor(_RawCuda(self._base + self._off[i], (max_rows, hidden), "<f4"), device=self.device)
+                       for i in (0, 1)]
+        self.records = torch.as_tensor(_RawCuda(self._base + self._off[2], (self.REC_ROWS, 4), "<f4"), device=self.device)
+        self._closed = False
+        dist.barrier(group=group)          # every rank has mapped every buffer before anybody launches
+
+    def partial(self, which: int, M: int) -> torch.Tensor:
+        if M > self.max_rows:
+            raise ValueError(f"{M} rows exceed the peer buffer ({self.max_rows})")
+        return self._local[which][:M]
+
+    def exchange(self, which: int, h: torch.Tensor, norm_w: Optional[torch.Tensor], y: Optional[torch.Tensor], eps: float,
+                 out_perm: bool = False):
+        from . import _lib, ops
+        M, H = h.shape
+        assert H == self.hidden and h.dtype == torch.float32 and h.is_contiguous()
+        dt = ops.dtype_code(norm_w.dtype) if norm_w is not None else _lib.F32
+        ops._call("b200p_allreduce_residual_rmsnorm", lambda: _lib.lib().b200p_allreduce_residual_rmsnorm(
+            self._tab[which], self._tab[3], self.world, self.rank, h.data_ptr(),
+            0 if norm_w is None else norm_w.data_ptr(), 0 if y is None else y.data_ptr(),
+            self._local[1 - which].data_ptr(), M, H, self.hidden, float(eps), dt,
+            _lib.OUT_PERM8 if (out_perm and y is not None) else 0, ops._stream()))
+
+    def allgather_records(self, B: int, dst: torch.Tensor):
+        """dst [W, B, 4] <- every rank's records[:B] (written by b200p_argmax_partial)."""
+        from . import _lib, ops
+        assert B <= self.REC_ROWS and dst.is_contiguous()
+        ops._call("b200p_peer_allgather", lambda: _lib.lib().b200p_peer_allgather(
+            self._tab[2], self._tab[3], self.world, self.rank, dst.data_ptr(), B * 16, ops._stream()))
+
+    def status(self) -> int:
+        import ctypes as C
+        from . import _lib, ops
+        out = C.c_uint32(0)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200p_peer_status(self._base + self._off[3], C.byref(out), ops._stream()), "b200p_peer_status")
+        return int(out.value)
+
+    def close(self):
+        if self._closed:
+            return
+        self._closed = True
+        from ._lib import lib
+        try:
+            with torch.cuda.device(self.device):
+                torch.cuda.synchronize()
+                for p, b in enumerate(self._peer_base):
+                    if p != self.rank:
+                        lib().b200p_ipc_close(b)
+                lib().b200p_symm_free(self._base)
+        except Exception:
+            pass
+
+    def __del__(self):
+        self.close()
+
+
+def attach(model, dist, rank: int, world: int, group=None, allreduce: Optional[Callable] = None, fused: Optional[bool] = None):
     """Wire a model whose weights are this rank's shards (shard_weights) to the process group:
     one all-reduce(sum) of the fp32 residual stream after o_proj and after down_proj, and the
     vocab-parallel sampling head.  ``allreduce(t)`` may be supplied (e.g. the fused NVLink kernel);
-    the default is ``dist.all_reduce`` (NCCL ring/NVLS on the GPUs, gloo in CPU tests)."""
+    the default on GPUs is the fused peer-memory exchange (``PeerExchange``: all-reduce + residual + next RMSNorm in
+    one kernel, ``fused=True``); ``fused=False`` / ``B200P_TP_FUSED=0`` keeps ``dist.all_reduce`` (NCCL ring/NVLS on
+    the GPUs, gloo in CPU tests) as the baseline."""
     if world == 1:
         return model
+    import os
+    if fused is None:
+        fused = (allreduce is None and torch.device(model.device).type == "cuda" and world in (2, 4, 8)
+                 and os.environ.get("B200P_TP_FUSED", "1") != "0")
     if allreduce is None:
         def allreduce(t):
             dist.all_reduce(t, group=group)
@@ -154,6 +273,13 @@ def attach(model, dist, rank: int, world: int, group=None, allreduce: Optional[C
     probe = torch.zeros((8,), dtype=torch.float32, device=model.device)
     allreduce(probe)
     model.set_tensor_parallel(rank, world, allreduce)
+    old = getattr(model, "_tp_fused", None)
+    if old is not None:
+        old.close()
+    model._tp_fused = None
+    if fused:
+        from .models._transformer import MAX_TOKENS_PER_FORWARD
+        model._tp_fused = PeerExchange(dist, group, rank, world, model.device, MAX_TOKENS_PER_FORWARD, model.args.hidden_size)
     sharded_vocab = model.lm_head is not None
     v0 = rank * model.lm_head.out_features if sharded_vocab else 0
     head = TensorParallelHead(model, dist, group, rank, world, v0, sharded_vocab)
