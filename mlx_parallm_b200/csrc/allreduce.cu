@@ -71,25 +71,34 @@ __device__ __forceinline__ float block_sum_ar(float v, float* sh) {
   return r;
 }
 
-// cross-rank handshake of CTA `cta`: returns when every peer's CTA `cta` has entered the same exchange
+__device__ __forceinline__ uint32_t ld_relaxed_sys_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// cross-rank handshake of CTA `cta`: returns when every peer's CTA `cta` has entered the same exchange.
+// One release store per peer (the partial buffer was completed by the PREVIOUS kernel, so st.release.sys is the only
+// fence needed on the way out), relaxed polling, one acquire fence on the way in.
 __device__ __forceinline__ void peer_handshake(const ArPeers& pe, int W, int rank, int cta, uint32_t* status) {
   if (threadIdx.x < 32) {
     const int t = threadIdx.x;
     uint32_t* mine = pe.flags[rank] + (size_t)cta * AR_MAX_WORLD;
     uint32_t e = 0;
-    if (t < W) e = ld_acquire_sys(mine + rank) + 1u;     // my own slot holds my last epoch
-    __syncwarp();                                        // every lane has read it before lane `rank` overwrites it
+    if (t < W) e = ld_relaxed_sys_u32(mine + rank) + 1u;   // my own slot holds my last epoch
+    __syncwarp();                                          // every lane has read it before lane `rank` overwrites it
     if (t < W) {
-      __threadfence_system();
       st_release_sys(pe.flags[t] + (size_t)cta * AR_MAX_WORLD + rank, e);
-      const unsigned long long t0 = globaltimer_ns();
+      unsigned long long t0 = 0;
       uint32_t spins = 0;
-      while ((int32_t)(ld_acquire_sys(mine + t) - e) < 0) {
-        if ((++spins & 0x3ffu) == 0 && globaltimer_ns() - t0 > 4000000000ull) {
-          atomicExch(status, 1u);
-          break;
+      while ((int32_t)(ld_relaxed_sys_u32(mine + t) - e) < 0) {
+        if ((++spins & 0xfffu) == 0) {
+          const unsigned long long now = globaltimer_ns();
+          if (t0 == 0) t0 = now;
+          else if (now - t0 > 4000000000ull) { atomicExch(status, 1u); break; }
         }
       }
+      asm volatile("fence.acq_rel.sys;" ::: "memory");
     }
     __syncwarp();
   }
@@ -232,6 +241,10 @@ static int fill_peers(ArPeers& pe, const void* const* partial, void* const* flag
 }
 
 static int g_ar_max_ctas = 0;     // 0 = auto (co-resident capacity of the device)
+// Programmatic dependent launch of the exchange kernel (B200P_AR_PDL=1).  Off by default: measured on 2 x B200 it makes the
+// decode step SLOWER (3.43 -> 3.70 ms at B=64, T=256) -- the early-launched exchange CTAs spin in the handshake and keep the
+// next projection's persistent one-CTA-per-SM GEMM off their SMs.
+static int g_ar_pdl = [] { const char* e = getenv("B200P_AR_PDL"); return e ? atoi(e) : 0; }();
 extern "C" int b200p_allreduce_set_max_ctas(int n) {
   B200P_REQUIRE(n >= 0 && n < B200P_AR_MAX_CTAS, B200P_ERR_ARG, "max ctas must be in [0, %d)", B200P_AR_MAX_CTAS);
   g_ar_max_ctas = n;
@@ -276,7 +289,7 @@ extern "C" int b200p_allreduce_residual_rmsnorm(const void* const* peer_partial,
     if ((int64_t)occ_ * sm_count() < cap) cap = (int64_t)occ_ * sm_count();                                          \
     if (g_ar_max_ctas > 0 && g_ar_max_ctas < cap) cap = g_ar_max_ctas;                                               \
     const unsigned grid = (unsigned)(M < cap ? M : cap);                                                             \
-    launch_pdl(allreduce_residual_rmsnorm_kernel<T, W_>, grid, AR_THREADS, smem, st, pe, rank, status, h,            \
+    launch_pdl_opt(g_ar_pdl != 0, allreduce_residual_rmsnorm_kernel<T, W_>, grid, AR_THREADS, smem, st, pe, rank, status, h, \
                (const T*)norm_w, (T*)y, zero_buf, M, H, ld_partial, eps, perm);                                      \
   } while (0)
 #define AR_DISPATCH_W(T)                                                                          \
