@@ -97,6 +97,8 @@ int b200p_qmm_tensor_supported(int64_t M, int64_t N, int64_t K, int group_size, 
                                int epilogue);
 /* force a path for tests/benchmarks: 0 = auto, 1 = GEMV only, 2 = tensor only (error if unsupported) */
 int b200p_qmm_set_path(int path);
+/* smallest M routed to the tensor path in auto mode (default 5; measured crossover, scripts/qmm_sweep.py) */
+int b200p_qmm_set_min_tensor_m(int m);
 
 /* mx.fast.rms_norm(x, w, eps)                                      [nn.RMSNorm: models/llama.py:187,
  * 189,231]  x float [M,H] (the fp32 residual stream) -> y `dtype` [M,H]; w `dtype` [H]. */
@@ -192,6 +194,13 @@ int b200p_allreduce_set_max_ctas(int n);
 int b200p_allreduce_residual_rmsnorm(const void* const* peer_partial, void* const* peer_flags, int world, int rank,
                                      float* h, const void* norm_w, void* y, float* zero_buf, int64_t M, int64_t H,
                                      int64_t ld_partial, float eps, int dtype, int flags, void* stream);
+/* Two-shot variant with a ROW-SHARDED residual stream (csrc/allreduce.cu): rank r owns rows [r*rpr, (r+1)*rpr), rpr =
+ * ceil(M/world); it pulls only its rows of the partials, updates its rows of h (other rows of h go stale on this rank) and
+ * pushes rms_norm(h rows) into EVERY rank's x buffer (peer_x[p]: `dtype` [M,H] as mapped here).  1/world of the one-shot
+ * traffic; two handshakes.  norm_w is required (x is the product).  Same calling discipline as above. */
+int b200p_allreduce_rows_rmsnorm(const void* const* peer_partial, void* const* peer_x, void* const* peer_flags,
+                                 int world, int rank, float* h, const void* norm_w, float* zero_buf, int64_t M,
+                                 int64_t H, int64_t ld_partial, float eps, int dtype, int flags, void* stream);
 /* dst[p * bytes_per_rank ...] = peer p's src block, through peer memory (vocab-parallel greedy head: the W records of
  * b200p_argmax_partial, then b200p_argmax_merge).  bytes_per_rank % 16 == 0. */
 int b200p_peer_allgather(const void* const* peer_src, void* const* peer_flags, int world, int rank, void* dst,

@@ -32,6 +32,7 @@ SIGNATURES = {
     "b200p_qmm_workspace_bytes": (_sz, [_i64, _i64, _i64]),
     "b200p_qmm_tensor_supported": (_i32, [_i64, _i64, _i64, _i32, _i32, _i32, _i32]),
     "b200p_qmm_set_path": (_i32, [_i32]),
+    "b200p_qmm_set_min_tensor_m": (_i32, [_i32]),
     "b200p_rmsnorm": (_i32, [_vp, _vp, _vp, _i64, _i64, _f32, _i32, _i32, _vp]),
     "b200p_rope_kv_append": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i32, _i32, _i32, _i64,
                                     _f32, _f32, _f32, _i32, _i32, _vp]),
@@ -52,6 +53,7 @@ SIGNATURES = {
     "b200p_allreduce_flag_bytes": (_sz, []),
     "b200p_allreduce_set_max_ctas": (_i32, [_i32]),
     "b200p_allreduce_residual_rmsnorm": (_i32, [_vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _f32, _i32, _i32, _vp]),
+    "b200p_allreduce_rows_rmsnorm": (_i32, [_vp, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _i64, _i64, _i64, _f32, _i32, _i32, _vp]),
     "b200p_peer_allgather": (_i32, [_vp, _vp, _i32, _i32, _vp, _i64, _vp]),
     "b200p_peer_status": (_i32, [_vp, _vp, _vp]),
 }

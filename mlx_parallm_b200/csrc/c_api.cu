@@ -28,6 +28,7 @@ int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b
                   int64_t K, int64_t ldx, int64_t ldy, int bits, int dtype, int epi, int flags, void* ws, size_t ws_bytes,
                   cudaStream_t st);
 size_t qmm_tc_workspace_bytes(int64_t M, int64_t N, int64_t K);
+void qmm_tc_set_min_m(int m);
 int attn_generic_launch(const void* q, const void* kc, const void* vc, const int32_t* lengths, void* out,
                         int64_t B, int64_t L, int Hq, int Hkv, int D, int64_t Tcap, float scale, int dtype,
                         int out_perm, cudaStream_t st);
@@ -87,6 +88,12 @@ extern "C" int b200p_sm_count(void) {
 
 extern "C" int b200p_set_pdl(int enabled) {
   g_pdl = enabled;
+  return B200P_OK;
+}
+
+extern "C" int b200p_qmm_set_min_tensor_m(int m) {
+  B200P_REQUIRE(m >= 1, B200P_ERR_ARG, "min tensor-path M must be >= 1");
+  qmm_tc_set_min_m(m);
   return B200P_OK;
 }
 

@@ -759,7 +759,10 @@ static EncodeTiledFn get_encode() {
 constexpr int SMEM_BUDGET = 227 * 1024;
 constexpr int SMEM_FIXED = 1024 /*align*/ + NSB * SB_SLOT_BYTES + EPI_NBUF * EPI_BUF_BYTES + 512 /*barriers*/;
 static_assert(8 * (4 * MAX_STAGES + 2 * NSLOT + 2 * NSB + 4) + 8 <= 512, "barrier block overflows its slot");
-constexpr int MIN_TC_M = 5;        // below this the CUDA-core GEMV wins (weights read once either way)
+// smallest M that takes the tensor path (below it: the CUDA-core GEMV).  Evidence: scripts/qmm_sweep.py, profiles/*qmm_sweep*.
+// B200P_MIN_TC_M / b200p_qmm_set_min_tensor_m override it.
+static int g_min_tc_m = [] { const char* e = getenv("B200P_MIN_TC_M"); return e ? atoi(e) : 5; }();
+void qmm_tc_set_min_m(int m) { g_min_tc_m = m < 1 ? 1 : m; }
 constexpr int MIN_UNITS_PER_CTA = 2;
 
 struct TcPlan {
@@ -793,7 +796,7 @@ bool qmm_tc_supported(int64_t M, int64_t N, int64_t K, int gs, int bits, int dty
   if (gs != 64) return false;
   if (dtype != B200P_F16 && dtype != B200P_BF16) return false;
   if (bits == 8 && dtype == B200P_BF16) return false;        // 128 + q is not exact in bf16 for q >= 128
-  if (M < MIN_TC_M) return false;
+  if (M < g_min_tc_m) return false;
   if (K % 64 != 0 || (K * bits / 8) % 16 != 0) return false;
   if (N % 8 != 0) return false;
   if (epi == B200P_EPI_SILU_MUL && (N / 2) % 8 != 0) return false;
@@ -809,7 +812,7 @@ static size_t ws_counter_bytes(int64_t M, int64_t N) {
 
 size_t qmm_tc_workspace_bytes(int64_t M, int64_t N, int64_t K) {
   (void)K;
-  if (M < MIN_TC_M) return 0;
+  if (M < 1) return 0;
   const int64_t tn = M >= MAX_TN ? MAX_TN : ((M + 15) / 16) * 16;
   // per-tile arrival counters + one fp32 [2*TN x 128] accumulator per CTA boundary; all must be ZERO on first use
   // (the kernel leaves them zero)

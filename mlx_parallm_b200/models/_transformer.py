@@ -310,6 +310,9 @@ class DecoderModel:
                 ws=torch.zeros((ws_q,), dtype=torch.uint8, device=dev),
                 ws_attn=torch.empty((ws_a,), dtype=torch.uint8, device=dev),
             )
+            fx = getattr(self, "_tp_fused", None)
+            if fx is not None and fx.mode == "rows":
+                a["x"] = fx.x_view(M, dt)          # filled on every rank by the row-sharded exchange (tp.PeerExchange)
             if len(self._arenas) > 8:
                 self._arenas.clear()
             self._arenas[key] = a
@@ -329,6 +332,8 @@ class DecoderModel:
         fx = getattr(self, "_tp_fused", None) if tp else None      # peer-memory exchange (tp.PeerExchange) or NCCL
         layers = self.model.layers
         M = a["h"].shape[0]
+        rows_mode = fx is not None and fx.mode == "rows"
+        a["x_final"] = False
         for li, (layer, c) in enumerate(zip(layers, cache)):
             at, mlp = layer.self_attn, layer.mlp
             lengths = c.lengths(self.device)
@@ -349,7 +354,10 @@ class DecoderModel:
                 # all-reduce over NVLink + residual add + post-attention RMSNorm (and re-zeroes the other buffer)
                 at.o_proj(a["att"], EPI_ADD_RESIDUAL, out=fx.partial(0, M), workspace=a["ws"], x_perm=pm)
                 n2 = layer.post_attention_layernorm
-                fx.exchange(0, a["h"], n2.weight, a["x"], n2.eps, out_perm=pm)
+                if rows_mode:
+                    fx.exchange_rows(0, a["h"], n2.weight, n2.eps, out_perm=pm)
+                else:
+                    fx.exchange(0, a["h"], n2.weight, a["x"], n2.eps, out_perm=pm)
             else:
                 if tp and self.tp_rank != 0:
                     a["h"].zero_()
@@ -366,8 +374,15 @@ class DecoderModel:
             if fx is not None:
                 mlp.down_proj(a["act"], EPI_ADD_RESIDUAL, out=fx.partial(1, M), workspace=a["ws"], x_perm=pm)
                 nxt = layers[li + 1].input_layernorm if li + 1 < len(layers) else None
-                fx.exchange(1, a["h"], nxt.weight if nxt else None, a["x"] if nxt else None,
-                            nxt.eps if nxt else 0.0, out_perm=pm)
+                if rows_mode:
+                    # the residual stream is row-sharded: the last exchange applies the FINAL norm so that x (the only
+                    # tensor every rank holds completely) feeds the head directly
+                    nn_ = nxt if nxt is not None else self.model.norm
+                    fx.exchange_rows(1, a["h"], nn_.weight, nn_.eps, out_perm=pm)
+                    a["x_final"] = nxt is None
+                else:
+                    fx.exchange(1, a["h"], nxt.weight if nxt else None, a["x"] if nxt else None,
+                                nxt.eps if nxt else 0.0, out_perm=pm)
             else:
                 if tp and self.tp_rank != 0:
                     a["h"].zero_()
@@ -375,11 +390,16 @@ class DecoderModel:
                 if tp:
                     self._allreduce(a["h"])
 
-    def _head(self, h_rows: torch.Tensor, a: dict, logits_out: Optional[torch.Tensor] = None):
-        """final RMSNorm + lm_head / tied embed_tokens.as_linear (llama.py:231,249-252) -> float32 logits."""
+    def _head(self, h_rows: Optional[torch.Tensor], a: dict, logits_out: Optional[torch.Tensor] = None,
+              x_rows: Optional[torch.Tensor] = None):
+        """final RMSNorm + lm_head / tied embed_tokens.as_linear (llama.py:231,249-252) -> float32 logits.
+        ``x_rows``: rows already final-normalised (row-sharded TP exchange) -- the norm is skipped."""
         n = self.model.norm
-        rows = h_rows.shape[0]
-        x = ops.rmsnorm(h_rows, n.weight, n.eps, out=a["xl"][:rows], out_perm=self._perm8)
+        if x_rows is not None:
+            x = x_rows
+        else:
+            rows = h_rows.shape[0]
+            x = ops.rmsnorm(h_rows, n.weight, n.eps, out=a["xl"][:rows], out_perm=self._perm8)
         head = self.lm_head if self.lm_head is not None else self.model.embed_tokens
         return QuantizedLinear.__call__(head, x, EPI_STORE_F32, out=logits_out, workspace=a["ws"], x_perm=self._perm8)
 
@@ -404,12 +424,13 @@ class DecoderModel:
             chunk = ids[:, l0:l1].contiguous().view(-1)
             self._layers_forward(chunk, B, n, cache, a)
             advance_cache(cache, n)
+            src = a["x"] if a.get("x_final") else a["h"]      # row-sharded TP: x already holds final_norm(h) on every rank
             if last_only:
                 if l1 == L:
-                    last_h = a["h"] if n == 1 else a["h"].view(B, n, -1)[:, -1, :].contiguous()
-                    return self._head(last_h, a).view(B, 1, -1)
+                    last = src if n == 1 else src.view(B, n, -1)[:, -1, :].contiguous()
+                    return (self._head(None, a, x_rows=last) if a.get("x_final") else self._head(last, a)).view(B, 1, -1)
             else:
-                outs.append(self._head(a["h"], a).view(B, n, -1))
+                outs.append((self._head(None, a, x_rows=src) if a.get("x_final") else self._head(src, a)).view(B, n, -1))
         return outs[0] if len(outs) == 1 else torch.cat(outs, 1)
 
 

@@ -159,7 +159,7 @@ class PeerExchange:
     One device allocation per rank, mapped by every peer through cudaIpc handles shipped with
     ``dist.all_gather_object`` (host plumbing, once, at attach time):
 
-        [ partial A : max_rows x hidden f32 | partial B : same | records : 4096 x 16 B | flags ]
+        [ partial A : max_rows x hidden f32 | partial B : same | records : 4096 x 16 B | flags | x : max_rows x hidden ]
 
     ``partial(i, M)`` is the tensor a row-parallel projection accumulates into (``EPI_ADD_RESIDUAL``);
     ``exchange(i, ...)`` sums the W partials over NVLink in rank order, adds the residual stream, applies the next
@@ -167,7 +167,12 @@ class PeerExchange:
 
     REC_ROWS = 4096
 
-    def __init__(self, dist, group, rank: int, world: int, device, max_rows: int, hidden: int):
+    def __init__(self, dist, group, rank: int, world: int, device, max_rows: int, hidden: int, mode: Optional[str] = None):
+        import os
+        # "rows": two-shot, row-sharded residual stream, normalised rows pushed to every rank's x (1/W of the traffic);
+        # "oneshot": every rank pulls all W partials and keeps the whole residual stream
+        self.mode = mode or os.environ.get("B200P_TP_EXCHANGE", "rows")
+        assert self.mode in ("rows", "oneshot"), self.mode
         import ctypes as C
         from ._lib import check, lib
         self.rank, self.world, self.hidden, self.max_rows = rank, world, hidden, max_rows
@@ -176,8 +181,8 @@ class PeerExchange:
         part = max_rows * hidden * 4
         rec = self.REC_ROWS * 16
         flag_bytes = int(L.b200p_allreduce_flag_bytes())
-        self._off = (0, part, 2 * part, 2 * part + rec)
-        total = 2 * part + rec + flag_bytes
+        self._off = (0, part, 2 * part, 2 * part + rec, 2 * part + rec + flag_bytes)
+        total = 2 * part + rec + flag_bytes + part            # x region sized for float32 models too
         with torch.cuda.device(self.device):
             base = C.c_void_p()
             check(L.b200p_symm_alloc(C.byref(base), total), "b200p_symm_alloc")
@@ -199,6 +204,7 @@ class PeerExchange:
         self._local = [torch.as_tensor(_RawCuda(self._base + self._off[i], (max_rows, hidden), "<f4"), device=self.device)
                        for i in (0, 1)]
         self.records = torch.as_tensor(_RawCuda(self._base + self._off[2], (self.REC_ROWS, 4), "<f4"), device=self.device)
+        self._x_views = {}
         self._closed = False
         dist.barrier(group=group)          # every rank has mapped every buffer before anybody launches
 
@@ -218,6 +224,27 @@ class PeerExchange:
             0 if norm_w is None else norm_w.data_ptr(), 0 if y is None else y.data_ptr(),
             self._local[1 - which].data_ptr(), M, H, self.hidden, float(eps), dt,
             _lib.OUT_PERM8 if (out_perm and y is not None) else 0, ops._stream()))
+
+    def x_view(self, M: int, dtype: torch.dtype) -> torch.Tensor:
+        """[M, hidden] view of the peer-mapped GEMM-input buffer (what exchange_rows fills on every rank)."""
+        if M > self.max_rows:
+            raise ValueError(f"{M} rows exceed the peer buffer ({self.max_rows})")
+        if dtype not in self._x_views:
+            ts = {torch.float32: "<f4", torch.float16: "<f2", torch.bfloat16: "<i2"}[dtype]
+            t = torch.as_tensor(_RawCuda(self._base + self._off[4], (self.max_rows, self.hidden), ts), device=self.device)
+            self._x_views[dtype] = t.view(torch.bfloat16) if dtype == torch.bfloat16 else t
+        return self._x_views[dtype][:M]
+
+    def exchange_rows(self, which: int, h: torch.Tensor, norm_w: torch.Tensor, eps: float, out_perm: bool = False):
+        """Two-shot exchange: afterwards x_view(M, norm_w.dtype) holds rms_norm(h + sum of partials) on EVERY rank and
+        this rank's h holds the updated rows it owns (rows [rank*ceil(M/W), ...))."""
+        from . import _lib, ops
+        M, H = h.shape
+        assert H == self.hidden and h.dtype == torch.float32 and h.is_contiguous()
+        ops._call("b200p_allreduce_rows_rmsnorm", lambda: _lib.lib().b200p_allreduce_rows_rmsnorm(
+            self._tab[which], self._tab[4], self._tab[3], self.world, self.rank, h.data_ptr(), norm_w.data_ptr(),
+            self._local[1 - which].data_ptr(), M, H, self.hidden, float(eps), ops.dtype_code(norm_w.dtype),
+            _lib.OUT_PERM8 if out_perm else 0, ops._stream()))
 
     def allgather_records(self, B: int, dst: torch.Tensor):
         """dst [W, B, 4] <- every rank's records[:B] (written by b200p_argmax_partial)."""
@@ -280,6 +307,7 @@ def attach(model, dist, rank: int, world: int, group=None, allreduce: Optional[C
     if fused:
         from .models._transformer import MAX_TOKENS_PER_FORWARD
         model._tp_fused = PeerExchange(dist, group, rank, world, model.device, MAX_TOKENS_PER_FORWARD, model.args.hidden_size)
+    model._arenas.clear()          # arenas bind x to the peer-mapped buffer in "rows" mode
     sharded_vocab = model.lm_head is not None
     v0 = rank * model.lm_head.out_features if sharded_vocab else 0
     head = TensorParallelHead(model, dist, group, rank, world, v0, sharded_vocab)

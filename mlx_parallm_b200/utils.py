@@ -116,7 +116,10 @@ class _DecodeStep:
     def _body(self):
         m = self.model
         m._layers_forward(self.tok, self.B, 1, self.cache, self.arena)
-        m._head(self.arena["h"], self.arena, logits_out=self.logits)
+        if self.arena.get("x_final"):          # row-sharded TP exchange already produced final_norm(h) in x
+            m._head(None, self.arena, logits_out=self.logits, x_rows=self.arena["x"])
+        else:
+            m._head(self.arena["h"], self.arena, logits_out=self.logits)
         seen = set()
         for c in self.cache:
             if c._lengths.data_ptr() not in seen:

@@ -31,6 +31,8 @@ def main():
                                  intermediate_size=64 * world * 3), "bfloat16", 3, 9),
              ("small-llama", dict(num_key_value_heads=world, num_attention_heads=2 * world, hidden_size=256 * world,
                                   intermediate_size=512 * world), "float16", 64, 200)]
+    if os.environ.get("TP_CHECK_QUICK"):
+        cases = cases[:2]
     for fused in ([True, False] if os.environ.get("B200P_TP_FUSED", "1") != "0" else [False]):
         for name, ov, dtype, B, Lp in cases:
             cfg = synth.get_config(name, **ov)

@@ -34,7 +34,7 @@ def main():
     from mlx_parallm_b200 import _lib, ops, tp
     _lib.require_device()
     NX = 128
-    for M, H in [(64, 4096), (1, 4096), (128, 8192), (2048, 4096)]:
+    for M, H in [(64, 4096), (8, 4096), (1, 4096), (128, 8192), (2048, 4096)]:
         fx = tp.PeerExchange(dist, None, rank, world, f"cuda:{local}", max(M, 64), H)
         h = torch.zeros((M, H), dtype=torch.float32, device="cuda")
         y = torch.zeros((M, H), dtype=torch.float16, device="cuda")
@@ -45,13 +45,17 @@ def main():
             for i in range(n):
                 fx.exchange(i & 1, h, w, y, 1e-5, out_perm=True)
 
+        def rows_body():
+            for i in range(n):
+                fx.exchange_rows(i & 1, h, w, 1e-5, out_perm=True)
+
         def nccl_body():
             for i in range(n):
                 dist.all_reduce(h)
                 ops.rmsnorm(h, w, 1e-5, out=y, out_perm=True)
 
         res = {}
-        for name, body in (("fused", fused_body), ("nccl", nccl_body)):
+        for name, body in (("fused", fused_body), ("rows", rows_body), ("nccl", nccl_body)):
             body()
             torch.cuda.synchronize()
             g = torch.cuda.CUDAGraph()
@@ -62,7 +66,8 @@ def main():
         st = fx.status()
         if rank == 0:
             byt = world * M * H * 4
-            print(f"tp{world} M={M} H={H}: fused {res['fused']:.2f} us/exchange ({byt / res['fused'] / 1e3:.0f} GB/s peer reads), "
+            print(f"tp{world} M={M} H={H}: one-shot {res['fused']:.2f} us/exchange ({byt / res['fused'] / 1e3:.0f} GB/s peer reads), "
+                  f"rows (two-shot) {res['rows']:.2f} us, "
                   f"nccl all-reduce + rmsnorm {res['nccl']:.2f} us, status {st}", flush=True)
         del g
         fx.close()
