@@ -85,8 +85,8 @@ int b200p_embed(const int32_t* ids, const uint32_t* w, const void* scales, const
 /* mx.quantized_matmul(x, w, scales, biases, transpose=True)       [nn.QuantizedLinear.__call__:
  * models/llama.py:93,143,165,250-252; models/qwen3.py:63,115]
  * x `dtype` [M,K] row-major (ldx elements between rows), y per `epilogue` (ldy elements between
- * rows).  fp32 accumulation.  Internally: CUDA-core GEMV (any dtype) or the tcgen05 tile path
- * (F16/BF16, group 64, M >= tile threshold).  `workspace` (>= b200p_qmm_workspace_bytes) is
+ * rows).  fp32 accumulation.  Internally: the mma.sync register GEMV (4-bit g64, 16-bit, M <= 16, fp32 outputs), the
+ * tcgen05 tile path (F16/BF16, group 64) or the generic CUDA-core GEMV (any dtype / shape).  `workspace` (>= b200p_qmm_workspace_bytes) is
  * required by the split-K tensor path; may be NULL for the GEMV path. */
 int b200p_qmm(const void* x, const uint32_t* w, const void* scales, const void* biases, void* y,
               int64_t M, int64_t N, int64_t K, int64_t ldx, int64_t ldy, int group_size, int bits,
@@ -95,9 +95,10 @@ size_t b200p_qmm_workspace_bytes(int64_t M, int64_t N, int64_t K);
 /* 1 if the tcgen05 tile path can run this call, else 0 */
 int b200p_qmm_tensor_supported(int64_t M, int64_t N, int64_t K, int group_size, int bits, int dtype,
                                int epilogue);
-/* force a path for tests/benchmarks: 0 = auto, 1 = GEMV only, 2 = tensor only (error if unsupported) */
+/* force a path for tests/benchmarks: 0 = auto, 1 = CUDA-core GEMV only, 2 = tcgen05 tile kernel only, 3 = mma.sync
+ * GEMV only (2 and 3: error if the call is unsupported on that path) */
 int b200p_qmm_set_path(int path);
-/* smallest M routed to the tensor path in auto mode (default 5; measured crossover, scripts/qmm_sweep.py) */
+/* smallest M routed to the tensor path in auto mode (default 1: measured, scripts/qmm_sweep.py, profiles/r1_run11_qmm_sweep_gemv_vs_tensor.txt) */
 int b200p_qmm_set_min_tensor_m(int m);
 
 /* mx.fast.rms_norm(x, w, eps)                                      [nn.RMSNorm: models/llama.py:187,

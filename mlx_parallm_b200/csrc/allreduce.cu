@@ -14,12 +14,14 @@
 // x W x H x 4 bytes of reads per CTA keep enough loads in flight (1 MiB per peer at B=64, H=4096).
 //
 // Handshake (per CTA, no grid-wide sync): CTA c of rank r bumps its epoch e, stores e into slot [c][r] of EVERY peer's flag
-// array (st.release.sys after a system fence) and spins until its own slots [c][p] have all reached e (ld.acquire.sys).
+// array and spins until its own slots [c][p] have all reached e (relaxed system-scope accesses; see peer_handshake for
+// where a fence is and is not needed -- a MEMBAR.SYS per handshake doubled the exchange time).
 // A peer's CTA c signalling means the peer's kernel has started, i.e. (stream order, griddepcontrol.wait) its projection
 // has finished writing its partial buffer AND its previous exchange has finished reading ours -- which is what makes the
 // two-buffer rotation safe: partial buffers alternate A (o_proj) / B (down_proj); the exchange on A zeroes the local B
 // behind the handshake and vice versa, and a buffer is next written only after the following exchange's handshake.
 // A spin that sees no progress for ~4 s (peer died) sets status[0] = 1 and falls through instead of hanging the GPU.
+// Because CTA c waits for CTA c of every peer, a grid never exceeds what the device can hold resident at once.
 //
 // Algorithmic bytes per launch: W * M * H * 4 read (of which (W-1)/W over NVLink) + M * H * (4 + 4 + 2) local.
 #include "common.cuh"

@@ -29,6 +29,9 @@ int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b
                   cudaStream_t st);
 size_t qmm_tc_workspace_bytes(int64_t M, int64_t N, int64_t K);
 void qmm_tc_set_min_m(int m);
+bool qmv_mma_supported(int64_t M, int64_t N, int64_t K, int gs, int bits, int dtype, int epi);
+int qmv_mma_launch(const void* x, const uint32_t* w, const void* s, const void* b, void* y, int64_t M, int64_t N, int64_t K,
+                   int64_t ldx, int64_t ldy, int dtype, int epi, int flags, cudaStream_t st);
 int attn_generic_launch(const void* q, const void* kc, const void* vc, const int32_t* lengths, void* out,
                         int64_t B, int64_t L, int Hq, int Hkv, int D, int64_t Tcap, float scale, int dtype,
                         int out_perm, cudaStream_t st);
@@ -38,7 +41,13 @@ int attn_decode_launch(const void* q, const void* kc, const void* vc, const int3
                        int out_perm, void* ws, size_t ws_bytes, cudaStream_t st);
 size_t attn_decode_workspace_bytes(int64_t B, int64_t L, int Hq, int D);
 
-static int g_qmm_path = 0;   // 0 auto, 1 gemv, 2 tensor
+static int g_qmm_path = 0;   // 0 auto, 1 CUDA-core gemv, 2 tcgen05 tiles, 3 mma.sync gemv
+// Auto rule for the mma.sync GEMV, from the measured three-way sweep (profiles/r1_run12_qmm_sweep_three_paths.txt, us per
+// launch in a CUDA graph): it wins where the tile kernel's fixed cost dominates -- M <= 4 and matrices up to ~32 M weights
+// (q|k|v 6.4 vs 8.4 us, o_proj 5.2 vs 6.5 us at M = 1) -- and loses on the big streams (gate|up 23.9 vs 22.4 us) and as M
+// grows (its activation loads are per 16-row warp, not shared through shared memory).  The CUDA-core GEMV loses everywhere.
+static int g_gemv_max_m = [] { const char* e = getenv("B200P_GEMV_MAX_M"); return e ? atoi(e) : 4; }();
+static long long g_gemv_max_weights = [] { const char* e = getenv("B200P_GEMV_MAX_WEIGHTS"); return e ? atoll(e) : (1ll << 25); }();
 static int g_attn_path = 0;  // 0 auto, 1 generic, 2 tensor
 // 0 off, 1 every kernel, 2 only the tensor-path GEMM (B200P_PDL overrides the default at load time)
 static int g_pdl = [] { const char* e = getenv("B200P_PDL"); return e ? atoi(e) : 2; }();
@@ -98,13 +107,13 @@ extern "C" int b200p_qmm_set_min_tensor_m(int m) {
 }
 
 extern "C" int b200p_qmm_set_path(int path) {
-  B200P_REQUIRE(path >= 0 && path <= 2, B200P_ERR_ARG, "path must be 0..2");
+  B200P_REQUIRE(path >= 0 && path <= 3, B200P_ERR_ARG, "path must be 0..3");
   g_qmm_path = path;
   return B200P_OK;
 }
 
 extern "C" int b200p_attn_set_path(int path) {
-  B200P_REQUIRE(path >= 0 && path <= 2, B200P_ERR_ARG, "path must be 0..2");
+  B200P_REQUIRE(path >= 0 && path <= 3, B200P_ERR_ARG, "path must be 0..3");
   g_attn_path = path;
   return B200P_OK;
 }
@@ -143,6 +152,11 @@ extern "C" int b200p_qmm(const void* x, const uint32_t* w, const void* scales, c
   B200P_REQUIRE(ldy >= (epilogue == B200P_EPI_SILU_MUL ? N / 2 : N), B200P_ERR_ARG, "ldy too small");
   if (M == 0) return B200P_OK;
   cudaStream_t st = (cudaStream_t)stream;
+  const bool mma_ok = qmv_mma_supported(M, N, K, group_size, bits, dtype, epilogue) && aligned(y, 4) &&
+                      !(flags & B200P_Y_PERM8);
+  if (g_qmm_path == 3) B200P_REQUIRE(mma_ok, B200P_ERR_ARG, "mma.sync GEMV forced but unsupported for this call");
+  if (mma_ok && (g_qmm_path == 3 || (g_qmm_path == 0 && M <= g_gemv_max_m && N * K <= g_gemv_max_weights)))
+    return qmv_mma_launch(x, w, scales, biases, y, M, N, K, ldx, ldy, dtype, epilogue, flags, st);
   const bool tc_ok = qmm_tc_supported(M, N, K, group_size, bits, dtype, epilogue);
   if (g_qmm_path == 2) {
     B200P_REQUIRE(tc_ok, B200P_ERR_ARG, "tensor path forced but unsupported for this call");

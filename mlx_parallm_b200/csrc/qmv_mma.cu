@@ -1,0 +1,213 @@
+// Small-batch (M <= 16) fused-dequant GEMV of b200p_qmm for 4-bit group-64 weights and 16-bit activations:
+//
+//   y[m, n] (+)= sum_k x[m, k] * (q[n,k] * s[n, k/64] + b[n, k/64])
+//
+// Why this shape of kernel.  At M <= 16 the step is a pure weight stream (AI = 3.56*M flop/B).  The ALU budget at HBM speed is
+// ~2.8 lane-ops per weight (148 SMs x 128 lanes x 1.9 GHz / 13e12 weights/s); a CUDA-core GEMV needs >= 2 ops to unpack a
+// code to fp32 plus M FMAs (the old qmv kernel: 1.4-2.2 TB/s at M = 1, collapsing with M -- profiles/r1_run11_*), while the
+// dequant itself costs 1.5 ops per weight when done on packed half2 (LOP3 + exponent magic + one HFMA2 for q*s+b).  So the
+// dot products go to the tensor cores -- but with NO shared-memory / TMEM / mbarrier pipeline in front of them: every warp
+// streams its own 16 weight rows global -> registers with 128-bit no-allocate loads, dequantises in registers and feeds
+// mma.sync.m16n8k16 directly (weights = the 16-row A operand, the <= 8 tokens of an n-tile = the B operand, fp32 accumulators
+// in registers).  Legacy mma.sync is the right instruction here: it takes register operands, needs ~0.3 G issues/s per SM, and
+// the kernel has no fixed setup cost -- the tcgen05 tile kernel (qmm_tc.cu) pays ~7 us per launch before its first MMA.
+//
+// Mapping.  Lane (g = lane/4, t = lane%4) of a warp owns rows r0 = 16*rg + g and r0 + 8.  Per step of 256 k it loads the 32
+// packed bytes [64t, 64t+64) of both rows (the four lanes of a row read one 128-byte line; the 64 codes are ONE quantisation
+// group, so the lane needs one scale and one bias per row per step).  A 4-bit word unpacks with two masks into the pairs
+// (k0,k4)(k1,k5)(k2,k6)(k3,k7); pairs 0,1 are the lane's k-slots (2t,2t+1),(2t+8,2t+9) of one MMA, pairs 2,3 of the next --
+// the MMA's k index is just a label, as long as the B operand uses the same one: lane (g,t) supplies x[token g][same k], which
+// in the PERM8 activation layout is exactly one 16-byte chunk per word (natural layout: 4 PRMT per word to re-pair).
+// The D fragment leaves every (row, token) sum in exactly one lane: no shuffle reduction.
+// Split-K: K is cut into `splits` ranges so that ~16 warps per SM are in flight even for N = 4096; partial sums are combined
+// with fp32 red.global.add into y (ADD_RESIDUAL: y already holds the residual / the zeroed accumulator).
+//
+// Algorithmic HBM bytes per launch: N*K/2 + 2*N*(K/64)*2.
+#include "common.cuh"
+#include "dequant.cuh"
+
+namespace b200p {
+
+int sm_count();
+
+template <typename T>
+__device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  if constexpr (std::is_same<T, __half>::value) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  } else {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  }
+}
+
+constexpr int QM_WARPS = 4;
+constexpr int QM_STEP_K = 256;
+
+// NT: n-tiles of 8 tokens (M <= 8*NT).  ATOMIC: combine with red.add (ADD_RESIDUAL / split-K) else plain fp32 store.
+template <typename T, int NT, bool XPERM, bool ATOMIC>
+__global__ void __launch_bounds__(QM_WARPS * 32)
+qmv_mma_kernel(const T* __restrict__ x, const uint32_t* __restrict__ w, const T* __restrict__ scales,
+               const T* __restrict__ biases, float* __restrict__ y, int M, int64_t N, int64_t K, int64_t ldx, int64_t ldy,
+               int splits, int steps_per_split) {
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int64_t wid = (int64_t)blockIdx.x * QM_WARPS + (threadIdx.x >> 5);
+  const int64_t rg = wid / splits;
+  const int ks = (int)(wid - rg * splits);
+  if (rg * 16 >= N) return;
+  const int64_t r0 = rg * 16 + g, r1 = r0 + 8;
+  const int64_t wrow = K / 8;                 // uint32 words per weight row
+  const int64_t ng = K / 64;
+  const int64_t total_steps = K / QM_STEP_K;
+  const int64_t s_begin = (int64_t)ks * steps_per_split;
+  const int64_t s_end = min(total_steps, s_begin + steps_per_split);
+
+  float acc[NT][4];
+#pragma unroll
+  for (int n = 0; n < NT; ++n)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[n][j] = 0.f;
+
+  const uint32_t* w0 = w + r0 * wrow + 8 * t;     // 8 words = 64 codes per lane per step
+  const uint32_t* w1 = w + r1 * wrow + 8 * t;
+  const T* sc0 = scales + r0 * ng + t;
+  const T* sc1 = scales + r1 * ng + t;
+  const T* bi0 = biases + r0 * ng + t;
+  const T* bi1 = biases + r1 * ng + t;
+  const T* xr[NT];
+  bool xok[NT];
+#pragma unroll
+  for (int n = 0; n < NT; ++n) {
+    const int tok = n * 8 + g;
+    xok[n] = tok < M;
+    xr[n] = x + (int64_t)(xok[n] ? tok : 0) * ldx + 64 * t;
+  }
+
+  // weights, scales and biases never depend on the previous kernel: fetch the first step before griddepcontrol.wait
+  uint4 qa[2], qb[2];
+  uint32_t s2a = 0, b2a = 0, s2b = 0, b2b = 0;
+  auto fetch_w = [&](int64_t s) {
+    const int64_t wo = s * (QM_STEP_K / 8);
+    qa[0] = ldg_stream(w0 + wo);
+    qa[1] = ldg_stream(w0 + wo + 4);
+    qb[0] = ldg_stream(w1 + wo);
+    qb[1] = ldg_stream(w1 + wo + 4);
+    s2a = dup16(__ldg(sc0 + 4 * s));
+    b2a = dup16(__ldg(bi0 + 4 * s));
+    s2b = dup16(__ldg(sc1 + 4 * s));
+    b2b = dup16(__ldg(bi1 + 4 * s));
+  };
+  if (s_begin < s_end) fetch_w(s_begin);
+  pdl_wait();                                  // x is the previous kernel's output; y its accumulator
+
+  for (int64_t s = s_begin; s < s_end; ++s) {
+    const uint4 ca[2] = {qa[0], qa[1]}, cb[2] = {qb[0], qb[1]};
+    const uint32_t cs2a = s2a, cb2a = b2a, cs2b = s2b, cb2b = b2b;
+    // activations of this step: 64 k of the lane's token per n-tile, 8 chunks of 16 bytes
+    uint4 xv[NT][8];
+#pragma unroll
+    for (int n = 0; n < NT; ++n) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        if (xok[n]) xv[n][i] = *reinterpret_cast<const uint4*>(xr[n] + s * QM_STEP_K + 8 * i);
+        else xv[n][i] = make_uint4(0u, 0u, 0u, 0u);
+      }
+    }
+    if (s + 1 < s_end) fetch_w(s + 1);          // next step's weights are in flight during this step's math
+    const uint32_t* pa = reinterpret_cast<const uint32_t*>(ca);
+    const uint32_t* pb = reinterpret_cast<const uint32_t*>(cb);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      uint32_t da[4], db[4];
+      dequant8<T, 4, true>(pa + i, cs2a, cb2a, da);      // pairs (k0,k4) (k1,k5) (k2,k6) (k3,k7) of word i, row r0
+      dequant8<T, 4, true>(pb + i, cs2b, cb2b, db);      // same, row r0 + 8
+      const uint32_t a_lo[4] = {da[0], db[0], da[1], db[1]};
+      const uint32_t a_hi[4] = {da[2], db[2], da[3], db[3]};
+#pragma unroll
+      for (int n = 0; n < NT; ++n) {
+        uint4 u = xv[n][i];
+        if constexpr (!XPERM) {                           // natural order -> (x0,x4) (x1,x5) (x2,x6) (x3,x7)
+          const uint4 v = u;
+          u.x = prmt(v.x, v.z, 0x5410u);
+          u.y = prmt(v.x, v.z, 0x7632u);
+          u.z = prmt(v.y, v.w, 0x5410u);
+          u.w = prmt(v.y, v.w, 0x7632u);
+        }
+        mma16816<T>(acc[n], a_lo, u.x, u.y);
+        mma16816<T>(acc[n], a_hi, u.z, u.w);
+      }
+    }
+  }
+  pdl_launch_dependents();
+  // D fragment: acc[n][0], [1] = (row r0, tokens 8n + 2t, 2t+1); acc[n][2], [3] = (row r0 + 8, same tokens)
+#pragma unroll
+  for (int n = 0; n < NT; ++n) {
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int tok = n * 8 + 2 * t + j;
+      if (tok < M) {
+        float* yr = y + (int64_t)tok * ldy;
+        if (ATOMIC) {
+          atomicAdd(yr + r0, acc[n][j]);
+          atomicAdd(yr + r1, acc[n][2 + j]);
+        } else {
+          yr[r0] = acc[n][j];
+          yr[r1] = acc[n][2 + j];
+        }
+      }
+    }
+  }
+}
+
+bool qmv_mma_supported(int64_t M, int64_t N, int64_t K, int gs, int bits, int dtype, int epi) {
+  if (bits != 4 || gs != 64) return false;
+  if (dtype != B200P_F16 && dtype != B200P_BF16) return false;
+  if (M < 1 || M > 16) return false;
+  if (K % QM_STEP_K != 0 || N % 16 != 0) return false;
+  return epi == B200P_EPI_STORE_F32 || epi == B200P_EPI_ADD_RESIDUAL;
+}
+
+template <typename T>
+static int launch_qmv_mma(const void* x, const uint32_t* w, const void* s, const void* b, void* y, int64_t M, int64_t N,
+                          int64_t K, int64_t ldx, int64_t ldy, int epi, bool xperm, cudaStream_t st) {
+  const int64_t row_groups = N / 16;
+  const int64_t total_steps = K / QM_STEP_K;
+  // enough warps to cover the HBM latency on every SM (~16 per SM); plain stores cannot be split
+  int64_t splits = 1;
+  if (epi == B200P_EPI_ADD_RESIDUAL) {
+    const int64_t want = (int64_t)sm_count() * 16;
+    splits = (want + row_groups - 1) / row_groups;
+    if (splits > total_steps / 2) splits = total_steps / 2;     // at least two steps per warp
+    if (splits < 1) splits = 1;
+  }
+  const int64_t sps = (total_steps + splits - 1) / splits;
+  splits = (total_steps + sps - 1) / sps;
+  const int64_t warps = row_groups * splits;
+  dim3 grid((unsigned)((warps + QM_WARPS - 1) / QM_WARPS)), block(QM_WARPS * 32);
+  const bool atomic = epi == B200P_EPI_ADD_RESIDUAL;
+#define GO(NT_, XP_, AT_)                                                                                                \
+  launch_pdl(qmv_mma_kernel<T, NT_, XP_, AT_>, grid, block, 0, st, (const T*)x, w, (const T*)s, (const T*)b, (float*)y,   \
+             (int)M, N, K, ldx, ldy, (int)splits, (int)sps)
+  if (M <= 8) {
+    if (xperm) { if (atomic) GO(1, true, true); else GO(1, true, false); }
+    else { if (atomic) GO(1, false, true); else GO(1, false, false); }
+  } else {
+    if (xperm) { if (atomic) GO(2, true, true); else GO(2, true, false); }
+    else { if (atomic) GO(2, false, true); else GO(2, false, false); }
+  }
+#undef GO
+  B200P_LAUNCH_CHECK("qmv_mma_kernel");
+  return B200P_OK;
+}
+
+int qmv_mma_launch(const void* x, const uint32_t* w, const void* s, const void* b, void* y, int64_t M, int64_t N, int64_t K,
+                   int64_t ldx, int64_t ldy, int dtype, int epi, int flags, cudaStream_t st) {
+  B200P_REQUIRE(aligned(s, 2) && aligned(b, 2) && aligned(y, 4), B200P_ERR_ALIGN, "bad alignment");
+  const bool xperm = (flags & B200P_X_PERM8) != 0;
+  if (dtype == B200P_F16) return launch_qmv_mma<__half>(x, w, s, b, y, M, N, K, ldx, ldy, epi, xperm, st);
+  return launch_qmv_mma<__nv_bfloat16>(x, w, s, b, y, M, N, K, ldx, ldy, epi, xperm, st);
+}
+
+}  // namespace b200p

@@ -171,7 +171,11 @@ class PeerExchange:
         import os
         # "rows": two-shot, row-sharded residual stream, normalised rows pushed to every rank's x (1/W of the traffic);
         # "oneshot": every rank pulls all W partials and keeps the whole residual stream
-        self.mode = mode or os.environ.get("B200P_TP_EXCHANGE", "rows")
+        # measured (profiles/r1_run10_*): TP=2 one-shot 9.2 us vs rows 13.8 us at M=64; TP=8 23.7 us both at M=64 but
+        # rows 175 us vs one-shot 383 us at M=2048 and 2.93 vs 3.05 ms per decode step -> rows from TP=4 up
+        self.mode = mode or os.environ.get("B200P_TP_EXCHANGE", "auto")
+        if self.mode == "auto":
+            self.mode = "rows" if world >= 4 else "oneshot"
         assert self.mode in ("rows", "oneshot"), self.mode
         import ctypes as C
         from ._lib import check, lib

@@ -18,7 +18,7 @@ shapes = [(6144, 4096, 2), (4096, 4096, 2), (28672, 4096, 2), (4096, 14336, 2), 
 Ms = [1, 2, 4, 8, 16, 64]
 if len(sys.argv) > 1:
     Ms = [int(v) for v in sys.argv[1].split(",")]
-print("N K epi M : gemv_us (GB/s) | tensor_us (GB/s)")
+print("N K epi M : cuda-core gemv us (GB/s) | tcgen05 tiles us (GB/s) | mma.sync gemv us (GB/s)")
 for N, K, epi in shapes:
     ncopy = 4 if N * K < 2e8 else 2
     mats = []
@@ -33,9 +33,9 @@ for N, K, epi in shapes:
         ws = torch.zeros((max(ops.qmm_workspace_bytes(max(M, 8), N, K), 16),), dtype=torch.uint8, device="cuda")
         out = torch.zeros((M, N), device="cuda", dtype=torch.float32)
         res = []
-        for path in (1, 2):
+        for path in (1, 2, 3):
             _lib.check(L.b200p_qmm_set_path(path))
-            if path == 2 and not L.b200p_qmm_tensor_supported(M, N, K, 64, 4, 1, epi):
+            if (path == 2 and not L.b200p_qmm_tensor_supported(M, N, K, 64, 4, 1, epi)) or (path == 3 and M > 16) or (path == 1 and M > 16):
                 res.append(float("nan"))
                 continue
             reps = 8
@@ -60,6 +60,6 @@ for N, K, epi in shapes:
             res.append(e0.elapsed_time(e1) * 1e3 / (3 * reps * len(mats)))
             del gr
         _lib.check(L.b200p_qmm_set_path(0))
-        print(f"{N} {K} {epi} {M} : {res[0]:.1f} ({wbytes / res[0] / 1e3:.0f}) | {res[1]:.1f} ({wbytes / res[1] / 1e3:.0f})", flush=True)
+        print(f"{N} {K} {epi} {M} : " + " | ".join(f"{r:.1f} ({wbytes / r / 1e3:.0f})" for r in res), flush=True)
     del mats
     torch.cuda.empty_cache()

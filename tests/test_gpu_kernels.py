@@ -288,6 +288,32 @@ def test_qmm_tensor_path_is_repeatable_and_matches_gemv(ops):
     assert rel_err(a1, g) < 1e-3
 
 
+# ---------------------------------------------------------------- mma.sync register GEMV of b200p_qmm (M <= 16)
+MMA_CASES = [  # M, N, K, dtype, epilogue (1 = fp32 store, 2 = += into fp32, split-K with red.add)
+    (1, 256, 256, "float16", 1), (3, 512, 1024, "float16", 2), (8, 96, 512, "bfloat16", 1), (9, 1024, 4096, "float16", 2),
+    (16, 2048, 256, "bfloat16", 2), (5, 64, 768, "float16", 1), (2, 4096, 4096, "float16", 2), (13, 160, 1280, "float16", 1),
+]
+
+
+@pytest.mark.parametrize("M,N,K,dtype,epi", MMA_CASES)
+def test_qmm_mma_gemv_matches_oracle(ops, M, N, K, dtype, epi):
+    got, exp = qmm_case(ops, M, N, K, 4, dtype, epi, seed=M + N + K, path=3, ragged_ld=(M == 5))
+    tol = {"float16": 3e-3, "bfloat16": 2e-2}[dtype]     # A = storage-rounded q*s+b, fp32 accumulation in the MMA
+    assert rel_err(got, exp) < tol
+
+
+def test_qmm_mma_gemv_agrees_with_the_other_paths_and_is_the_auto_choice(ops):
+    from mlx_parallm_b200 import _lib
+    m, _ = qmm_case(ops, 4, 512, 2048, 4, "float16", 1, seed=9, path=3)
+    t, _ = qmm_case(ops, 4, 512, 2048, 4, "float16", 1, seed=9, path=2) if \
+        _lib.lib().b200p_qmm_tensor_supported(4, 512, 2048, 64, 4, 1, 1) else (m, None)
+    g, _ = qmm_case(ops, 4, 512, 2048, 4, "float16", 1, seed=9, path=1)
+    a, _ = qmm_case(ops, 4, 512, 2048, 4, "float16", 1, seed=9, path=0)
+    assert rel_err(m, t) < 1e-5 and rel_err(m, g) < 1e-3
+    assert np.array_equal(a, m)                          # small matrix, M <= 4: auto == the mma.sync GEMV, bit for bit
+    assert _lib.lib().b200p_qmm_set_path(4) == -1
+
+
 # ---------------------------------------------------------------- split-K tensor decode attention
 @pytest.mark.parametrize("dtype,Hq,Hkv,lengths", [
     ("float16", 8, 2, [0, 5, 130]),             # ragged rows incl. an empty cache (only the new token)

@@ -82,6 +82,7 @@ def _qmm_inputs(M, N, K, dtype, seed):
 @pytest.mark.parametrize("M,N,K,dtype,path", [
     (64, 1024, 512, "float16", 2), (16, 512, 1024, "bfloat16", 2), (64, 256, 4096, "float16", 2),   # tensor path
     (3, 128, 256, "float16", 1), (8, 96, 512, "bfloat16", 1),                                       # GEMV path
+    (3, 128, 256, "float16", 3), (12, 512, 1024, "bfloat16", 3), (1, 64, 4096, "float16", 3),       # mma.sync GEMV
 ])
 def test_qmm_x_perm8_equals_natural(ops, M, N, K, dtype, path):
     from mlx_parallm_b200 import _lib
