@@ -244,6 +244,40 @@ def run_workload(name, model, cfg, steps, warmup, tp_world, dist, with_profile, 
     return res
 
 
+def time_prefill(model, cfg, B, Lp, reps=3, dist=None):
+    """prefill tok/s = B * Lp / t_first_token (utils.py:533-537): the eager chunked prefill of a [B, Lp] prompt batch through
+    the public Model.__call__ (last-position logits) + greedy sample, device-timed, max over ranks."""
+    import torch
+    g = torch.Generator(device=model.device)
+    g.manual_seed(11)
+    ids = torch.randint(0, cfg["vocab_size"], (B, Lp), generator=g, device=model.device)
+    cache = model.make_cache(B, step=Lp + 8)
+    times = []
+    for r in range(reps + 1):
+        for c in cache:
+            c.reset(B)
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        logits = model(ids, cache=cache, last_only=True)[:, -1, :]
+        tok = torch.empty((B,), dtype=torch.int32, device=model.device)
+        model.greedy_tokens(logits.contiguous(), tok)
+        e1.record()
+        torch.cuda.synchronize()
+        if r > 0:
+            times.append(e0.elapsed_time(e1))
+    ms = min(times)
+    if dist is not None:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    del cache
+    torch.cuda.empty_cache()
+    return {"batch": B, "prompt_len": Lp, "ms": ms, "tok_s": B * Lp / ms * 1e3}
+
+
 # ------------------------------------------------------------------------------------------ CPU arm
 def cpu_reference(cfg_name, B, T, budget_layers=1, repeats=1, seed=1234):
     """The oracle (numpy restatement of the reference's decode step) timed on the host cores on a bounded
@@ -296,6 +330,7 @@ def main():
     ap.add_argument("--workload", default=HEADLINE)
     ap.add_argument("--sweep", default=",".join(DEFAULT_SWEEP), help="comma list of extra workloads ('' = none)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-prefill", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
@@ -357,6 +392,12 @@ def main():
             sweep.append({k: r[k] for k in ("workload", "ms_per_step", "tok_s", "step_frac_of_hbm_peak")})
         except Exception as ex:  # a sweep entry must not sink the headline line
             sweep.append({"workload": name, "error": str(ex)[:200]})
+    prefill = None
+    if not args.no_prefill:
+        try:
+            prefill = time_prefill(model, cfg, 8, 256, dist=dist)
+        except Exception as ex:
+            prefill = {"error": str(ex)[:200]}
     cb = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
@@ -382,7 +423,7 @@ def main():
                                     "step_frac_of_hbm_peak": main_res["step_frac_of_hbm_peak"],
                                     "step_frac_of_8TBs_nominal": main_res["step_gbs_per_gpu"] / 8000.0},
                 "kernels": {k: {"calls": v["calls_per_step"], "mean_us": round(v["mean_ms"] * 1e3, 2)} for k, v in main_res["kernels"].items()},
-                "clocks": clocks, "sweep": sweep}
+                "clocks": clocks, "sweep": sweep, "prefill": prefill}
         if cb is not None:
             line["cpu_baseline"] = cb
         emit(line)

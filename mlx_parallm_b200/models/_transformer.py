@@ -31,6 +31,10 @@ from .._lib import EPI_ADD_RESIDUAL, EPI_SILU_MUL, EPI_STORE, EPI_STORE_F32
 from .base import BatchedKVCache, PagedKVCache
 
 MAX_TOKENS_PER_FORWARD = 8192     # chunk size (B*L) of one prefill pass through the layers
+# Up to this many rows the fused q|k|v and gate|up projections accumulate in fp32 buffers (stream-K partial tiles are summed
+# by TMA reduce-adds, the consumer kernel rounds and re-zeroes).  Above it (prefill) few tiles are split, the fp32 buffers
+# would be HBM traffic (235 MB per layer at 2048 rows: silu_mul alone took 245 us), so the 16-bit fused epilogues are used.
+ACC32_MAX_ROWS = 64
 USE_PERM8 = True                  # 4-bit 16-bit models: GEMM inputs in the PERM8 column order (include/b200p.h)
 
 
@@ -47,10 +51,10 @@ class QuantizedLinear:
         self.out_features = weight.shape[0]
         self.in_features = weight.shape[1] * 32 // self.bits
 
-    def __call__(self, x, epilogue=EPI_STORE, out=None, workspace=None, x_perm=False):
+    def __call__(self, x, epilogue=EPI_STORE, out=None, workspace=None, x_perm=False, y_perm=False):
         lead = x.shape[:-1]
         y = ops.qmm(x.reshape(-1, x.shape[-1]), self.weight, self.scales, self.biases, self.group_size,
-                    self.bits, epilogue, out, workspace, x_perm=x_perm)
+                    self.bits, epilogue, out, workspace, x_perm=x_perm, y_perm=y_perm)
         return y if out is not None else y.reshape(*lead, -1)
 
 
@@ -300,8 +304,8 @@ class DecoderModel:
                 qkv=torch.empty((M, nqkv), dtype=dt, device=dev),
                 # fp32 split-K accumulation buffers of the fused q|k|v and gate|up projections (16-bit models): zero
                 # once, the consumer kernels (rope_kv_append, silu_mul) re-zero them behind their reads
-                qkv32=torch.zeros((M, nqkv), dtype=torch.float32, device=dev) if self._fast16 else None,
-                gu32=torch.zeros((M, 2 * inter_local), dtype=torch.float32, device=dev) if self._fast16 else None,
+                qkv32=torch.zeros((M, nqkv), dtype=torch.float32, device=dev) if self._fast16 and M <= ACC32_MAX_ROWS else None,
+                gu32=torch.zeros((M, 2 * inter_local), dtype=torch.float32, device=dev) if self._fast16 and M <= ACC32_MAX_ROWS else None,
                 q=torch.empty((M, att.n_heads * att.head_dim), dtype=dt, device=dev),
                 att=torch.empty((M, att.n_heads * att.head_dim), dtype=dt, device=dev),
                 act=torch.empty((M, inter_local), dtype=dt, device=dev),
@@ -327,7 +331,7 @@ class DecoderModel:
         # 16-bit models: (i) the fused projections accumulate in fp32 (stream-K partial tiles are summed by TMA
         # reduce-adds, no second pass) and the consumer kernel rounds to the storage type; (ii) with 4-bit weights the
         # GEMM inputs travel in the PERM8 column order the tensor path unpacks nibbles in.
-        f16 = self._fast16
+        f16 = self._fast16 and a["qkv32"] is not None
         pm = self._perm8
         fx = getattr(self, "_tp_fused", None) if tp else None      # peer-memory exchange (tp.PeerExchange) or NCCL
         layers = self.model.layers
@@ -342,7 +346,7 @@ class DecoderModel:
             if f16:
                 at.qkv_proj(a["x"], EPI_ADD_RESIDUAL, out=a["qkv32"], workspace=a["ws"], x_perm=pm)
             else:
-                at.qkv_proj(a["x"], EPI_STORE, out=a["qkv"], workspace=a["ws"])
+                at.qkv_proj(a["x"], EPI_STORE, out=a["qkv"], workspace=a["ws"], x_perm=pm)
             ops.rope_kv_append(a["qkv32"] if f16 else a["qkv"], a["q"], c.keys, c.values, lengths, B, L, at.n_heads,
                                at.n_kv_heads, at.head_dim, args.rope_theta, self.rope_scale,
                                at.q_norm.weight if at.q_norm else None, at.k_norm.weight if at.k_norm else None,
@@ -370,7 +374,7 @@ class DecoderModel:
                 mlp.gate_up_proj(a["x"], EPI_ADD_RESIDUAL, out=a["gu32"], workspace=a["ws"], x_perm=pm)
                 ops.silu_mul(a["gu32"], a["act"], out_perm=pm)
             else:
-                mlp.gate_up_proj(a["x"], EPI_SILU_MUL, out=a["act"], workspace=a["ws"])
+                mlp.gate_up_proj(a["x"], EPI_SILU_MUL, out=a["act"], workspace=a["ws"], x_perm=pm, y_perm=pm)
             if fx is not None:
                 mlp.down_proj(a["act"], EPI_ADD_RESIDUAL, out=fx.partial(1, M), workspace=a["ws"], x_perm=pm)
                 nxt = layers[li + 1].input_layernorm if li + 1 < len(layers) else None
