@@ -139,7 +139,8 @@ int b200p_attn(const void* q, const void* kcache, const void* vcache, const int3
                void* out, int64_t B, int64_t L, int Hq, int Hkv, int D, int64_t Tcap,
                float scale, int dtype, int flags, void* workspace, size_t workspace_bytes, void* stream);
 size_t b200p_attn_workspace_bytes(int64_t B, int64_t L, int Hq, int D);
-/* 0 = auto, 1 = generic CUDA-core kernel only, 2 = tensor (mma) split-K kernel only */
+/* 0 = auto, 1 = generic CUDA-core kernel only, 2 = tensor (mma) kernels only: split-K decode for L == 1, causal flash
+ * prefill for L > 1 (16-bit, head_dim 128) */
 int b200p_attn_set_path(int path);
 
 /* mx.argmax(logits, axis=-1, keepdims=True)                         [utils.py:350-352,363]

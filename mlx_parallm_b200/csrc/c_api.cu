@@ -40,6 +40,9 @@ int attn_decode_launch(const void* q, const void* kc, const void* vc, const int3
                        int64_t B, int64_t L, int Hq, int Hkv, int D, int64_t Tcap, float scale, int dtype,
                        int out_perm, void* ws, size_t ws_bytes, cudaStream_t st);
 size_t attn_decode_workspace_bytes(int64_t B, int64_t L, int Hq, int D);
+bool attn_prefill_supported(int64_t L, int Hq, int Hkv, int D, int dtype);
+int attn_prefill_launch(const void* q, const void* kc, const void* vc, const int32_t* lengths, void* out, int64_t B, int64_t L,
+                        int Hq, int Hkv, int D, int64_t Tcap, float scale, int dtype, int out_perm, cudaStream_t st);
 
 static int g_qmm_path = 0;   // 0 auto, 1 CUDA-core gemv, 2 tcgen05 tiles, 3 mma.sync gemv
 // Auto rule for the mma.sync GEMV, from the measured three-way sweep (profiles/r1_run12_qmm_sweep_three_paths.txt, us per
@@ -187,7 +190,10 @@ extern "C" int b200p_attn(const void* q, const void* kcache, const void* vcache,
   if (B * L == 0) return B200P_OK;
   cudaStream_t st = (cudaStream_t)stream;
   const bool tc_ok = attn_decode_supported(L, Hq, Hkv, D, dtype);
-  if (g_attn_path == 2) B200P_REQUIRE(tc_ok, B200P_ERR_ARG, "tensor attention forced but unsupported for this call");
+  const bool pf_ok = attn_prefill_supported(L, Hq, Hkv, D, dtype);
+  if (g_attn_path == 2) B200P_REQUIRE(tc_ok || pf_ok, B200P_ERR_ARG, "tensor attention forced but unsupported for this call");
+  if (pf_ok && g_attn_path != 1)
+    return attn_prefill_launch(q, kcache, vcache, lengths, out, B, L, Hq, Hkv, D, Tcap, scale, dtype, out_perm, st);
   if (tc_ok && g_attn_path != 1) {
     B200P_REQUIRE(workspace && workspace_bytes >= attn_decode_workspace_bytes(B, L, Hq, D), B200P_ERR_ARG,
                   "attention needs a workspace of %zu bytes", attn_decode_workspace_bytes(B, L, Hq, D));

@@ -215,6 +215,20 @@ def test_attention_generic_prefill_causal(ops):
     assert rel_err(got, exp) < 1.5e-3
 
 
+@pytest.mark.parametrize("dtype,B,L,Hq,Hkv,lengths", [
+    ("float16", 2, 70, 8, 2, [0, 37]),            # two query tiles per row, ragged cache offsets
+    ("bfloat16", 3, 9, 5, 1, [0, 4, 130]),        # fewer queries than a tile, G = 5
+    ("float16", 1, 200, 4, 4, [64]),              # several key tiles, MHA
+    ("float16", 2, 64, 8, 8, [0, 0]),             # exactly one query tile, pure causal
+])
+def test_attention_tensor_prefill_causal(ops, dtype, B, L, Hq, Hkv, lengths):
+    """mma.sync flash prefill (attn_prefill.cu) against the oracle's SDPA with the additive causal mask."""
+    got, exp = attn_case(ops, B, L, Hq, Hkv, 128, lengths, dtype, path=2)
+    assert rel_err(got, exp) < {"float16": 2e-3, "bfloat16": 1.2e-2}[dtype]
+    gen, _ = attn_case(ops, B, L, Hq, Hkv, 128, lengths, dtype, path=1)
+    assert rel_err(got, gen) < {"float16": 2e-3, "bfloat16": 1.2e-2}[dtype]
+
+
 # ---------------------------------------------------------------- samplers
 def test_argmax_ties_and_probs(ops):
     rng = np.random.default_rng(6)

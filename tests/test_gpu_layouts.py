@@ -49,10 +49,10 @@ def test_rmsnorm_perm8(ops, dtype):
     assert np.array_equal(from_perm8(per), nat)          # same values, permuted columns: bit-exact
 
 
-@pytest.mark.parametrize("path", [1, 2])
-def test_attention_perm8_output(ops, path):
+@pytest.mark.parametrize("path,L", [(1, 1), (2, 1), (2, 70)])
+def test_attention_perm8_output(ops, path, L):
     from mlx_parallm_b200 import _lib
-    B, L, Hq, Hkv, D, lengths = 3, 1, 8, 2, 128, [0, 50, 700]
+    B, Hq, Hkv, D, lengths = 3, 8, 2, 128, [0, 50, 700]
     nat, _ = attn_case(ops, B, L, Hq, Hkv, D, lengths, "float16", path=path, seed=2)
     rng = np.random.default_rng(2)
     Tcap = int(max(lengths)) + L + 3
