@@ -260,13 +260,8 @@ class DecoderModel:
 
     # -- sampling heads (overridden by the vocab-parallel variant in tp.py) ------------------------
     def graph_safe(self, B: int) -> bool:
-        """A decode step of batch B runs only graph-capturable b200p kernels (no interim dense GEMM)."""
-        if B <= ops.DENSE_INTERIM_MIN_M:
-            return True
-        head = self.lm_head if self.lm_head is not None else self.model.embed_tokens
-        from .._lib import lib
-        return bool(lib().b200p_qmm_tensor_supported(B, head.out_features, head.in_features, head.group_size,
-                                                    head.bits, ops.dtype_code(self.dtype), EPI_STORE_F32))
+        """Every kernel of a decode step is a graph-capturable b200p launch (there is no library or eager fallback)."""
+        return True
 
     def greedy_tokens(self, logits, tok_out, probs_out=None):
         """mx.argmax(logits, -1) (utils.py:352) into static buffers."""

@@ -112,37 +112,9 @@ def qmm(x, w, scales, biases, group_size=64, bits=4, epilogue=EPI_STORE, out=Non
         else:
             raise ValueError("EPI_ADD_RESIDUAL needs the residual tensor as `out`")
     epi_flags = epilogue | (_lib.X_PERM8 if x_perm else 0) | (_lib.Y_PERM8 if y_perm else 0)
-    if M > DENSE_INTERIM_MIN_M and not lib().b200p_qmm_tensor_supported(M, N, K, group_size, bits, dtype_code(x.dtype), epilogue):
-        if x_perm or y_perm:
-            raise _lib.B200PError("PERM8 layouts are not available on the interim dense path")
-        return _qmm_dense_interim(x, w, scales, biases, group_size, bits, epilogue, out)
     ws_ptr, ws_bytes = (0, 0) if workspace is None else (workspace.data_ptr(), workspace.numel() * workspace.element_size())
     _call(("b200p_qmm", N, K), lambda: lib().b200p_qmm(_p(x), _p(w), _p(scales), _p(biases), _p(out), M, N, K, x.stride(0), out.stride(0),
                           group_size, bits, dtype_code(x.dtype), epi_flags, ws_ptr, ws_bytes, _stream()))
-    return out
-
-
-# INTERIM (prefill only, SURVEY 8f-2 "next" row): until the tcgen05 tile kernel covers a shape, large-M
-# calls dequantise with our kernel and hand the dense GEMM to cuBLAS through torch.matmul.  The decode
-# hot path (M <= DENSE_INTERIM_MIN_M) never comes here.
-DENSE_INTERIM_MIN_M = 64
-
-
-def _qmm_dense_interim(x, w, scales, biases, group_size, bits, epilogue, out):
-    wd = dequantize(w, scales, biases, group_size, bits, mode=_lib.DQ_FMA)
-    if x.dtype == torch.float32:
-        acc = x @ wd.t()
-    else:
-        acc = torch.matmul(x, wd.t()).float() if epilogue != EPI_STORE else torch.matmul(x, wd.t())
-    if epilogue == EPI_STORE:
-        out.copy_(acc)
-    elif epilogue == EPI_STORE_F32:
-        out.copy_(acc)
-    elif epilogue == EPI_ADD_RESIDUAL:
-        out.add_(acc)
-    else:
-        n2 = acc.shape[1] // 2
-        out.copy_(torch.nn.functional.silu(acc[:, :n2]) * acc[:, n2:])
     return out
 
 
