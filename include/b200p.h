@@ -75,6 +75,13 @@ int b200p_dequantize(const uint32_t* w, const void* scales, const void* biases, 
                      int64_t N, int64_t K, int group_size, int bits, int dtype, int mode,
                      void* stream);
 
+/* mx.quantize(w, group_size, bits)                                  [nn.quantize, utils.py:886-905; convert, utils.py:934-981]
+ * w `dtype` [N,K] -> wq uint32 [N, K*bits/32], scales / biases `dtype` [N, K/group_size]; every step rounded to `dtype`
+ * where MLX's composed ops round it: bit-exact against oracle/mlx_ops.py quantize.
+ * group_size 32, 64 or 128. */
+int b200p_quantize(const void* w, uint32_t* wq, void* scales, void* biases, int64_t N, int64_t K, int group_size,
+                   int bits, int dtype, void* stream);
+
 /* embed_tokens(ids): gather rows + dequantize                    [models/llama.py:212]
  * ids int32 [M]; out float [M,K] if out_f32 else `dtype` [M,K] (values are the dtype-rounded
  * dequantised weights either way). */

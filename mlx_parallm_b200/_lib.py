@@ -27,6 +27,7 @@ SIGNATURES = {
     "b200p_sm_count": (_i32, []),
     "b200p_set_pdl": (_i32, [_i32]),
     "b200p_dequantize": (_i32, [_vp, _vp, _vp, _vp, _i64, _i64, _i32, _i32, _i32, _i32, _vp]),
+    "b200p_quantize": (_i32, [_vp, _vp, _vp, _vp, _i64, _i64, _i32, _i32, _i32, _vp]),
     "b200p_embed": (_i32, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _i32, _vp]),
     "b200p_qmm": (_i32, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _vp, _sz, _vp]),
     "b200p_qmm_workspace_bytes": (_sz, [_i64, _i64, _i64]),

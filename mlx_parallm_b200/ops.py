@@ -70,6 +70,19 @@ def dequantize(w, scales, biases, group_size=64, bits=4, mode=DQ_F32_MULADD, out
     return out
 
 
+def quantize(w, group_size=64, bits=4):
+    """mx.quantize: w [N, K] (float32 / float16 / bfloat16) -> (wq int32 [N, K*bits/32], scales, biases [N, K/gs])."""
+    _dev(w)
+    assert w.dim() == 2 and w.is_contiguous()
+    N, K = w.shape
+    wq = torch.empty((N, K * bits // 32), dtype=torch.int32, device=w.device)
+    s = torch.empty((N, K // group_size), dtype=w.dtype, device=w.device)
+    b = torch.empty_like(s)
+    _call("b200p_quantize", lambda: lib().b200p_quantize(_p(w), _p(wq), _p(s), _p(b), N, K, group_size, bits, dtype_code(w.dtype),
+                                                         _stream()))
+    return wq, s, b
+
+
 def embed(ids, w, scales, biases, group_size=64, bits=4, mode=DQ_F32_MULADD, out=None, out_f32=True):
     """QuantizedEmbedding.__call__: ids int32 [M] -> [M, K] (float32 carrier of dtype-rounded values)."""
     _dev(ids, w, scales, biases)

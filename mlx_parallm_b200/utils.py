@@ -493,6 +493,57 @@ def load_model(model_path: Path, lazy: bool = False, model_config: dict = {}, de
     return model
 
 
+# --------------------------------------------------------------------------------- quantiser / converter (row f3)
+QUANTIZED_LEAVES = ("q_proj", "k_proj", "v_proj", "o_proj", "gate_proj", "up_proj", "down_proj", "embed_tokens", "lm_head")
+
+
+def quantize_model(weights: Dict[str, torch.Tensor], config: dict, q_group_size: int = 64, q_bits: int = 4,
+                   device="cuda") -> Tuple[Dict[str, torch.Tensor], dict]:
+    """utils.py:886-905 on a dense state dict: every ``nn.Linear`` / ``nn.Embedding`` weight (nn.quantize replaces all
+    modules that have ``to_quantized``) becomes ``weight`` uint32 codes + ``scales`` + ``biases`` through b200p_quantize
+    (mx.quantize, bit-exact against the oracle); norms pass through.  Returns (weights, config with "quantization")."""
+    out: Dict[str, torch.Tensor] = {}
+    for name, t in weights.items():
+        mod, _, leaf = name.rpartition(".")
+        if leaf == "weight" and t.dim() == 2 and mod.rsplit(".", 1)[-1] in QUANTIZED_LEAVES and t.shape[1] % q_group_size == 0:
+            wq, sc, bi = ops.quantize(t.to(device).contiguous(), q_group_size, q_bits)
+            out[name], out[mod + ".scales"], out[mod + ".biases"] = wq.cpu(), sc.cpu(), bi.cpu()
+        else:
+            out[name] = t
+    qcfg = copy.deepcopy(config)
+    qcfg["quantization"] = {"group_size": q_group_size, "bits": q_bits}
+    return out, qcfg
+
+
+def convert(hf_path: str, mlx_path: str = "mlx_model", quantize: bool = False, q_group_size: int = 64, q_bits: int = 4,
+            dtype: str = "float16", upload_repo: Optional[str] = None, revision: Optional[str] = None,
+            dequantize: bool = False):
+    """utils.py:934-981 for local checkpoints: HF dense safetensors -> (quantised) MLX-format checkpoint
+    (``model.safetensors`` with metadata format=mlx + ``config.json`` with the quantization block)."""
+    if quantize and dequantize:
+        raise ValueError("Choose either quantize or dequantize, not both.")
+    if dequantize or upload_repo is not None:
+        raise NotImplementedError("dequantize / upload are outside this build (no network; decode path only)")
+    from safetensors import safe_open
+    from . import synth
+    model_path = get_model_path(hf_path, revision)
+    config = load_config(model_path)
+    files = glob.glob(str(model_path / "model*.safetensors")) or glob.glob(str(model_path / "*.safetensors"))
+    if not files:
+        raise FileNotFoundError(f"No safetensors found in {model_path}")
+    tdt = torch.float16 if quantize else getattr(torch, dtype)
+    weights: Dict[str, torch.Tensor] = {}
+    for wf in files:
+        with safe_open(wf, framework="pt", device="cpu") as f:
+            for k in f.keys():
+                t = f.get_tensor(k)
+                weights[k] = t.to(tdt) if t.is_floating_point() else t
+    if quantize:
+        weights, config = quantize_model(weights, config, q_group_size, q_bits)
+    synth.save_checkpoint(str(mlx_path), config, weights)
+    return Path(mlx_path)
+
+
 def load(path_or_hf_repo: str, tokenizer_config={}, model_config={}, adapter_path: Optional[str] = None,
          lazy: bool = False):
     """utils.py:711-747 -> (model, TokenizerWrapper)."""

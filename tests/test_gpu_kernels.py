@@ -71,6 +71,45 @@ def test_dequantize_empty_and_embed_gather(ops):
     assert e.dtype == torch.float32 and np.array_equal(e.cpu().numpy(), exp)
 
 
+# ---------------------------------------------------------------- quantize: bit-exact (codes, scales, biases)
+@pytest.mark.parametrize("bits", [4, 8])
+@pytest.mark.parametrize("dtype", ["float32", "float16", "bfloat16"])
+@pytest.mark.parametrize("gs", [32, 64, 128])
+def test_quantize_bit_exact(ops, bits, dtype, gs):
+    rng = np.random.default_rng(bits * 100 + gs)
+    N, K = 37, 512
+    w = rng.standard_normal((N, K)).astype(np.float32) * 0.05
+    w[0] = 0.0                                     # all-zero groups: scale falls back to eps, codes 0
+    if dtype != "float16":
+        w[1] = 0.031                               # constant groups (in f16 edge / eps overflows: NaN codes in MLX and the oracle alike)
+    w[2, :gs] = -np.abs(w[2, :gs])                 # min side dominates -> positive scale
+    w[3, :gs] = np.abs(w[3, :gs])                  # max side dominates -> negative scale
+    w[4, ::2] = 0.0                                # zeros must be exactly representable
+    w = ref.round_to(w, dtype)
+    eq, es, eb = ref.quantize(w, gs, bits, dtype)
+    gq, gsx, gb = ops.quantize(t_(w, dtype), gs, bits)
+    assert np.array_equal(gq.cpu().numpy().view(np.uint32), eq)
+    assert np.array_equal(bits_of(gsx, dtype), ref.storage_bits(es, dtype))
+    assert np.array_equal(bits_of(gb, dtype), ref.storage_bits(eb, dtype))
+
+
+def test_quantize_dequantize_roundtrip_full_size(ops):
+    """Size-independent property at a BASELINE shape (down_proj of Llama-3-8B): dequantize(quantize(w)) is within half a
+    quantisation step (+ storage rounding) of w, group by group, and quantising the dequantised matrix again reproduces
+    the codes (idempotence)."""
+    g = torch.Generator(device="cuda").manual_seed(4)
+    w = (torch.randn((4096, 14336), generator=g, device="cuda") * 0.02).to(torch.float16)
+    wq, s, b = ops.quantize(w, 64, 4)
+    d = ops.dequantize(wq, s, b, 64, 4)
+    step = s.float().abs().repeat_interleave(64, 1)
+    # the scale is snapped to edge / rint(edge / scale), so the far end of a group may clip by up to ~0.8 step
+    assert bool(((d.float() - w.float()).abs() <= 1.0 * step + 4e-3 * w.float().abs() + 1e-5).all())
+    assert float(((d.float() - w.float()).abs() / step).mean()) < 0.3
+    wq2, s2, b2 = ops.quantize(d, 64, 4)
+    d2 = ops.dequantize(wq2, s2, b2, 64, 4)
+    assert float((d2.float() - d.float()).abs().max()) <= float(step.max()) * 1.01
+
+
 # ---------------------------------------------------------------- quantized matmul
 def qmm_case(ops, M, N, K, bits, dtype, epi, seed=0, path=0, ragged_ld=False):
     from mlx_parallm_b200 import _lib

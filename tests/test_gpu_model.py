@@ -150,3 +150,37 @@ def test_load_model_from_mlx_checkpoint(tmp_path):
     ids = prompts_for(cfg, 2, 5)
     assert torch.equal(m(torch.from_numpy(ids)), gm(torch.from_numpy(ids)))
     assert m.head_dim == 64 and m.n_kv_heads == 2 and len(m.layers) == 3 and m.model_type == "qwen3"
+
+
+def test_convert_quantizes_a_dense_checkpoint_like_the_oracle(tmp_path):
+    """utils.convert(quantize=True): HF dense safetensors -> MLX 4-bit checkpoint whose tensors equal the oracle's
+    mx.quantize restatement bit for bit, and which load_model + generate_step run."""
+    from safetensors.torch import save_file
+    import json
+    from mlx_parallm_b200 import synth, utils
+    from oracle import mlx_ops as ref
+    cfg = synth.get_config("tiny-llama")
+    dense_cfg = {k: v for k, v in cfg.items() if k != "quantization"}
+    rng = np.random.default_rng(21)
+    dense = {}
+    for name, (n, k) in synth.linear_shapes(cfg).items():
+        dense[name + ".weight"] = torch.from_numpy(rng.uniform(-1, 1, (n, k)).astype(np.float32) / np.sqrt(k)).to(torch.float16)
+    for name in synth.norm_names(cfg):
+        dense[name] = torch.ones((cfg["hidden_size"],), dtype=torch.float16)
+    src = tmp_path / "hf"
+    src.mkdir()
+    save_file({k: v.contiguous() for k, v in dense.items()}, str(src / "model.safetensors"))
+    json.dump(dense_cfg, open(src / "config.json", "w"))
+    out = utils.convert(str(src), str(tmp_path / "mlx"), quantize=True, q_group_size=64, q_bits=4)
+    from safetensors import safe_open
+    with safe_open(str(out / "model.safetensors"), framework="pt") as f:
+        assert f.metadata() == {"format": "mlx"}
+        got = {k: f.get_tensor(k) for k in f.keys()}
+    assert json.load(open(out / "config.json"))["quantization"] == {"group_size": 64, "bits": 4}
+    name = "model.layers.1.mlp.down_proj"
+    eq, es, eb = ref.quantize(dense[name + ".weight"].float().numpy(), 64, 4, "float16")
+    assert np.array_equal(got[name + ".weight"].view(torch.int32).numpy().view(np.uint32), eq)
+    assert np.array_equal(got[name + ".scales"].float().numpy(), es) and np.array_equal(got[name + ".biases"].float().numpy(), eb)
+    gm = utils.load_model(out)
+    y, _ = next(utils.generate_step(torch.zeros((2, 5), dtype=torch.int64), gm))
+    assert y.shape == (2, 1)
