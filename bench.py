@@ -44,6 +44,11 @@ HEADLINE = "llama3-8b-4bit-b64-t8192"
 DEFAULT_SWEEP = ["llama3-8b-4bit-b64-t256", "llama3-8b-4bit-b8-t8192", "llama3-8b-4bit-b1-t8192"]
 
 
+# (workload, kernel, tp) -> bytes per launch from profiles/r1_run5_prof_attn_t8192_raw.csv
+# (dram__bytes_read.sum 2.149204 GB + dram__bytes_write.sum 8.531712 MB; algorithmic 2.158 GB)
+NCU_TRAFFIC = {("llama3-8b-4bit-b64-t8192", "b200p_attn", 1): 2.149204e9 + 8.531712e6}
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -235,8 +240,11 @@ def run_workload(name, model, cfg, steps, warmup, tp_world, dist, with_profile, 
         per_step = {k: kinds[k] * prof[k]["calls_per_step"] for k in kinds if k in prof}
         dom = max(per_step, key=per_step.get)
         ach = kinds[dom] / (prof[dom]["mean_ms"] * 1e-3) / 1e9
+        # measured DRAM traffic of one launch of the dominant kernel (ncu --set full, dram__bytes_read.sum +
+        # dram__bytes_write.sum): only known for the configuration that was captured
+        traffic = NCU_TRAFFIC.get((name, dom, tp_world))
         res["roofline"] = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
-                           "frac": ach / hbm_peak, "traffic": None,
+                           "frac": ach / hbm_peak, "traffic": traffic,
                            "algorithmic_bytes_per_launch": kinds[dom],
                            "share_of_step_time": prof[dom]["total_ms_per_step"] / sum(v["total_ms_per_step"] for v in prof.values())}
     del sess, cache
@@ -411,6 +419,7 @@ def main():
                 "scaling": "strong", "vs_baseline": None, "dtype": "f16 storage / f32 accumulate (4-bit g64 weights)",
                 "data": "synthetic (random-init MLX-format weights, synthetic KV context)",
                 "config": {"workload": args.workload, "batch": B, "context": T, "parallelism": f"tp{world}",
+                           "tp_exchange": (getattr(getattr(model, "_tp_fused", None), "mode", "nccl") if world > 1 else None),
                            "l2_policy": "inputs larger than L2 (weights 4.2 GB + KV >> 126 MB are re-streamed every step)"},
                 "e2e": {"value": main_res["e2e"]["tok_s"], "unit": UNIT, "h2d_bytes_per_step": main_res["e2e"]["h2d"],
                         "d2h_bytes_per_step": main_res["e2e"]["d2h"], "ms_per_step": main_res["e2e"]["ms_per_step"]},

@@ -58,6 +58,24 @@ def main():
                 out = ops.dequantize(wq, s, b, 64, bits, dt, mode)
                 dq[f"out_{bits}_{dt}_{mode}"] = ops.storage_bits(out, dt)
     np.savez_compressed(os.path.join(OUT, "dequantize_bits.npz"), **dq)
+    # 3. quantize: codes + scale / bias bit patterns for dense inputs covering both sign branches, exact zeros, all-zero groups
+    rngq = np.random.default_rng(77)
+    qz = {}
+    wd = (rngq.standard_normal((24, 256)) * 0.05).astype(np.float32)
+    wd[0] = 0.0
+    wd[1, :64] = -np.abs(wd[1, :64])
+    wd[2, :64] = np.abs(wd[2, :64])
+    wd[3, ::2] = 0.0
+    for dt in ops.DTYPES:
+        w = ops.round_to(wd, dt)
+        qz[f"w_{dt}"] = ops.storage_bits(w, dt)
+        for bits in (4, 8):
+            for gs in (32, 64, 128):
+                wq, sc, bi = ops.quantize(w, gs, bits, dt)
+                qz[f"q_{dt}_{bits}_{gs}"] = wq
+                qz[f"s_{dt}_{bits}_{gs}"] = ops.storage_bits(sc, dt)
+                qz[f"b_{dt}_{bits}_{gs}"] = ops.storage_bits(bi, dt)
+    np.savez_compressed(os.path.join(OUT, "quantize_bits.npz"), **qz)
     print("golden fixtures written to", OUT)
 
 

@@ -38,3 +38,28 @@ def test_oracle_dequantize_bits_match_golden(golden_dir):
             for mode in (0, 1, 2):
                 out = ops.dequantize(g[f"w_{bits}"], g[f"s_{bits}_{dt}"], g[f"b_{bits}_{dt}"], 64, bits, dt, mode)
                 assert np.array_equal(ops.storage_bits(out, dt), g[f"out_{bits}_{dt}_{mode}"]), (bits, dt, mode)
+
+
+def _from_bits(bits, dt):
+    if dt == "float32":
+        return bits.view(np.float32)
+    if dt == "float16":
+        return bits.view(np.float16).astype(np.float32)
+    return ops.bf16_from_bits(bits)
+
+
+def test_oracle_quantize_bits_match_golden(golden_dir):
+    g = np.load(os.path.join(golden_dir, "quantize_bits.npz"))
+    for dt in ops.DTYPES:
+        w = _from_bits(g[f"w_{dt}"], dt)
+        for bits in (4, 8):
+            for gs in (32, 64, 128):
+                wq, sc, bi = ops.quantize(w, gs, bits, dt)
+                assert np.array_equal(wq, g[f"q_{dt}_{bits}_{gs}"]), (dt, bits, gs)
+                assert np.array_equal(ops.storage_bits(sc, dt), g[f"s_{dt}_{bits}_{gs}"])
+                assert np.array_equal(ops.storage_bits(bi, dt), g[f"b_{dt}_{bits}_{gs}"])
+                # properties of A.1: the scale is snapped so that zero sits on the code grid (up to storage rounding of
+                # q*s + b), and codes stay in range
+                d = ops.dequantize(wq, sc, bi, gs, bits, dt)
+                assert np.abs(d[w == 0]).max() <= np.abs(w).max() * 2.0 ** -6
+                assert ops.unpack_codes(wq, bits).max() <= (1 << bits) - 1

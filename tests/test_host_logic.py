@@ -95,3 +95,23 @@ def test_streaming_detokenizer_and_wrapper_passthrough():
     assert "".join(segs) == "abc" == d.text and d.tokens == [1, 2, 3]
     tw.pad_token = "<eos>"                                 # setattr passes through (utils.py:513-515)
     assert tw._tokenizer.pad_token == "<eos>"
+
+
+def test_compat_install_aliases_the_reference_module_names():
+    """the names the reference's server / demo import resolve to this engine."""
+    import sys
+    import mlx_parallm_b200.compat as compat
+    saved = {k: v for k, v in sys.modules.items() if k == "mlx_parallm" or k.startswith("mlx_parallm.")}
+    try:
+        compat.install()
+        from mlx_parallm.utils import load, generate, stream_generate, batch_generate, generate_step, \
+            batch_stream_generate_text, batch_generate_text                                   # noqa: F401  (server/main.py:22-28)
+        from mlx_parallm.sample_utils import top_p_sampling                                    # noqa: F401  (server/main.py:29)
+        from mlx_parallm.models.base import BatchedKVCache, PagedKVCache                       # noqa: F401
+        import mlx_parallm.models.llama as llama
+        import mlx_parallm_b200.utils as ours
+        assert generate_step is ours.generate_step and llama.Model.__module__ == "mlx_parallm_b200.models.llama"
+    finally:
+        for k in [k for k in sys.modules if k == "mlx_parallm" or k.startswith("mlx_parallm.")]:
+            del sys.modules[k]
+        sys.modules.update(saved)
