@@ -13,6 +13,8 @@
 // Algorithmic HBM bytes per launch: sum_b len_b * Hkv * D * 2 (K and V) * sizeof(T).
 #include <type_traits>
 
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "mma_util.cuh"
 
@@ -20,20 +22,20 @@ namespace b200p {
 
 int sm_count();
 
-constexpr int AD_WARPS = 8;
-constexpr int AD_THREADS = AD_WARPS * 32;
+// warps per CTA: 8 (one 192 KB CTA per SM) for long key ranges; 2 (four 48 KB CTAs per SM) when a CTA's key range is
+// short -- then the step is a few waves of fixed per-CTA latency and smaller CTAs cut the number of waves
 constexpr int AD_TILE = 16;                    // keys per warp tile
 constexpr int AD_STAGES = 3;
 constexpr int AD_D = 128;
 constexpr int AD_TILE_BYTES = AD_TILE * AD_D * 2;                 // 4 KB (K) ; same for V
 constexpr int AD_WARP_SMEM = AD_STAGES * 2 * AD_TILE_BYTES;       // 24 KB per warp
-constexpr int AD_SMEM = AD_WARPS * AD_WARP_SMEM;                  // 192 KB
+constexpr int AD_SHORT_KEYS = 1024;                               // key range per CTA up to which the 2-warp variant is used
 
 // workspace record per (b, q head, split): [m, l, pad, pad, O[128]] floats
 constexpr int AD_REC = 4 + AD_D;
 
-template <typename T>
-__global__ void __launch_bounds__(AD_THREADS, 1)
+template <typename T, int AD_WARPS>
+__global__ void __launch_bounds__(AD_WARPS * 32, AD_WARPS == 8 ? 1 : 4)
 attn_decode_kernel(const T* __restrict__ q, const T* __restrict__ kc, const T* __restrict__ vc,
                    const int32_t* __restrict__ lengths, T* __restrict__ out, float* __restrict__ ws, int Hq, int Hkv,
                    int64_t Tcap, float scale_log2e, int splits, int out_perm) {
@@ -187,7 +189,7 @@ attn_decode_kernel(const T* __restrict__ q, const T* __restrict__ kc, const T* _
   __syncthreads();
   // merge the 8 warps: thread t -> (row = t / 16 ... ) : 256 threads cover G rows x 128 dims in passes
   const float* all = reinterpret_cast<const float*>(smem);
-  for (int idx = threadIdx.x; idx < G * AD_D; idx += AD_THREADS) {
+  for (int idx = threadIdx.x; idx < G * AD_D; idx += AD_WARPS * 32) {
     const int row = idx / AD_D, d = idx - row * AD_D;
     float M = -INFINITY;
 #pragma unroll
@@ -235,17 +237,17 @@ attn_reduce_kernel(const float* __restrict__ ws, T* __restrict__ out, int splits
 // ------------------------------------------------------------------------------------------------ host
 constexpr int AD_MAX_SPLITS = 32;
 
-static int pick_splits(int64_t B, int Hkv, int64_t Tcap) {
+static int pick_splits(int64_t B, int Hkv, int64_t Tcap, int ctas_per_sm) {
   // enough CTAs to fill the machine for >= ~2 waves, but >= 256 keys per CTA
   const int64_t base = B * Hkv;
-  const int sms = sm_count();
+  const int64_t slots = (int64_t)sm_count() * ctas_per_sm;
   int best = 1;
   double best_eff = 0.0;
   for (int s = 1; s <= AD_MAX_SPLITS; ++s) {
     if (s > 1 && Tcap / s < 256) break;
     const int64_t ctas = base * s;
-    const int64_t waves = (ctas + sms - 1) / sms;
-    const double eff = (double)ctas / (double)(waves * sms);
+    const int64_t waves = (ctas + slots - 1) / slots;
+    const double eff = (double)ctas / (double)(waves * slots);
     if (eff > best_eff + 0.02) { best_eff = eff; best = s; }
   }
   return best;
@@ -260,27 +262,41 @@ size_t attn_decode_workspace_bytes(int64_t B, int64_t L, int Hq, int D) {
   return (size_t)B * Hq * AD_MAX_SPLITS * AD_REC * sizeof(float);
 }
 
-template <typename T>
-static int launch_attn_decode(const void* q, const void* kc, const void* vc, const int32_t* lengths, void* out, int64_t B,
-                              int Hq, int Hkv, int64_t Tcap, float scale, int out_perm, void* ws, cudaStream_t st) {
-  auto kern = attn_decode_kernel<T>;
+template <typename T, int WARPS>
+static int launch_attn_decode_w(const void* q, const void* kc, const void* vc, const int32_t* lengths, void* out, int64_t B,
+                                int Hq, int Hkv, int64_t Tcap, float scale, int out_perm, void* ws, int splits, cudaStream_t st) {
+  auto kern = attn_decode_kernel<T, WARPS>;
+  constexpr int SMEM = WARPS * AD_WARP_SMEM;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, AD_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(attn_decode_kernel)");
     attr_set = true;
   }
-  // the split count depends on capacity, not on the (device-side) lengths, so a captured graph stays valid
-  const int splits = pick_splits(B, Hkv, Tcap);
   dim3 grid((unsigned)splits, (unsigned)Hkv, (unsigned)B);
-  launch_pdl(kern, grid, AD_THREADS, AD_SMEM, st, (const T*)q, (const T*)kc, (const T*)vc, lengths, (T*)out, (float*)ws, Hq, Hkv,
-                                          Tcap, scale * 1.4426950408889634f, splits, out_perm);
+  launch_pdl(kern, grid, WARPS * 32, SMEM, st, (const T*)q, (const T*)kc, (const T*)vc, lengths, (T*)out, (float*)ws, Hq, Hkv,
+             Tcap, scale * 1.4426950408889634f, splits, out_perm);
   B200P_LAUNCH_CHECK("attn_decode_kernel");
   if (splits > 1) {
     launch_pdl(attn_reduce_kernel<T>, (unsigned)(B * Hq), AD_D, 0, st, (const float*)ws, (T*)out, splits, out_perm);
     B200P_LAUNCH_CHECK("attn_reduce_kernel");
   }
   return B200P_OK;
+}
+
+static int g_ad_warps = [] { const char* e = getenv("B200P_ATTN_WARPS"); return e ? atoi(e) : 0; }();   // 0 = auto
+
+template <typename T>
+static int launch_attn_decode(const void* q, const void* kc, const void* vc, const int32_t* lengths, void* out, int64_t B,
+                              int Hq, int Hkv, int64_t Tcap, float scale, int out_perm, void* ws, cudaStream_t st) {
+  // the variant and the split count depend on capacity, not on the (device-side) lengths, so a captured graph stays valid
+  const int s8 = pick_splits(B, Hkv, Tcap, 1);
+  const bool small = g_ad_warps ? g_ad_warps == 2 : (Tcap / s8 <= AD_SHORT_KEYS);
+  if (small) {
+    const int s2 = pick_splits(B, Hkv, Tcap, 4);
+    return launch_attn_decode_w<T, 2>(q, kc, vc, lengths, out, B, Hq, Hkv, Tcap, scale, out_perm, ws, s2, st);
+  }
+  return launch_attn_decode_w<T, 8>(q, kc, vc, lengths, out, B, Hq, Hkv, Tcap, scale, out_perm, ws, s8, st);
 }
 
 int attn_decode_launch(const void* q, const void* kc, const void* vc, const int32_t* lengths, void* out, int64_t B,
