@@ -133,6 +133,14 @@ int b200p_rope_kv_append(void* qkv, void* q_out, void* kcache, void* vcache,
  * The kernel re-zeroes gu behind its read, so the buffer is ready for the next step. */
 int b200p_silu_mul(float* gu, void* out, int64_t M, int64_t I, int64_t ldg, int64_t ldo, int dtype, int flags,
                    void* stream);
+/* LoRA low-rank update (mlx_lm LoRALinear: y = linear(x) + (scale * (x @ lora_a) @ lora_b).astype(x.dtype))
+ *                                       [adapters on q_proj / v_proj: lora_init.py:63-73; SURVEY A.9, row f4]
+ * x `dtype` [M,K] (ldx); At `dtype` [16, K] = lora_a transposed, rank padded to 16 with zero rows (k axis permuted like x
+ * when x is PERM8); Bt `dtype` [N, 16] = lora_b transposed, padded likewise; y[m, col0 + n] += update for n < N:
+ * out_f32 = 1 -> y is the float accumulation buffer of the projection (ldy floats), else its `dtype` output (the update
+ * is rounded to `dtype` first, as MLX's astype does).  16-bit types only. */
+int b200p_lora_add(const void* x, const void* At, const void* Bt, void* y, int64_t M, int64_t N, int64_t K, int64_t ldx,
+                   int64_t ldy, int64_t col0, float scale, int dtype, int out_f32, void* stream);
 /* lengths[b] += delta (device side, keeps the decode graph replayable) */
 int b200p_advance_lengths(int32_t* lengths, int64_t B, int32_t delta, void* stream);
 

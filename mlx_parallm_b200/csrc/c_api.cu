@@ -70,7 +70,11 @@ static int query_device() {
   return B200P_OK;
 }
 
-bool pdl_enabled() { return g_pdl == 1; }
+// per-class PDL mask for the non-GEMM kernels (see common.cuh); B200P_PDL=1 means every class
+static int g_pdl_mask = [] { const char* e = getenv("B200P_PDL_MASK"); return e ? atoi(e) : 0; }();
+static thread_local int g_pdl_class = 0;
+void pdl_set_class(int cls) { g_pdl_class = cls; }
+bool pdl_enabled() { return g_pdl == 1 || (g_pdl_mask & g_pdl_class) != 0; }
 bool pdl_enabled_gemm() { return g_pdl != 0; }
 
 int sm_count() {
@@ -154,6 +158,7 @@ extern "C" int b200p_qmm(const void* x, const uint32_t* w, const void* scales, c
                 (long long)K);
   B200P_REQUIRE(ldy >= (epilogue == B200P_EPI_SILU_MUL ? N / 2 : N), B200P_ERR_ARG, "ldy too small");
   if (M == 0) return B200P_OK;
+  PdlClass pdl_cls(64);
   cudaStream_t st = (cudaStream_t)stream;
   const bool mma_ok = qmv_mma_supported(M, N, K, group_size, bits, dtype, epilogue) && aligned(y, 4) &&
                       !(flags & B200P_Y_PERM8);
@@ -188,6 +193,7 @@ extern "C" int b200p_attn(const void* q, const void* kcache, const void* vcache,
   B200P_REQUIRE(B >= 0 && L >= 0 && Tcap > 0, B200P_ERR_ARG, "bad shape");
   B200P_REQUIRE(dtype >= 0 && dtype <= 2, B200P_ERR_ARG, "bad dtype %d", dtype);
   if (B * L == 0) return B200P_OK;
+  PdlClass pdl_cls(8);
   cudaStream_t st = (cudaStream_t)stream;
   const bool tc_ok = attn_decode_supported(L, Hq, Hkv, D, dtype);
   const bool pf_ok = attn_prefill_supported(L, Hq, Hkv, D, dtype);

@@ -94,6 +94,13 @@ __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepc
 // next kernel's CTAs may be scheduled as soon as this one's have all passed griddepcontrol.launch_dependents or
 // exited, and each kernel executes griddepcontrol.wait before it touches anything a predecessor reads or writes.
 bool pdl_enabled();
+// kernel class of the C-ABI call being executed (B200P_PDL_MASK selects, per class, which launches carry the PDL attribute):
+// 2 rmsnorm, 4 rope+append, 8 attention, 16 silu_mul, 32 embed / dequantize / advance / samplers, 64 GEMV paths
+void pdl_set_class(int cls);
+struct PdlClass {
+  explicit PdlClass(int c) { pdl_set_class(c); }
+  ~PdlClass() { pdl_set_class(0); }
+};
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl_opt(bool pdl, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
   cudaLaunchConfig_t cfg = {};

@@ -99,6 +99,7 @@ using namespace b200p;
 extern "C" int b200p_dequantize(const uint32_t* w, const void* scales, const void* biases, void* out,
                                 int64_t N, int64_t K, int group_size, int bits, int dtype, int mode,
                                 void* stream) {
+  PdlClass pdl_cls(32);
   B200P_REQUIRE(N >= 0, B200P_ERR_ARG, "N < 0");
   if (N == 0) return B200P_OK;                      // empty input: nothing to launch (pointers may be null)
   int rc = check_quant_args(w, scales, biases, K, group_size, bits, mode);
@@ -112,6 +113,7 @@ extern "C" int b200p_dequantize(const uint32_t* w, const void* scales, const voi
 extern "C" int b200p_embed(const int32_t* ids, const uint32_t* w, const void* scales, const void* biases,
                            void* out, int64_t M, int64_t V, int64_t K, int group_size, int bits, int dtype,
                            int mode, int out_f32, void* stream) {
+  PdlClass pdl_cls(32);
   if (M == 0) return B200P_OK;
   int rc = check_quant_args(w, scales, biases, K, group_size, bits, mode);
   if (rc) return rc;
@@ -202,6 +204,7 @@ rmsnorm_kernel(const float* __restrict__ x, const T* __restrict__ w, T* __restri
 
 extern "C" int b200p_rmsnorm(const float* x, const void* w, void* y, int64_t M, int64_t H, float eps,
                              int dtype, int flags, void* stream) {
+  PdlClass pdl_cls(2);
   B200P_REQUIRE(x && w && y, B200P_ERR_ARG, "null pointer");
   B200P_REQUIRE((flags & ~B200P_OUT_PERM8) == 0, B200P_ERR_ARG, "unknown flags 0x%x", flags);
   const int perm = (flags & B200P_OUT_PERM8) ? 1 : 0;
@@ -335,6 +338,7 @@ extern "C" int b200p_rope_kv_append(void* qkv, void* q_out, void* kcache, void* 
                                     int64_t B, int64_t L, int Hq, int Hkv, int D, int64_t Tcap,
                                     float rope_base, float rope_scale, float norm_eps, int dtype,
                                     int qkv_f32, void* stream) {
+  PdlClass pdl_cls(4);
   B200P_REQUIRE(qkv && q_out && kcache && vcache && lengths, B200P_ERR_ARG, "null pointer");
   B200P_REQUIRE(!qkv_f32 || dtype != B200P_F32, B200P_ERR_ARG, "qkv_f32 is the accumulation-buffer input of 16-bit models");
   B200P_REQUIRE(D >= 2 && D % 2 == 0 && D <= 2048, B200P_ERR_ARG, "head_dim %d unsupported", D);
@@ -359,6 +363,7 @@ extern "C" int b200p_rope_kv_append(void* qkv, void* q_out, void* kcache, void* 
 
 extern "C" int b200p_silu_mul(float* gu, void* out, int64_t M, int64_t I, int64_t ldg, int64_t ldo, int dtype, int flags,
                               void* stream) {
+  PdlClass pdl_cls(16);
   B200P_REQUIRE(gu && out, B200P_ERR_ARG, "null pointer");
   B200P_REQUIRE(dtype == B200P_F16 || dtype == B200P_BF16, B200P_ERR_ARG, "silu_mul writes a 16-bit activation");
   B200P_REQUIRE((flags & ~B200P_OUT_PERM8) == 0, B200P_ERR_ARG, "unknown flags 0x%x", flags);
@@ -376,6 +381,7 @@ extern "C" int b200p_silu_mul(float* gu, void* out, int64_t M, int64_t I, int64_
 }
 
 extern "C" int b200p_advance_lengths(int32_t* lengths, int64_t B, int32_t delta, void* stream) {
+  PdlClass pdl_cls(32);
   B200P_REQUIRE(lengths, B200P_ERR_ARG, "null lengths");
   if (B == 0) return B200P_OK;
   launch_pdl(advance_lengths_kernel, (unsigned)((B + 255) / 256), 256, 0, (cudaStream_t)stream, lengths, B, delta);

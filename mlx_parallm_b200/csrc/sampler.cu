@@ -316,6 +316,7 @@ using namespace b200p;
 
 extern "C" int b200p_argmax(const float* logits, int32_t* tokens, float* probs_out, int64_t B, int64_t V,
                             int64_t ldl, void* stream) {
+  PdlClass pdl_cls(32);
   B200P_REQUIRE(logits && tokens, B200P_ERR_ARG, "null pointer");
   B200P_REQUIRE(V > 0 && V < (1ll << 31) && ldl >= V, B200P_ERR_ARG, "bad V/ldl");
   if (B == 0) return B200P_OK;
@@ -326,6 +327,7 @@ extern "C" int b200p_argmax(const float* logits, int32_t* tokens, float* probs_o
 
 extern "C" int b200p_argmax_partial(const float* logits, float* rec_out, int64_t B, int64_t V, int64_t ldl,
                                     int32_t vocab_offset, void* stream) {
+  PdlClass pdl_cls(32);
   B200P_REQUIRE(logits && rec_out, B200P_ERR_ARG, "null pointer");
   B200P_REQUIRE(V > 0 && V < (1ll << 31) && ldl >= V && vocab_offset >= 0, B200P_ERR_ARG, "bad V/ldl/offset");
   B200P_REQUIRE(aligned(rec_out, 16), B200P_ERR_ALIGN, "rec_out must be 16-byte aligned");
@@ -338,6 +340,7 @@ extern "C" int b200p_argmax_partial(const float* logits, float* rec_out, int64_t
 
 extern "C" int b200p_argmax_merge(const float* recs, int32_t* tokens, float* probs_out, int W, int64_t B,
                                   void* stream) {
+  PdlClass pdl_cls(32);
   B200P_REQUIRE(recs && tokens, B200P_ERR_ARG, "null pointer");
   B200P_REQUIRE(W > 0 && aligned(recs, 16), B200P_ERR_ARG, "bad shard count / alignment");
   if (B == 0) return B200P_OK;
@@ -350,6 +353,7 @@ extern "C" int b200p_argmax_merge(const float* recs, int32_t* tokens, float* pro
 extern "C" int b200p_sample_top_p(const float* logits, int32_t* tokens, float* probs_out, int64_t B, int64_t V,
                                   int64_t ldl, float temperature, float top_p, uint64_t seed, uint64_t offset,
                                   void* stream) {
+  PdlClass pdl_cls(32);
   B200P_REQUIRE(logits && tokens, B200P_ERR_ARG, "null pointer");
   B200P_REQUIRE(V > 0 && V < (1ll << 31) && ldl >= V, B200P_ERR_ARG, "bad V/ldl");
   B200P_REQUIRE(temperature > 0.f, B200P_ERR_ARG, "temperature must be > 0 (use b200p_argmax for greedy)");

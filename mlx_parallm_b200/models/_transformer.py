@@ -88,6 +88,7 @@ class Attention:
         self.v_proj = QuantizedLinear(h, self.n_kv_heads * head_dim, gs, bits)
         self.o_proj = QuantizedLinear(self.n_heads * head_dim, h, gs, bits)
         self.qkv_proj = QuantizedLinear(h, (self.n_heads + 2 * self.n_kv_heads) * head_dim, gs, bits)
+        self.lora: Dict[str, tuple] = {}      # "q_proj" / "v_proj" -> (At [16,K], Bt [N,16], scale): set by apply_lora
         self.q_norm = RMSNorm(head_dim, args.rms_norm_eps) if qk_norm else None
         self.k_norm = RMSNorm(head_dim, args.rms_norm_eps) if qk_norm else None
 
@@ -254,6 +255,36 @@ class DecoderModel:
         self._arenas.clear()
         return self
 
+    def apply_lora(self, adapters: Dict[str, torch.Tensor], scale: float, keys=("self_attn.q_proj", "self_attn.v_proj")):
+        """Attach mlx_lm-format LoRA adapters (``model.layers.{i}.self_attn.q_proj.lora_a [K, r]`` / ``.lora_b [r, N]``;
+        lora_init.py:63-73, 140-149) to the attention projections.  Stored transposed and rank-padded to 16 for the
+        mma kernel; lora_a's k axis follows the PERM8 activation layout when the model uses it.  Pass {} to detach."""
+        if self.tp_world > 1:
+            raise NotImplementedError("LoRA under tensor parallelism is not built")
+        if not self._fast16:
+            raise NotImplementedError("LoRA needs a 16-bit model (b200p_lora_add)")
+        for i, layer in enumerate(self.model.layers):
+            layer.self_attn.lora = {}
+            for key in keys:
+                if key not in ("self_attn.q_proj", "self_attn.v_proj"):
+                    raise NotImplementedError(f"LoRA on {key} is not built (reference default: q_proj, v_proj)")
+                pa, pb = f"model.layers.{i}.{key}.lora_a", f"model.layers.{i}.{key}.lora_b"
+                if pa not in adapters:
+                    continue
+                A = adapters[pa].to(self.device, self.dtype)           # [K, r]
+                Bm = adapters[pb].to(self.device, self.dtype)          # [r, N]
+                K, r = A.shape
+                if r > 16:
+                    raise NotImplementedError(f"LoRA rank {r} > 16")
+                At = torch.zeros((16, K), dtype=self.dtype, device=self.device)
+                At[:r] = A.t()
+                if self._perm8:                                        # x arrives as [0,4,1,5,2,6,3,7] inside each group of 8
+                    At = At.view(16, K // 8, 8)[:, :, [0, 4, 1, 5, 2, 6, 3, 7]].reshape(16, K)
+                Bt = torch.zeros((Bm.shape[1], 16), dtype=self.dtype, device=self.device)
+                Bt[:, :r] = Bm.t()
+                layer.self_attn.lora[key.split(".")[-1]] = (At.contiguous(), Bt.contiguous(), float(scale))
+        return self
+
     def set_tensor_parallel(self, rank: int, world: int, allreduce):
         """allreduce(tensor_f32) sums in place across ranks on the current stream."""
         self.tp_rank, self.tp_world, self._allreduce = rank, world, allreduce
@@ -342,6 +373,11 @@ class DecoderModel:
                 at.qkv_proj(a["x"], EPI_ADD_RESIDUAL, out=a["qkv32"], workspace=a["ws"], x_perm=pm)
             else:
                 at.qkv_proj(a["x"], EPI_STORE, out=a["qkv"], workspace=a["ws"], x_perm=pm)
+            if at.lora:                    # LoRA on q_proj / v_proj (A.9): low-rank update of the q / v column blocks
+                qkv_buf = a["qkv32"] if f16 else a["qkv"]
+                for name, (At, Bt, scale) in at.lora.items():
+                    col0 = 0 if name == "q_proj" else (at.n_heads + at.n_kv_heads) * at.head_dim
+                    ops.lora_add(a["x"], At, Bt, qkv_buf, col0, scale)
             ops.rope_kv_append(a["qkv32"] if f16 else a["qkv"], a["q"], c.keys, c.values, lengths, B, L, at.n_heads,
                                at.n_kv_heads, at.head_dim, args.rope_theta, self.rope_scale,
                                at.q_norm.weight if at.q_norm else None, at.k_norm.weight if at.k_norm else None,

@@ -164,6 +164,18 @@ def silu_mul(gu, out, out_perm=False):
     return out
 
 
+def lora_add(x, At, Bt, y, col0: int, scale: float):
+    """y[:, col0:col0+N] += scale * (x @ lora_a) @ lora_b with At = lora_a^T [16, K], Bt = lora_b^T [N, 16] (rank padded)."""
+    _dev(x, At, Bt, y)
+    M, K = x.shape
+    N = Bt.shape[0]
+    assert At.shape == (16, K) and Bt.shape[1] == 16 and At.is_contiguous() and Bt.is_contiguous() and x.stride(1) == 1
+    _call("b200p_lora_add", lambda: lib().b200p_lora_add(_p(x), _p(At), _p(Bt), _p(y), M, N, K, x.stride(0), y.stride(0), int(col0),
+                                                         float(scale), dtype_code(x.dtype), 1 if y.dtype == torch.float32 else 0,
+                                                         _stream()))
+    return y
+
+
 def advance_lengths(lengths, delta: int):
     _dev(lengths)
     _call("b200p_advance_lengths", lambda: lib().b200p_advance_lengths(_p(lengths), lengths.numel(), int(delta), _stream()))

@@ -544,12 +544,32 @@ def convert(hf_path: str, mlx_path: str = "mlx_model", quantize: bool = False, q
     return Path(mlx_path)
 
 
+def load_adapters(model: DecoderModel, adapter_path) -> DecoderModel:
+    """mlx_lm.tuner.utils.load_adapters as the reference calls it (utils.py:737-741): ``adapter_config.json``
+    {fine_tune_type, num_layers, lora_parameters{rank, scale, dropout, keys}} + ``adapters.safetensors`` (lora_init.py:140-149)."""
+    from safetensors import safe_open
+    adapter_path = Path(adapter_path)
+    cfg_file = adapter_path / "adapter_config.json"
+    if not cfg_file.exists():
+        raise FileNotFoundError(f"The adapter path does not exist: {adapter_path}")
+    cfg = json.load(open(cfg_file))
+    if cfg.get("fine_tune_type", "lora") != "lora":
+        raise NotImplementedError(f"fine_tune_type {cfg.get('fine_tune_type')} is not built (LoRA only)")
+    lp = cfg.get("lora_parameters", {})
+    weights: Dict[str, torch.Tensor] = {}
+    with safe_open(str(adapter_path / "adapters.safetensors"), framework="pt", device="cpu") as f:
+        for k in f.keys():
+            weights[k] = f.get_tensor(k)
+    model.apply_lora(weights, lp.get("scale", 10.0), tuple(lp.get("keys", ("self_attn.q_proj", "self_attn.v_proj"))))
+    return model
+
+
 def load(path_or_hf_repo: str, tokenizer_config={}, model_config={}, adapter_path: Optional[str] = None,
          lazy: bool = False):
     """utils.py:711-747 -> (model, TokenizerWrapper)."""
     model_path = get_model_path(path_or_hf_repo)
     model = load_model(model_path, lazy, model_config)
     if adapter_path is not None:
-        raise NotImplementedError("LoRA adapters are a 'next' row (SURVEY 8f-4), not built yet")
+        load_adapters(model, adapter_path)
     tokenizer = load_tokenizer(model_path, tokenizer_config)
     return model, tokenizer

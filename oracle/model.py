@@ -133,6 +133,8 @@ class OracleModel:
         self.numerics = numerics
         self.tp_allreduce, self.tp_gather = tp_allreduce, tp_gather
         self._deq_cache: Dict[str, np.ndarray] = {}
+        # LoRA adapters (mlx_lm LoRALinear, A.9): prefix -> (lora_a [K, r], lora_b [r, N], scale)
+        self.lora: Dict[str, tuple] = {}
 
     # -- helpers ---------------------------------------------------------------------------
     @property
@@ -159,8 +161,16 @@ class OracleModel:
         return self._deq_cache[prefix]
 
     def _linear(self, prefix, x, out_dtype):
-        y = np.asarray(x, np.float32) @ self._wf(prefix).T          # A.3, fp32 accumulate
-        return ops.round_to(y, out_dtype) if out_dtype else y
+        x = np.asarray(x, np.float32)
+        y = x @ self._wf(prefix).T                                  # A.3, fp32 accumulate
+        y = ops.round_to(y, out_dtype) if out_dtype else y
+        if prefix in self.lora:                                     # y + (scale * (x @ A) @ B).astype(x.dtype)   (A.9)
+            a, b, scale = self.lora[prefix]
+            T = self.cfg.dtype
+            z = ops.round_to(ops.round_to(x @ np.asarray(a, np.float32), T) @ np.asarray(b, np.float32), T)
+            y = y + ops.round_to(np.float32(scale) * z, T)
+            y = ops.round_to(y, out_dtype) if out_dtype else y
+        return y
 
     # -- forward ---------------------------------------------------------------------------
     def forward(self, inputs: np.ndarray, cache: Optional[list] = None, last_only: bool = False) -> np.ndarray:
