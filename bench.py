@@ -295,6 +295,14 @@ def cpu_reference(cfg_name, B, T, budget_layers=1, repeats=1, seed=1234):
     import torch
     from mlx_parallm_b200 import synth
     from oracle.model import OracleConfig, OracleModel
+    # use every host core: torchrun exports OMP_NUM_THREADS=1 to its workers, which would silently make this a 1-thread run
+    ncores = os.cpu_count() or 1
+    try:
+        from threadpoolctl import threadpool_limits
+        threadpool_limits(limits=ncores)
+    except Exception:
+        pass
+    torch.set_num_threads(ncores)
     cfg = synth.get_config(cfg_name)
     L = cfg["num_hidden_layers"]
     sub = dict(cfg, num_hidden_layers=budget_layers)
@@ -356,6 +364,8 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return
+        for var in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):     # before numpy / BLAS load
+            os.environ[var] = str(os.cpu_count() or 1)
         cb = cpu_reference(cfg_name, B, T, repeats=max(1, min(args.steps, 3)))
         line = {"metric": METRIC, "value": cb["value"], "unit": UNIT, "impl": "reference", "n_gpus": args.gpus,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
