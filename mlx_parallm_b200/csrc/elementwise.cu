@@ -22,42 +22,57 @@ __device__ __forceinline__ float dq_one(uint32_t q, float s, float b) {
   }
 }
 
-// one thread per packed uint32 word; row index comes from `rows` (gather) or is the identity.
+// one thread per FOUR packed uint32 words (one 16-byte load, 32 / 16 outputs = 64 bytes of 16-bit stores); blockIdx.y = row,
+// so there is no 64-bit division on the index path; the row index comes from `rows` (gather) or is the identity.
 template <typename T, int BITS, int MODE, typename OUT>
 __global__ void __launch_bounds__(256)
 dequant_kernel(const uint32_t* __restrict__ w, const T* __restrict__ scales,
                const T* __restrict__ biases, OUT* __restrict__ out,
-               const int32_t* __restrict__ rows, int64_t n_rows, int64_t V, int64_t K, int gs) {
+               const int32_t* __restrict__ rows, int64_t row0, int64_t V, int64_t K, int gs) {
   constexpr int PER = 32 / BITS;
-  const int64_t words_per_row = K / PER;
-  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= n_rows * words_per_row) return;
+  const int words_per_row = (int)(K / PER);
+  const int w0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;          // first of this thread's 4 words
+  if (w0 >= words_per_row) return;
   pdl_wait();   // `rows` (token ids) and `out` belong to the previous kernels
-  int64_t r = idx / words_per_row;
-  int64_t wi = idx - r * words_per_row;
+  const int64_t r = row0 + blockIdx.y;
   int64_t src = rows ? (int64_t)rows[r] : r;
   if (src < 0 || src >= V) src = 0;  // out-of-vocab ids read row 0 (MLX would index modulo/UB)
-  uint32_t word = w[src * words_per_row + wi];
-  int64_t k0 = wi * PER;
-  int64_t g = k0 / gs;
-  float s = Tr<T>::to_f(scales[src * (K / gs) + g]);
-  float b = Tr<T>::to_f(biases[src * (K / gs) + g]);
-  __align__(16) OUT vals[PER];
-#pragma unroll
-  for (int j = 0; j < PER; ++j) {
-    uint32_t q = (word >> (j * BITS)) & ((1u << BITS) - 1u);
-    float v = dq_one<T, MODE>(q, s, b);
-    T vt = Tr<T>::from_f(v);  // storage rounding always happens
-    vals[j] = Tr<OUT>::from_f(Tr<T>::to_f(vt));
-  }
-  OUT* dst = out + r * K + k0;
-  constexpr int BYTES = PER * sizeof(OUT);
-  if (BYTES % 16 == 0) {
-#pragma unroll
-    for (int j = 0; j < BYTES / 16; ++j) reinterpret_cast<uint4*>(dst)[j] = reinterpret_cast<uint4*>(vals)[j];
+  const uint32_t* wp = w + src * words_per_row + w0;
+  uint32_t wd[4];
+  const int nw = min(4, words_per_row - w0);
+  if (nw == 4 && ((reinterpret_cast<uintptr_t>(wp) & 15) == 0)) {
+    const uint4 u = ldg_stream(wp);
+    wd[0] = u.x; wd[1] = u.y; wd[2] = u.z; wd[3] = u.w;
   } else {
 #pragma unroll
-    for (int j = 0; j < BYTES / 8; ++j) reinterpret_cast<uint2*>(dst)[j] = reinterpret_cast<uint2*>(vals)[j];
+    for (int i = 0; i < 4; ++i) wd[i] = i < nw ? wp[i] : 0u;
+  }
+  const int ng = (int)(K / gs);
+  OUT* dst_row = out + r * K;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    if (i >= nw) break;
+    const int k0 = (w0 + i) * PER;
+    const int g = k0 / gs;
+    const float s = Tr<T>::to_f(scales[src * ng + g]);
+    const float b = Tr<T>::to_f(biases[src * ng + g]);
+    __align__(16) OUT vals[PER];
+#pragma unroll
+    for (int j = 0; j < PER; ++j) {
+      const uint32_t q = (wd[i] >> (j * BITS)) & ((1u << BITS) - 1u);
+      const float v = dq_one<T, MODE>(q, s, b);
+      const T vt = Tr<T>::from_f(v);  // storage rounding always happens
+      vals[j] = Tr<OUT>::from_f(Tr<T>::to_f(vt));
+    }
+    OUT* dst = dst_row + k0;
+    constexpr int BYTES = PER * sizeof(OUT);
+    if (BYTES % 16 == 0) {
+#pragma unroll
+      for (int j = 0; j < BYTES / 16; ++j) reinterpret_cast<uint4*>(dst)[j] = reinterpret_cast<uint4*>(vals)[j];
+    } else {
+#pragma unroll
+      for (int j = 0; j < BYTES / 8; ++j) reinterpret_cast<uint2*>(dst)[j] = reinterpret_cast<uint2*>(vals)[j];
+    }
   }
 }
 
@@ -66,16 +81,24 @@ static int launch_dequant(const uint32_t* w, const void* scales, const void* bia
                           const int32_t* rows, int64_t n_rows, int64_t V, int64_t K, int gs, int bits,
                           int mode, cudaStream_t st) {
   const int per = 32 / bits;
-  int64_t total = n_rows * (K / per);
-  if (total == 0) return B200P_OK;
-  dim3 grid((unsigned)((total + 255) / 256)), block(256);
+  const int64_t words_per_row = K / per;
+  if (n_rows * words_per_row == 0) return B200P_OK;
+  B200P_REQUIRE(n_rows < 65536 * 1024ll && words_per_row < (1ll << 30), B200P_ERR_ARG, "matrix too large for one dequantize launch");
+  // rows go to blockIdx.y (<= 65535 per launch): larger matrices are cut into row slabs
+  const int threads = words_per_row / 4 >= 256 ? 256 : (int)(((words_per_row + 3) / 4 + 31) / 32 * 32);
+  dim3 block((unsigned)threads);
+  const unsigned gx = (unsigned)(((words_per_row + 3) / 4 + threads - 1) / threads);
 #define L(B_, M_)                                                                                   \
   launch_pdl(dequant_kernel<T, B_, M_, OUT>, grid, block, 0, st, w, (const T*)scales, (const T*)biases,      \
-                                                         (OUT*)out, rows, n_rows, V, K, gs)
-  if (bits == 4) {
-    if (mode == 0) L(4, 0); else if (mode == 1) L(4, 1); else L(4, 2);
-  } else {
-    if (mode == 0) L(8, 0); else if (mode == 1) L(8, 1); else L(8, 2);
+                                                         (OUT*)out, rows, row0, V, K, gs)
+  for (int64_t row0 = 0; row0 < n_rows; row0 += 65535) {
+    const int64_t nr = n_rows - row0 < 65535 ? n_rows - row0 : 65535;
+    dim3 grid(gx, (unsigned)nr);
+    if (bits == 4) {
+      if (mode == 0) L(4, 0); else if (mode == 1) L(4, 1); else L(4, 2);
+    } else {
+      if (mode == 0) L(8, 0); else if (mode == 1) L(8, 1); else L(8, 2);
+    }
   }
 #undef L
   B200P_LAUNCH_CHECK("dequant_kernel");
