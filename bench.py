@@ -36,6 +36,8 @@ WORKLOADS = {
     "llama3-8b-4bit-b64-t256": ("llama-3-8b", 64, 256),
     "llama3-8b-4bit-b8-t8192": ("llama-3-8b", 8, 8192),
     "llama3-8b-4bit-b1-t8192": ("llama-3-8b", 1, 8192),
+    # configs[2]'s B=256 point: 256 x 8192 tokens of 16-bit KV are 275 GB and do not fit one GPU; context capped at 4096 (137 GB)
+    "llama3-8b-4bit-b256-t4096": ("llama-3-8b", 256, 4096),
     "mistral-7b-4bit-b8-t256": ("mistral-7b", 8, 256),
     "qwen3-14b-4bit-b64-t256": ("qwen3-14b", 64, 256),
     "small": ("small-llama", 4, 64),

@@ -34,7 +34,9 @@ MAX_TOKENS_PER_FORWARD = 8192     # chunk size (B*L) of one prefill pass through
 # Up to this many rows the fused q|k|v and gate|up projections accumulate in fp32 buffers (stream-K partial tiles are summed
 # by TMA reduce-adds, the consumer kernel rounds and re-zeroes).  Above it (prefill) few tiles are split, the fp32 buffers
 # would be HBM traffic (235 MB per layer at 2048 rows: silu_mul alone took 245 us), so the 16-bit fused epilogues are used.
-ACC32_MAX_ROWS = 64
+# 128, not 64: a decode batch of 128 rows is still ONE row tile split over all SMs, and the 16-bit epilogues' fix-up of
+# the split tiles through the workspace cost 2.3x there (profiles/r1_run29_tp_shard_proxy.txt: q|k|v 39.5 vs 15.3 us).
+ACC32_MAX_ROWS = 128
 USE_PERM8 = True                  # 4-bit 16-bit models: GEMM inputs in the PERM8 column order (include/b200p.h)
 
 

@@ -34,6 +34,10 @@ CONFIGS: Dict[str, dict] = {
     "small-llama": dict(model_type="llama", hidden_size=512, num_hidden_layers=2, intermediate_size=1024,
                         num_attention_heads=4, num_key_value_heads=1, rms_norm_eps=1e-5, vocab_size=1024,
                         rope_theta=500000.0, tie_word_embeddings=False, quantization=dict(group_size=64, bits=4)),
+    # Phi-3 graph (fused qkv_proj / gate_up_proj checkpoint keys, models/phi3.py); D=128, GQA-2
+    "small-phi3": dict(model_type="phi3", hidden_size=512, num_hidden_layers=2, intermediate_size=1024,
+                       num_attention_heads=4, num_key_value_heads=2, rms_norm_eps=1e-5, vocab_size=1024,
+                       rope_theta=10000.0, tie_word_embeddings=False, quantization=dict(group_size=64, bits=4)),
     "mistral-7b": dict(model_type="mistral", hidden_size=4096, num_hidden_layers=32, intermediate_size=14336,
                        num_attention_heads=32, num_key_value_heads=8, rms_norm_eps=1e-5, vocab_size=32000,
                        rope_theta=10000.0, tie_word_embeddings=False, sliding_window=4096,
@@ -153,6 +157,25 @@ def random_weights(cfg: dict, seed: int = 1234, dtype: str = "float16", device="
         g.manual_seed(_stable_seed(seed, name))
         dim = head_dim_of(cfg) if ("q_norm" in name or "k_norm" in name) else cfg["hidden_size"]
         out[name] = (1.0 + 0.02 * torch.randn((dim,), generator=g, device=dev)).to(tdt)
+    return out
+
+
+def to_phi3_checkpoint(weights: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+    """Per-projection tensors -> the key layout of a Phi-3 checkpoint: rows [q | k | v] as ``self_attn.qkv_proj`` and
+    [gate | up] as ``mlp.gate_up_proj`` (reference phi3.py:56-57, 92-96, 117-126)."""
+    out = {}
+    for name, t in weights.items():
+        mod, _, leaf = name.rpartition(".")
+        if mod.endswith(("self_attn.k_proj", "self_attn.v_proj", "mlp.up_proj")):
+            continue
+        if mod.endswith("self_attn.q_proj"):
+            base = mod[:-len("q_proj")]
+            out[f"{base}qkv_proj.{leaf}"] = torch.cat([weights[f"{base}{p}_proj.{leaf}"] for p in "qkv"], 0)
+        elif mod.endswith("mlp.gate_proj"):
+            base = mod[:-len("gate_proj")]
+            out[f"{base}gate_up_proj.{leaf}"] = torch.cat([t, weights[f"{base}up_proj.{leaf}"]], 0)
+        else:
+            out[name] = t
     return out
 
 

@@ -55,6 +55,11 @@ class OracleConfig:
         if rs and (rs.get("type") == "linear" or rs.get("rope_type") == "linear"):
             scale = 1.0 / rs["factor"]                                      # llama.py:69-76
         mt = {"mistral": "llama"}.get(cfg["model_type"], cfg["model_type"])  # utils.py:33-36
+        tie = cfg.get("tie_word_embeddings", True)
+        if mt == "phi3":
+            # phi3.py:43-126, 186-200: the Llama block with fused qkv_proj / gate_up_proj matrices (see split_phi3_weights)
+            # and an lm_head that is never tied
+            mt, tie = "llama", False
         return cls(model_type=mt, hidden_size=cfg["hidden_size"],
                    num_hidden_layers=cfg["num_hidden_layers"],
                    intermediate_size=cfg["intermediate_size"],
@@ -63,8 +68,31 @@ class OracleConfig:
                    rms_norm_eps=cfg["rms_norm_eps"], vocab_size=cfg["vocab_size"],
                    head_dim=cfg.get("head_dim") if mt == "qwen3" else None,
                    rope_theta=cfg.get("rope_theta", 10000.0), rope_scale=scale,
-                   tie_word_embeddings=cfg.get("tie_word_embeddings", True),
+                   tie_word_embeddings=tie,
                    group_size=q.get("group_size", 64), bits=q.get("bits", 4), dtype=dtype)
+
+
+def split_phi3_weights(weights: dict, cfg: dict) -> dict:
+    """Phi-3 checkpoints keep q|k|v in one ``qkv_proj`` and gate|up in one ``gate_up_proj``; the graph splits the
+    OUTPUT of those matmuls (phi3.py:92-96 ``mx.split(qkv, [Hq*D, Hq*D + Hkv*D])``, phi3.py:123-125 ``mx.split(x, 2)``),
+    which equals three / two matmuls with the row blocks -- the form OracleModel evaluates."""
+    D = cfg["hidden_size"] // cfg["num_attention_heads"]                    # phi3.py:53
+    nq = cfg["num_attention_heads"] * D
+    nkv = (cfg.get("num_key_value_heads") or cfg["num_attention_heads"]) * D
+    inter = cfg["intermediate_size"]
+    out = {}
+    for name, t in weights.items():
+        mod, _, leaf = name.rpartition(".")
+        if mod.endswith("self_attn.qkv_proj"):
+            base = mod[:-len("qkv_proj")]
+            out[f"{base}q_proj.{leaf}"], out[f"{base}k_proj.{leaf}"], out[f"{base}v_proj.{leaf}"] = \
+                t[:nq], t[nq:nq + nkv], t[nq + nkv:]
+        elif mod.endswith("mlp.gate_up_proj"):
+            base = mod[:-len("gate_up_proj")]
+            out[f"{base}gate_proj.{leaf}"], out[f"{base}up_proj.{leaf}"] = t[:inter], t[inter:]
+        else:
+            out[name] = t
+    return out
 
 
 class OraclePagedKVCache:

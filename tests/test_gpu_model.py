@@ -26,9 +26,11 @@ def test_prefill_logits_all_positions(name, dtype):
 
 
 @pytest.mark.parametrize("name,dtype,B,L", [("small-llama", "float16", 8, 40), ("tiny-qwen3", "bfloat16", 5, 33),
-                                            ("small-llama", "float16", 2, 32)])
+                                            ("small-llama", "float16", 2, 32), ("small-llama", "float16", 4, 32), ("small-llama", "float16", 3, 32),
+                                            ("small-llama", "float16", 3, 43)])
 def test_prefill_above_and_at_the_fp32_accumulator_limit(name, dtype, B, L):
-    """B*L > 64 rows take the 16-bit fused epilogues (STORE q|k|v, SILU_MUL gate|up), B*L <= 64 the fp32 accumulators:
+    """B*L > ACC32_MAX_ROWS (128) rows take the 16-bit fused epilogues (STORE q|k|v, SILU_MUL gate|up), B*L <= 128 the fp32
+    accumulators (64, 128 rows = whole tiles; 129 = first size above):
     same logits within tolerance, and the decode steps that follow (M = B rows) agree with the oracle."""
     cfg, om, gm = make_pair(name, dtype=dtype)
     ids = prompts_for(cfg, B, L, seed=3)
@@ -150,6 +152,26 @@ def test_load_model_from_mlx_checkpoint(tmp_path):
     ids = prompts_for(cfg, 2, 5)
     assert torch.equal(m(torch.from_numpy(ids)), gm(torch.from_numpy(ids)))
     assert m.head_dim == 64 and m.n_kv_heads == 2 and len(m.layers) == 3 and m.model_type == "qwen3"
+
+
+def test_phi3_checkpoint_with_fused_projections(tmp_path):
+    """Phi-3 (reference models/phi3.py): the checkpoint holds qkv_proj / gate_up_proj; logits and greedy ids against the
+    oracle's restatement of the same graph, loaded through load_model from the fused keys."""
+    from mlx_parallm_b200 import synth, utils
+    from oracle.model import OracleConfig, OracleModel, split_phi3_weights
+    cfg = synth.get_config("small-phi3")
+    ck = synth.to_phi3_checkpoint(synth.random_weights(cfg, seed=21, dtype="float16"))
+    synth.save_checkpoint(str(tmp_path), cfg, ck)
+    gm = utils.load_model(tmp_path)
+    assert gm.model_type == "phi3" and gm.head_dim == 128 and gm.n_kv_heads == 2 and gm.lm_head is not None
+    om = OracleModel(OracleConfig.from_hf(cfg, "float16"), split_phi3_weights(synth.to_numpy_weights(ck), cfg))
+    ids = prompts_for(cfg, 5, 19)
+    exp = om.forward(ids, om.make_cache(5), last_only=True)
+    got = gm(torch.from_numpy(ids), cache=gm.make_cache(5), last_only=True).cpu().numpy()
+    assert rel_err(got, exp) < LOGIT_TOL
+    g = run_greedy(gm, ids, 16)
+    e = np.stack([y[:, 0] for _, (y, _) in zip(range(16), oracle_generate_step(ids, om))], 1)
+    assert sequences_identical(g, e).all()
 
 
 def test_convert_quantizes_a_dense_checkpoint_like_the_oracle(tmp_path):

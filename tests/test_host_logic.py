@@ -27,6 +27,39 @@ def test_model_args_from_dict_drops_unknown_keys_and_defaults():
     assert q.head_dim == 128
 
 
+def test_phi3_fused_checkpoint_keys_split_into_the_projection_blocks():
+    """models/phi3.py: qkv_proj rows [q | k | v], gate_up_proj rows [gate | up] (reference phi3.py:92-96, 123-125); the
+    CUDA model's splitter and the oracle's agree with the per-projection tensors the checkpoint was fused from."""
+    from mlx_parallm_b200.models import phi3
+    from mlx_parallm_b200.utils import _get_classes
+    from oracle.model import OracleConfig, split_phi3_weights
+    cfg = synth.get_config("small-phi3")
+    Model, Args = _get_classes(cfg)
+    assert Model is phi3.Model
+    a = Args.from_dict(dict(cfg, sliding_window=2047))
+    assert a.tie_word_embeddings is False and a.num_key_value_heads == 2
+    w = synth.random_weights(cfg, seed=5, dtype="float16")
+    ck = synth.to_phi3_checkpoint(w)
+    assert "model.layers.0.self_attn.qkv_proj.weight" in ck and "model.layers.1.mlp.gate_up_proj.scales" in ck
+    assert not any(".q_proj." in k or ".up_proj." in k for k in ck)
+    assert ck["model.layers.0.self_attn.qkv_proj.weight"].shape == ((4 + 2 * 2) * 128, 512 // 8)
+    back = Model(a).split_fused(ck)
+    assert set(back) == set(w) and all(torch.equal(back[k], w[k]) for k in w)
+    ob = split_phi3_weights(synth.to_numpy_weights(ck), cfg)
+    wn = synth.to_numpy_weights(w)
+    assert set(ob) == set(wn) and all(np.array_equal(ob[k], wn[k]) for k in wn)
+    oc = OracleConfig.from_hf(cfg, "float16")
+    assert oc.model_type == "llama" and oc.tie_word_embeddings is False and oc.head_dim == 128
+    with pytest.raises(NotImplementedError):                               # su_rope.py is not built
+        Args.from_dict(dict(cfg, rope_scaling={"type": "su", "long_factor": [1.0] * 64, "short_factor": [1.0] * 64}))
+    with pytest.raises(ValueError):
+        Args.from_dict(dict(cfg, rope_scaling={"type": "su"}))
+    bad = dict(ck)
+    bad["model.layers.0.self_attn.qkv_proj.weight"] = bad["model.layers.0.self_attn.qkv_proj.weight"][:-8]
+    with pytest.raises(ValueError):
+        Model(a).split_fused(bad)
+
+
 def test_byte_model_matches_baseline_md():
     gb = lambda n: synth.weight_bytes_per_step(synth.get_config(n)) / 1e9
     assert gb("mistral-7b") == pytest.approx(4.000, abs=2e-3)
