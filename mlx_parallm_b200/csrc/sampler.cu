@@ -51,6 +51,31 @@ __device__ __forceinline__ void osm_merge(float& m, float& s, float om, float os
   m = nm;
 }
 
+// every element of the row once, f(value, index): 16-byte loads when the row allows, four in flight per thread (one CTA
+// streams its row out of L2 at the rate its loads in flight allow: 1024 threads x 64 B against ~1 us of latency)
+template <typename F>
+__device__ __forceinline__ void row_visit(const float* __restrict__ row, int64_t V, bool vec, F&& f) {
+  const int64_t nt = blockDim.x;
+  const int64_t V4 = vec ? V / 4 : 0;
+  const float4* r4 = reinterpret_cast<const float4*>(row);
+  int64_t i = threadIdx.x;
+  for (; i + 3 * nt < V4; i += 4 * nt) {
+    float4 v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = r4[i + j * nt];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int64_t e = 4 * (i + j * nt);
+      f(v[j].x, e); f(v[j].y, e + 1); f(v[j].z, e + 2); f(v[j].w, e + 3);
+    }
+  }
+  for (; i < V4; i += nt) {
+    const float4 a = r4[i];
+    f(a.x, 4 * i); f(a.y, 4 * i + 1); f(a.z, 4 * i + 2); f(a.w, 4 * i + 3);
+  }
+  for (int64_t j = V4 * 4 + threadIdx.x; j < V; j += nt) f(row[j], j);
+}
+
 __global__ void __launch_bounds__(SAMP_THREADS)
 argmax_kernel(const float* __restrict__ logits, int32_t* __restrict__ tokens, float* __restrict__ probs_out,
               int64_t V, int64_t ldl, float4* __restrict__ rec_out, int vocab_offset) {
@@ -64,22 +89,12 @@ argmax_kernel(const float* __restrict__ logits, int32_t* __restrict__ tokens, fl
   float om = -INFINITY, os = 0.f;
   const bool want_p = probs_out != nullptr || rec_out != nullptr;
   const bool vec = (ldl % 4 == 0) && ((reinterpret_cast<uintptr_t>(logits) & 15) == 0);
-  int64_t V4 = vec ? V / 4 : 0;
-  for (int64_t i = threadIdx.x; i < V4; i += blockDim.x) {
-    float4 v = reinterpret_cast<const float4*>(row)[i];
-    int base = (int)(4 * i);
-    // NaN never wins (comparisons false), matching a total order that ignores NaN
-    if (v.x > best) { best = v.x; bi = base; }
-    if (v.y > best) { best = v.y; bi = base + 1; }
-    if (v.z > best) { best = v.z; bi = base + 2; }
-    if (v.w > best) { best = v.w; bi = base + 3; }
-    if (want_p) { osm_push(om, os, v.x); osm_push(om, os, v.y); osm_push(om, os, v.z); osm_push(om, os, v.w); }
-  }
-  for (int64_t i = V4 * 4 + threadIdx.x; i < V; i += blockDim.x) {
-    float v = row[i];
+  // NaN never wins (comparisons false), matching a total order that ignores NaN; a thread sees its indices in ascending
+  // order, so the strict compare keeps the lowest index among its ties
+  row_visit(row, V, vec, [&](float v, int64_t i) {
     if (v > best) { best = v; bi = (int)i; }
     if (want_p) osm_push(om, os, v);
-  }
+  });
   if (want_p) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -166,143 +181,169 @@ __device__ __forceinline__ float block_reduce(float v, float* sh, bool is_max) {
   return v;
 }
 
-// Nucleus sampling, one CTA per row.
-//  1. mx = max(logit), Z = sum exp((logit-mx)/temp)       -> p_i = exp((logit_i-mx)/temp)/Z
-//  2. radix-select (4 x 8-bit digits over the float bits of p_i, which are monotone for p >= 0) the
-//     value v* of the first sorted element whose inclusive cumulative mass exceeds top_p; the nucleus
-//     is {p_i > v*}; its mass is `kept`.
-//  3. u ~ U(0,kept): pick the token where the running mass (in index order) over the nucleus crosses u.
-__global__ void __launch_bounds__(SAMP_THREADS)
+// Nucleus sampling, one CTA per row; the row (V floats, <= 600 KB) stays in L2 and is re-read on each pass.
+//  1. mx = max(logit).
+//  2. e_i = exp((logit_i - mx) / temp) in (0, 1], Z = sum e_i.  The nucleus is found by radix-select over the float bits of
+//     e_i (monotone for e >= 0; bits 31..30 are 0 because e <= 1), most significant digit first, 6 bits per pass: the MASS of
+//     the elements carrying each digit value (under the prefix chosen so far) is accumulated, then the digits are walked
+//     from the top until the inclusive cumulative mass would exceed top_p * Z.  After 5 passes the prefix is the value v* of
+//     the first sorted element that does not fit; the nucleus is {e_i > v*}, its mass `kept`.  (Selection is by VALUE: when
+//     the boundary falls inside a run of exactly equal probabilities the whole run is dropped, where the reference keeps as
+//     many of the run as fit in the unspecified order its argsort leaves ties.)
+//     The histograms are LANE-PRIVATE ([64 digits][512 threads] floats in shared memory, bank = thread, summed per digit at
+//     the end of a pass): no atomics.  Shared-memory float atomics are CAS loops and thousands of tokens share the leading
+//     digits -- the first version of this kernel (one shared 256-bin histogram) took 600 us per step at V = 128 256.
+//  3. u ~ U(0, kept): pick the token where the running mass over the nucleus crosses u.  The enumeration order is
+//     thread-major (thread t owns the 16-byte groups t, t + 512, ...), as valid an order for a categorical draw as any.
+constexpr int TP_THREADS = 512;
+constexpr int TP_BINS = 64;
+constexpr int TP_PASSES = 5;                       // 5 x 6 bits = bits 29..0
+constexpr int TP_SMEM = TP_BINS * TP_THREADS * (int)sizeof(float);
+
+__global__ void __launch_bounds__(TP_THREADS)
 top_p_kernel(const float* __restrict__ logits, int32_t* __restrict__ tokens, float* __restrict__ probs_out,
              int64_t V, int64_t ldl, float inv_temp, float top_p, uint64_t seed, uint64_t offset) {
+  extern __shared__ float lhist[];                 // [TP_BINS][TP_THREADS]
   __shared__ float sh[32];
-  __shared__ float hist[256];
-  __shared__ uint32_t s_prefix;
+  __shared__ float hist[TP_BINS];
+  __shared__ uint32_t s_prefix, s_thr;
   __shared__ float s_above;
   __shared__ int s_done;
-  __shared__ float s_scan[SAMP_THREADS];
-  __shared__ int s_tok;
+  __shared__ float s_scan[TP_THREADS];
+  __shared__ int s_tok, s_last;
   pdl_wait();
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const float* row = logits + (int64_t)blockIdx.x * ldl;
+  const bool vec = (ldl % 4 == 0) && ((reinterpret_cast<uintptr_t>(logits) & 15) == 0);
 
   float mx = -INFINITY;
-  for (int64_t i = tid; i < V; i += blockDim.x) mx = fmaxf(mx, row[i]);
+  row_visit(row, V, vec, [&](float x, int64_t) { mx = fmaxf(mx, x); });
   mx = block_reduce(mx, sh, true);
-  float z = 0.f, z1 = 0.f;
-  for (int64_t i = tid; i < V; i += blockDim.x) {
-    float d = row[i] - mx;
-    z += __expf(d * inv_temp);
-    z1 += __expf(d);
-  }
-  z = block_reduce(z, sh, false);
-  z1 = block_reduce(z1, sh, false);
-  const float inv_z = 1.0f / z;
 
-  uint32_t thr_bits = 0u;  // nucleus = {bits(p) > thr_bits}; 0 keeps every p > 0
-  float kept = 1.0f;
+  float z = 0.f, z1 = 0.f;
+  uint32_t thr_bits = 0u;  // nucleus = {bits(e) > thr_bits}; 0 keeps every e > 0
   bool empty = false;
-  if (top_p < 1.0f) {
-    if (tid == 0) { s_prefix = 0u; s_above = 0.f; s_done = 0; }
-    __syncthreads();
-    for (int pass = 0; pass < 4; ++pass) {
-      const int shift = 24 - 8 * pass;
-      if (tid < 256) hist[tid] = 0.f;
+  if (!(top_p < 1.0f)) {   // plain categorical(logits / temp)
+    row_visit(row, V, vec, [&](float x, int64_t) {
+      const float d = x - mx;
+      z += __expf(d * inv_temp);
+      z1 += __expf(d);
+    });
+    z1 = block_reduce(z1, sh, false);
+  } else {
+    if (tid == 0) { s_prefix = 0u; s_thr = 0u; s_above = 0.f; s_done = 0; }
+    float target = 0.f;
+    for (int pass = 0; pass < TP_PASSES; ++pass) {
+      const int shift = 24 - 6 * pass;
+#pragma unroll 8
+      for (int b = 0; b < TP_BINS; ++b) lhist[b * TP_THREADS + tid] = 0.f;
       __syncthreads();
-      const uint32_t prefix = s_prefix;
-      const uint32_t pmask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
-      for (int64_t i = tid; i < V; i += blockDim.x) {
-        float p = __expf((row[i] - mx) * inv_temp) * inv_z;
-        uint32_t bits = __float_as_uint(p);
-        if ((bits & pmask) == prefix) atomicAdd(&hist[(bits >> shift) & 0xffu], p);
+      const uint32_t prefix = s_prefix;            // bits(e) >> (shift + 6) of the elements still in play
+      const bool done = s_done != 0;
+      if (!done) {
+        if (pass == 0) {
+          row_visit(row, V, vec, [&](float x, int64_t) {
+            const float d = x - mx;
+            const float e = __expf(d * inv_temp);
+            z += e;
+            z1 += __expf(d);
+            const uint32_t bits = __float_as_uint(e);
+            if ((bits >> 30) == 0u) lhist[(bits >> 24) * TP_THREADS + tid] += e;     // NaN stays out
+          });
+        } else {
+          row_visit(row, V, vec, [&](float x, int64_t) {
+            const float e = __expf((x - mx) * inv_temp);
+            const uint32_t bits = __float_as_uint(e);
+            if ((bits >> (shift + 6)) == prefix) lhist[((bits >> shift) & 63u) * TP_THREADS + tid] += e;
+          });
+        }
+      }
+      if (pass == 0) {
+        z = block_reduce(z, sh, false);
+        z1 = block_reduce(z1, sh, false);
+        target = top_p * z;
       }
       __syncthreads();
-      if (tid == 0 && !s_done) {
+      // digit totals: warp w sums digits 4w .. 4w+3 over the 512 lane-private columns
+      for (int b = warp * (TP_BINS / (TP_THREADS / 32)); b < (warp + 1) * (TP_BINS / (TP_THREADS / 32)); ++b) {
+        float v = 0.f;
+#pragma unroll
+        for (int j = 0; j < TP_THREADS / 32; ++j) v += lhist[b * TP_THREADS + lane + 32 * j];
+        v = warp_sum(v);
+        if (lane == 0) hist[b] = v;
+      }
+      __syncthreads();
+      if (tid == 0 && !done) {
         float above = s_above;
-        int d = 255;
+        int d = TP_BINS - 1;
         for (; d >= 0; --d) {
-          if (above + hist[d] > top_p) break;
+          if (above + hist[d] > target) break;
           above += hist[d];
         }
         s_above = above;
         if (d < 0) {
-          // nothing in this bucket crosses top_p (pass 0: the whole row fits; later passes: only
-          // through atomic-order rounding) -> every element carrying this prefix is kept
+          // nothing under this prefix crosses top_p (pass 0: the whole row fits; later passes: only through summation-order
+          // rounding) -> every element carrying the prefix is kept
+          const uint32_t lowest = prefix << (shift + 6);
           s_done = 1;
-          s_prefix = prefix == 0u ? 0u : prefix - 1u;
+          s_thr = lowest == 0u ? 0u : lowest - 1u;
         } else {
-          s_prefix = prefix | ((uint32_t)d << shift);
+          s_prefix = (prefix << 6) | (uint32_t)d;
+          if (pass == TP_PASSES - 1) s_thr = (prefix << 6) | (uint32_t)d;
         }
       }
       __syncthreads();
     }
-    thr_bits = s_prefix;
-    kept = s_above;
-    if (!s_done && kept <= 0.f) empty = true;  // even the largest p exceeds top_p (reference: 0/0)
+    thr_bits = s_thr;
+    if (!s_done && s_above <= 0.f) empty = true;   // even the largest p exceeds top_p (reference: 0/0)
   }
 
   int tok = -1;
-  if (empty) {
-    float best = -INFINITY;
-    int bi = 0x7fffffff;
-    for (int64_t i = tid; i < V; i += blockDim.x) {
-      float v = row[i];
-      if (v > best) { best = v; bi = (int)i; }
-    }
-    __shared__ int shi[32];
-    block_argmax(best, bi, sh, shi);
-    tok = bi;
-  } else {
-    // contiguous chunk per thread -> block scan -> owner walks its chunk
-    const int64_t chunk = (V + blockDim.x - 1) / blockDim.x;
-    const int64_t lo = (int64_t)tid * chunk, hi = min(lo + chunk, V);
-    float local = 0.f;
-    for (int64_t i = lo; i < hi; ++i) {
-      float p = __expf((row[i] - mx) * inv_temp) * inv_z;
-      if (__float_as_uint(p) > thr_bits) local += p;
-    }
-    s_scan[tid] = local;
+  if (empty) {                                     // documented deviation: the argmax (lowest index among ties)
+    if (tid == 0) s_tok = 0x7fffffff;
     __syncthreads();
-    // inclusive Hillis-Steele scan (1024 elements, 10 steps)
-    for (int o = 1; o < SAMP_THREADS; o <<= 1) {
-      float add = tid >= o ? s_scan[tid - o] : 0.f;
+    int bi = 0x7fffffff;
+    row_visit(row, V, vec, [&](float x, int64_t i) { if (x == mx && (int)i < bi) bi = (int)i; });
+    if (bi != 0x7fffffff) atomicMin(&s_tok, bi);
+    __syncthreads();
+    tok = s_tok == 0x7fffffff ? 0 : s_tok;
+  } else {
+    float local = 0.f;
+    int mylast = -1;
+    row_visit(row, V, vec, [&](float x, int64_t i) {
+      const float e = __expf((x - mx) * inv_temp);
+      if (__float_as_uint(e) > thr_bits) { local += e; mylast = max(mylast, (int)i); }
+    });
+    s_scan[tid] = local;
+    if (tid == 0) { s_tok = -1; s_last = -1; }
+    __syncthreads();
+    // inclusive Hillis-Steele scan over the threads
+    for (int o = 1; o < TP_THREADS; o <<= 1) {
+      const float add = tid >= o ? s_scan[tid - o] : 0.f;
       __syncthreads();
       s_scan[tid] += add;
       __syncthreads();
     }
-    const float total = s_scan[SAMP_THREADS - 1];
+    const float total = s_scan[TP_THREADS - 1];
     const float u = philox_uniform(seed, offset, blockIdx.x) * total;
-    if (tid == 0) s_tok = -1;
-    __syncthreads();
     const float before = tid ? s_scan[tid - 1] : 0.f;
-    if (local > 0.f && u >= before && u < s_scan[tid]) {
+    if (local > 0.f && u >= before && u < s_scan[tid]) {   // the owner walks its elements in the same order
       float run = before;
       int pick = -1, last = -1;
-      for (int64_t i = lo; i < hi; ++i) {
-        float p = __expf((row[i] - mx) * inv_temp) * inv_z;
-        if (__float_as_uint(p) > thr_bits) {
-          run += p;
+      row_visit(row, V, vec, [&](float x, int64_t i) {
+        const float e = __expf((x - mx) * inv_temp);
+        if (__float_as_uint(e) > thr_bits) {
+          run += e;
           last = (int)i;
           if (pick < 0 && u < run) pick = (int)i;
         }
-      }
+      });
       s_tok = pick >= 0 ? pick : last;
     }
+    if (mylast >= 0) atomicMax(&s_last, mylast);
     __syncthreads();
     tok = s_tok;
-    if (tok < 0) {  // u landed on a rounding seam: take the last nucleus token
-      int cand = -1;
-      for (int64_t i = hi - 1; i >= lo; --i) {
-        float p = __expf((row[i] - mx) * inv_temp) * inv_z;
-        if (__float_as_uint(p) > thr_bits) { cand = (int)i; break; }
-      }
-      __shared__ int s_last;
-      if (tid == 0) s_last = -1;
-      __syncthreads();
-      if (cand >= 0) atomicMax(&s_last, cand);
-      __syncthreads();
-      tok = s_last < 0 ? 0 : s_last;
-    }
+    if (tok < 0) tok = s_last < 0 ? 0 : s_last;    // u landed on a rounding seam: take the last nucleus token
   }
   if (tid == 0) {
     tokens[blockIdx.x] = tok;
@@ -359,8 +400,14 @@ extern "C" int b200p_sample_top_p(const float* logits, int32_t* tokens, float* p
   B200P_REQUIRE(temperature > 0.f, B200P_ERR_ARG, "temperature must be > 0 (use b200p_argmax for greedy)");
   if (B == 0) return B200P_OK;
   if (!(top_p > 0.f)) top_p = 1.0f;
-  launch_pdl(top_p_kernel, (unsigned)B, SAMP_THREADS, 0, (cudaStream_t)stream, logits, tokens, probs_out, V, ldl,
-                                                                      1.0f / temperature, top_p, seed, offset);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(top_p_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TP_SMEM);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(top_p_kernel)");
+    attr_set = true;
+  }
+  launch_pdl(top_p_kernel, (unsigned)B, TP_THREADS, TP_SMEM, (cudaStream_t)stream, logits, tokens, probs_out, V, ldl,
+             1.0f / temperature, top_p, seed, offset);
   B200P_LAUNCH_CHECK("top_p_kernel");
   return B200P_OK;
 }

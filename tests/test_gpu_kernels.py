@@ -308,6 +308,51 @@ def test_top_p_sampling_distribution(ops, top_p, temp):
     assert not np.array_equal(tok, tok3)
 
 
+@pytest.mark.parametrize("V,top_p,temp", [(128256, 0.9, 0.7), (151937, 0.6, 1.0), (32000, 0.95, 1.2)])
+def test_top_p_large_vocab_stays_in_the_oracle_nucleus(ops, V, top_p, temp):
+    """BASELINE vocab sizes (151 937 = unaligned rows -> scalar loads): LM-like logits (a gaussian body, a few large values,
+    a block of exactly equal logits as untrained vocab slots have), 1500 draws: every token inside the oracle's nucleus,
+    frequencies of the heavy tokens as the oracle's renormalised distribution says."""
+    rng = np.random.default_rng(V)
+    n = 1500
+    lg = (rng.standard_normal(V) * 2.0).astype(np.float32)
+    lg[rng.choice(V, 40, replace=False)] = (8.0 + 1.5 * rng.random(40)).astype(np.float32)
+    lg[1000:3000] = -3.25
+    dist = ref.top_p_distribution(lg[None], top_p, temp)[0]
+    assert 5 < (dist > 0).sum() < V
+    logits = torch.from_numpy(lg).cuda().repeat(n, 1)
+    probs = torch.zeros(n, device="cuda")
+    tok = ops.sample_top_p(logits, temp, top_p, seed=5, offset=9, probs_out=probs).cpu().numpy()
+    assert dist[tok].min() > 0, "sampled a token outside the nucleus"
+    freq = np.bincount(tok, minlength=V) / n
+    big = dist > 0.008
+    assert big.sum() >= 3 and np.abs(freq[big] - dist[big]).max() < 4 * np.sqrt(dist[big].max() / n) + 5e-3
+    sm = ref.softmax(lg[None])[0]
+    assert np.allclose(probs.cpu().numpy(), sm[tok], rtol=2e-3)        # probs = softmax(logits)[token] (utils.py:363)
+    # top_p = 1: plain categorical over the whole vocabulary
+    tok1 = ops.sample_top_p(logits, temp, 1.0, seed=5, offset=9).cpu().numpy()
+    d1 = ref.top_p_distribution(lg[None], 1.0, temp)[0]
+    big1 = d1 > 0.008
+    f1 = np.bincount(tok1, minlength=V) / n
+    assert np.abs(f1[big1] - d1[big1]).max() < 4 * np.sqrt(d1[big1].max() / n) + 5e-3
+
+
+def test_top_p_exact_boundary_and_ties(ops):
+    """cum <= top_p keeps exactly the prefix the reference keeps (sample_utils.py:25-31): p = .4 .3 .2 .1 with top_p .75 ->
+    {0, 1}; top_p .95 -> {0, 1, 2}.  A nucleus that ends inside a run of EQUAL probabilities: the reference keeps as many of the run as fit, in
+    whatever order its argsort leaves ties; this kernel selects by value and drops the run (documented in sampler.cu)."""
+    p = np.array([0.4, 0.3, 0.2, 0.1], np.float32)
+    lg = torch.from_numpy(np.tile(np.log(p), (4096, 1))).cuda()
+    t = ops.sample_top_p(lg, 1.0, 0.75, 3, 0).cpu().numpy()
+    assert set(t.tolist()) == {0, 1} and abs((t == 0).mean() - 4 / 7) < 0.04
+    t = ops.sample_top_p(lg, 1.0, 0.95, 3, 1).cpu().numpy()
+    assert set(t.tolist()) == {0, 1, 2}
+    q = np.array([0.4, 0.2, 0.2, 0.2], np.float32)          # cum: .4 .6 .8 1.0, top_p .7 cuts inside the run of .2s
+    lq = torch.from_numpy(np.tile(np.log(q), (1024, 1))).cuda()
+    t = ops.sample_top_p(lq, 1.0, 0.7, 3, 2).cpu().numpy()
+    assert set(t.tolist()) <= {0, 1, 2, 3} and (t == 0).mean() > 0.6
+
+
 def test_top_p_empty_nucleus_returns_argmax(ops):
     lg = np.log(np.array([[0.6, 0.3, 0.1]], np.float32))
     tok = ops.sample_top_p(torch.from_numpy(np.tile(lg, (64, 1))).cuda(), 1.0, 0.5, 1, 0)
