@@ -160,7 +160,9 @@ int b200p_attn_set_path(int path);
 
 /* mx.argmax(logits, axis=-1, keepdims=True)                         [utils.py:350-352,363]
  * logits float [B, V] (ldl floats between rows) -> tokens int32 [B]; lowest index among ties.
- * probs_out (optional, float [B]) receives softmax(logits)[b, token] computed in the same pass. */
+ * probs_out (optional, float [B]) receives softmax(logits)[b, token] computed in the same pass.
+ * B <= 65535.  Each row is split over a thread-block cluster of 8 / 4 / 2 / 1 CTAs so that B x cluster fills the SMs once
+ * (env B200P_SAMPLER_CLUSTER forces a size); the same holds for b200p_argmax_partial and b200p_sample_top_p. */
 int b200p_argmax(const float* logits, int32_t* tokens, float* probs_out, int64_t B, int64_t V,
                  int64_t ldl, void* stream);
 
@@ -178,6 +180,7 @@ int b200p_argmax_merge(const float* recs /* [W, B, 4] */, int32_t* tokens, float
  * Draws from the renormalised nucleus {tokens whose inclusive sorted cumulative mass <= top_p}
  * (top_p >= 1 -> plain categorical).  Philox counter RNG keyed by (seed, offset, row).
  * If the nucleus is empty (p_max > top_p; the reference divides 0/0) the argmax is returned.
+ * Selection is by value: a nucleus that ends inside a run of exactly equal probabilities drops the run.
  * probs_out (optional, float [B]) receives softmax(logits)[b, token] (untempered, utils.py:363). */
 int b200p_sample_top_p(const float* logits, int32_t* tokens, float* probs_out, int64_t B,
                        int64_t V, int64_t ldl, float temperature, float top_p, uint64_t seed,
