@@ -163,7 +163,10 @@ extern "C" int b200p_qmm(const void* x, const uint32_t* w, const void* scales, c
   const bool mma_ok = qmv_mma_supported(M, N, K, group_size, bits, dtype, epilogue) && aligned(y, 4) &&
                       !(flags & B200P_Y_PERM8);
   if (g_qmm_path == 3) B200P_REQUIRE(mma_ok, B200P_ERR_ARG, "mma.sync GEMV forced but unsupported for this call");
-  if (mma_ok && (g_qmm_path == 3 || (g_qmm_path == 0 && M <= g_gemv_max_m && N * K <= g_gemv_max_weights)))
+  // up to two rows the GEMV also wins on matrices of twice that size (down_proj 4096 x 14336: 12.8 vs 14.1 us at M = 1,
+  // profiles/r1_run34_gemv_splits.txt); gate|up (117 M weights) stays on the tile kernel
+  if (mma_ok && (g_qmm_path == 3 || (g_qmm_path == 0 && M <= g_gemv_max_m &&
+                                     N * K <= (M <= 2 ? 2 * g_gemv_max_weights : g_gemv_max_weights))))
     return qmv_mma_launch(x, w, scales, biases, y, M, N, K, ldx, ldy, dtype, epilogue, flags, st);
   const bool tc_ok = qmm_tc_supported(M, N, K, group_size, bits, dtype, epilogue);
   if (g_qmm_path == 2) {

@@ -174,13 +174,29 @@ static int launch_qmv_mma(const void* x, const uint32_t* w, const void* s, const
                           int64_t K, int64_t ldx, int64_t ldy, int epi, bool xperm, cudaStream_t st) {
   const int64_t row_groups = N / 16;
   const int64_t total_steps = K / QM_STEP_K;
-  // enough warps to cover the HBM latency on every SM (~16 per SM); plain stores cannot be split
+  // Split-K so that every SM holds ~16 warps, but never a grid that spills a few CTAs into a second wave (4096 x 14336 at ten
+  // splits was 640 CTAs on 592 slots: 1.08 waves, 30 % slower than 8 splits in one wave): among the split counts pick the
+  // one with the lowest waves x (steps per warp + ~1.5 steps of fixed latency); ties go to fewer splits (fewer red.adds).  Plain stores cannot
+  // be split.  (More weights in flight per lane instead of more warps was tried and is slower:
+  // profiles/r1_run33_gemv_prefetch_depth_experiment.txt.)
   int64_t splits = 1;
   if (epi == B200P_EPI_ADD_RESIDUAL) {
-    const int64_t want = (int64_t)sm_count() * 16;
-    splits = (want + row_groups - 1) / row_groups;
-    if (splits > total_steps / 2) splits = total_steps / 2;     // at least two steps per warp
-    if (splits < 1) splits = 1;
+    const int64_t capacity = (int64_t)sm_count() * 4;            // resident CTAs: 4 per SM at 121 registers x 128 threads
+    const int64_t max_splits = total_steps / 2 > 1 ? total_steps / 2 : 1;   // at least two steps per warp
+    double best = 1e30;
+    for (int64_t sp = 1; sp <= max_splits; ++sp) {
+      const int64_t sps_c = (total_steps + sp - 1) / sp;
+      const int64_t sp_eff = (total_steps + sps_c - 1) / sps_c;
+      const int64_t ctas = (row_groups * sp_eff + QM_WARPS - 1) / QM_WARPS;
+      // a partly filled wave after the first costs its fill fraction, but never less than half a wave (measured: 28672 x 4096 runs
+      // 24.1 us as 1.51 waves of 8 steps against 25.5 us as 0.76 wave of 16; 4096 x 14336 16.9 us as 1.08 waves of 6 steps
+      // against 12.9 us as 0.86 wave of 7 -- profiles/r1_run34_gemv_splits.txt)
+      const int64_t full = ctas / capacity;
+      const double frac = (double)(ctas - full * capacity) / (double)capacity;
+      const double waves = full == 0 ? 1.0 : (double)full + (frac > 0.0 ? (frac > 0.5 ? frac : 0.5) : 0.0);
+      const double cost = waves * ((double)sps_c + 1.5) * (full == 0 ? 1.0 : 1.1);   // near-ties go to the single wave
+      if (cost < best - 1e-9) { best = cost; splits = sp_eff; }
+    }
   }
   const int64_t sps = (total_steps + splits - 1) / splits;
   splits = (total_steps + sps - 1) / sps;
