@@ -160,7 +160,7 @@ extern "C" int b200p_qmm(const void* x, const uint32_t* w, const void* scales, c
   if (M == 0) return B200P_OK;
   PdlClass pdl_cls(64);
   cudaStream_t st = (cudaStream_t)stream;
-  const bool mma_ok = qmv_mma_supported(M, N, K, group_size, bits, dtype, epilogue) && aligned(y, 4) &&
+  const bool mma_ok = qmv_mma_supported(M, N, K, group_size, bits, dtype, epilogue) && aligned(y, 4) && aligned(w, 32) &&
                       !(flags & B200P_Y_PERM8);
   if (g_qmm_path == 3) B200P_REQUIRE(mma_ok, B200P_ERR_ARG, "mma.sync GEMV forced but unsupported for this call");
   // up to two rows the GEMV also wins on matrices of twice that size (down_proj 4096 x 14336: 12.8 vs 14.1 us at M = 1,

@@ -77,6 +77,14 @@ __device__ __forceinline__ uint4 ldg_stream(const void* p) {
   return r;
 }
 
+// streaming 256-bit load (sm_100: LDG.E.256): one whole 32-byte sector per lane.  Two 128-bit loads of the two halves of a
+// sector by the same lane make the warp request every sector twice (each instruction touches half of it).
+__device__ __forceinline__ void ldg_stream256(const void* p, uint4& lo, uint4& hi) {
+  asm volatile("ld.global.nc.L1::no_allocate.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(lo.x), "=r"(lo.y), "=r"(lo.z), "=r"(lo.w), "=r"(hi.x), "=r"(hi.y), "=r"(hi.z), "=r"(hi.w)
+               : "l"(p));
+}
+
 // exact small-integer -> float via the 2^23 magic (avoids I2F)
 __device__ __forceinline__ float u8_to_float(uint32_t q) {
   return __uint_as_float(0x4B000000u | q) - 8388608.0f;

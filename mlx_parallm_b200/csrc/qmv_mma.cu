@@ -90,10 +90,8 @@ qmv_mma_kernel(const T* __restrict__ x, const uint32_t* __restrict__ w, const T*
   uint32_t s2a = 0, b2a = 0, s2b = 0, b2b = 0;
   auto fetch_w = [&](int64_t s) {
     const int64_t wo = s * (QM_STEP_K / 8);
-    qa[0] = ldg_stream(w0 + wo);
-    qa[1] = ldg_stream(w0 + wo + 4);
-    qb[0] = ldg_stream(w1 + wo);
-    qb[1] = ldg_stream(w1 + wo + 4);
+    ldg_stream256(w0 + wo, qa[0], qa[1]);       // the lane's 64 codes of the step = one 32-byte sector per row
+    ldg_stream256(w1 + wo, qb[0], qb[1]);
     s2a = dup16(__ldg(sc0 + 4 * s));
     b2a = dup16(__ldg(bi0 + 4 * s));
     s2b = dup16(__ldg(sc1 + 4 * s));
@@ -220,7 +218,7 @@ static int launch_qmv_mma(const void* x, const uint32_t* w, const void* s, const
 
 int qmv_mma_launch(const void* x, const uint32_t* w, const void* s, const void* b, void* y, int64_t M, int64_t N, int64_t K,
                    int64_t ldx, int64_t ldy, int dtype, int epi, int flags, cudaStream_t st) {
-  B200P_REQUIRE(aligned(s, 2) && aligned(b, 2) && aligned(y, 4), B200P_ERR_ALIGN, "bad alignment");
+  B200P_REQUIRE(aligned(s, 2) && aligned(b, 2) && aligned(y, 4) && aligned(w, 32), B200P_ERR_ALIGN, "bad alignment (weights: 32 bytes)");
   const bool xperm = (flags & B200P_X_PERM8) != 0;
   if (dtype == B200P_F16) return launch_qmv_mma<__half>(x, w, s, b, y, M, N, K, ldx, ldy, epi, xperm, st);
   return launch_qmv_mma<__nv_bfloat16>(x, w, s, b, y, M, N, K, ldx, ldy, epi, xperm, st);
