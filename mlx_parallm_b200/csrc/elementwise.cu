@@ -321,6 +321,92 @@ __global__ void rope_kv_append_kernel(TIN* __restrict__ qkv, T* __restrict__ q_o
   }
 }
 
+// head_dim 128 (every BASELINE model): a WARP per (token, head), 8 heads of a token per CTA; lane = pairs (2*lane, 2*lane + 1)
+// of the first half and their partners 64 further.  The kernel is pure latency (4 MB of traffic): every warp issues its
+// position load and its four 8-byte value loads at once and finishes after one round trip; the per-head RMSNorm of Qwen3 is a
+// warp reduction (no block barrier); 8-byte (fp32 input) / 4-byte (16-bit) accesses per lane, whole lines per warp.
+// (A warp looping over 6 heads to reuse its sincos was tried first: 6 dependent round trips, slower -- 18 us cold in ncu
+// against 14.6 us for the generic kernel above, profiles/r1_run37_small_kernels_ncu.txt.)
+template <typename T, typename TIN>
+__global__ void __launch_bounds__(256)
+rope_kv_append_d128_kernel(TIN* __restrict__ qkv, T* __restrict__ q_out, T* __restrict__ kc, T* __restrict__ vc,
+                           const int32_t* __restrict__ lengths, const T* __restrict__ qn_w, const T* __restrict__ kn_w,
+                           int L, int Hq, int Hkv, int64_t Tcap, float log2_base, float rope_scale, float eps) {
+  constexpr int D = 128, HALF = 64;
+  constexpr bool ACC_IN = std::is_same<TIN, float>::value && !std::is_same<T, float>::value;
+  pdl_wait();
+  const int tok = blockIdx.x;  // b*L + l
+  const int b = tok / L, l = tok - b * L;
+  const int lane = threadIdx.x & 31;
+  const int H = Hq + 2 * Hkv;
+  const int head = blockIdx.y * 8 + (threadIdx.x >> 5);
+  if (head >= H) return;
+  const int i0 = 2 * lane;
+  const int pos_i = lengths[b] + l;
+  TIN* row = qkv + (int64_t)tok * H * D;
+  {
+    TIN* src = row + (int64_t)head * D;
+    float x1[2], x2[2];
+    if constexpr (std::is_same<TIN, float>::value) {
+      const float2 a = *reinterpret_cast<const float2*>(src + i0), c = *reinterpret_cast<const float2*>(src + HALF + i0);
+      x1[0] = a.x; x1[1] = a.y; x2[0] = c.x; x2[1] = c.y;
+      if constexpr (ACC_IN) {    // the projection's fp32 accumulator: round as its 16-bit output would be, re-zero behind the read
+#pragma unroll
+        for (int j = 0; j < 2; ++j) { x1[j] = Tr<T>::to_f(Tr<T>::from_f(x1[j])); x2[j] = Tr<T>::to_f(Tr<T>::from_f(x2[j])); }
+        *reinterpret_cast<float2*>(src + i0) = make_float2(0.f, 0.f);
+        *reinterpret_cast<float2*>(src + HALF + i0) = make_float2(0.f, 0.f);
+      }
+    } else {
+      x1[0] = Tr<TIN>::to_f(src[i0]); x1[1] = Tr<TIN>::to_f(src[i0 + 1]);
+      x2[0] = Tr<TIN>::to_f(src[HALF + i0]); x2[1] = Tr<TIN>::to_f(src[HALF + i0 + 1]);
+    }
+    T* dst;
+    float o1[2], o2[2];
+    if (head >= Hq + Hkv) {      // V head: plain append
+      if (pos_i >= Tcap) return;
+      dst = vc + (((int64_t)b * Hkv + (head - Hq - Hkv)) * Tcap + pos_i) * D;
+      o1[0] = x1[0]; o1[1] = x1[1]; o2[0] = x2[0]; o2[1] = x2[1];
+    } else {
+      const bool is_q = head < Hq;
+      const T* nw = is_q ? qn_w : kn_w;
+      if (nw != nullptr) {       // mx.fast.rms_norm over head_dim (qwen3.py:65-70), rounded to the storage type
+        const float ss = warp_sum(x1[0] * x1[0] + x1[1] * x1[1] + x2[0] * x2[0] + x2[1] * x2[1]);
+        const float inv = 1.0f / sqrtf(ss / (float)D + eps);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          x1[j] = Tr<T>::to_f(Tr<T>::from_f(x1[j] * inv * Tr<T>::to_f(nw[i0 + j])));
+          x2[j] = Tr<T>::to_f(Tr<T>::from_f(x2[j] * inv * Tr<T>::to_f(nw[HALF + i0 + j])));
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {  // theta = pos * scale * base^(-i/half)
+        const float inv_freq = exp2f(-(float)(i0 + j) * (log2_base / (float)HALF));
+        float sn, cs;
+        sincosf((float)pos_i * rope_scale * inv_freq, &sn, &cs);
+        o1[j] = x1[j] * cs - x2[j] * sn;
+        o2[j] = x1[j] * sn + x2[j] * cs;
+      }
+      if (is_q) {
+        dst = q_out + ((int64_t)tok * Hq + head) * D;
+      } else {
+        if (pos_i >= Tcap) return;
+        dst = kc + (((int64_t)b * Hkv + (head - Hq)) * Tcap + pos_i) * D;
+      }
+    }
+    if constexpr (sizeof(T) == 2) {     // one 32-bit store per pair: 128 contiguous bytes per warp
+      __align__(4) T p1[2] = {Tr<T>::from_f(o1[0]), Tr<T>::from_f(o1[1])};
+      __align__(4) T p2[2] = {Tr<T>::from_f(o2[0]), Tr<T>::from_f(o2[1])};
+      *reinterpret_cast<uint32_t*>(dst + i0) = *reinterpret_cast<const uint32_t*>(p1);
+      *reinterpret_cast<uint32_t*>(dst + HALF + i0) = *reinterpret_cast<const uint32_t*>(p2);
+    } else {
+      dst[i0] = Tr<T>::from_f(o1[0]);
+      dst[i0 + 1] = Tr<T>::from_f(o1[1]);
+      dst[HALF + i0] = Tr<T>::from_f(o2[0]);
+      dst[HALF + i0 + 1] = Tr<T>::from_f(o2[1]);
+    }
+  }
+}
+
 // act[m, i] = silu(gu[m, i]) * gu[m, I + i] from the fp32 accumulation buffer of the fused gate|up projection
 // (models/llama.py:165); the buffer is re-zeroed behind the read.  One thread per aligned group of 8 outputs.
 template <typename T>
@@ -368,6 +454,20 @@ extern "C" int b200p_rope_kv_append(void* qkv, void* q_out, void* kcache, void* 
   B200P_REQUIRE(Hq > 0 && Hkv > 0 && Hq % Hkv == 0, B200P_ERR_ARG, "bad head counts %d/%d", Hq, Hkv);
   B200P_REQUIRE(B * L < (1ll << 31) && Hq + 2 * Hkv < 65536, B200P_ERR_ARG, "grid too large");
   if (B * L == 0) return B200P_OK;
+  if (D == 128) {
+    const dim3 g128((unsigned)(B * L), (unsigned)((Hq + 2 * Hkv + 7) / 8)), b128(256);
+    if (qkv_f32) {
+      B200P_DISPATCH_DTYPE(dtype, T, (launch_pdl(rope_kv_append_d128_kernel<T, float>, g128, b128, 0, (cudaStream_t)stream,
+                                         (float*)qkv, (T*)q_out, (T*)kcache, (T*)vcache, lengths, (const T*)q_norm_w,
+                                         (const T*)k_norm_w, (int)L, Hq, Hkv, Tcap, log2f(rope_base), rope_scale, norm_eps)));
+    } else {
+      B200P_DISPATCH_DTYPE(dtype, T, (launch_pdl(rope_kv_append_d128_kernel<T, T>, g128, b128, 0, (cudaStream_t)stream,
+                                         (T*)qkv, (T*)q_out, (T*)kcache, (T*)vcache, lengths, (const T*)q_norm_w,
+                                         (const T*)k_norm_w, (int)L, Hq, Hkv, Tcap, log2f(rope_base), rope_scale, norm_eps)));
+    }
+    B200P_LAUNCH_CHECK("rope_kv_append_d128_kernel");
+    return B200P_OK;
+  }
   dim3 grid((unsigned)(B * L), (unsigned)(Hq + 2 * Hkv)), block(((D / 2 + 31) / 32) * 32);
   if (qkv_f32) {
     B200P_DISPATCH_DTYPE(dtype, T, (launch_pdl(rope_kv_append_kernel<T, float>, grid, block, 0, (cudaStream_t)stream, 
