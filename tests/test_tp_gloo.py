@@ -87,6 +87,7 @@ def _rank_main(rank, world, port, name, overrides, ret):
     ("tiny-llama", 2, {}),
     ("tiny-qwen3", 2, {}),
     ("tiny-qwen3", 4, {"num_key_value_heads": 4}),
+    ("small-phi3", 2, {}),                      # Phi-3: sharded after its fused qkv / gate_up matrices are split
 ])
 def test_tp_decomposition_matches_single_rank(name, world, overrides):
     import torch.multiprocessing as mp
