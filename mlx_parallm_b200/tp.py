@@ -172,10 +172,12 @@ class PeerExchange:
         # "rows": two-shot, row-sharded residual stream, normalised rows pushed to every rank's x (1/W of the traffic);
         # "oneshot": every rank pulls all W partials and keeps the whole residual stream
         # measured (profiles/r1_run10_*): TP=2 one-shot 9.2 us vs rows 13.8 us at M=64; TP=8 23.7 us both at M=64 but
-        # rows 175 us vs one-shot 383 us at M=2048 and 2.93 vs 3.05 ms per decode step -> rows from TP=4 up
+        # rows 175 us vs one-shot 383 us at M=2048 and 2.93 vs 3.05 ms per decode step.  TP=4 (profiles/r1_run40_*): the
+        # B=64 decode step is faster one-shot (Qwen3-14B 3.69 vs 4.33 ms, Llama-3-8B at 8k context 5.33 vs 5.57 ms)
+        # -> rows from TP=8 up
         self.mode = mode or os.environ.get("B200P_TP_EXCHANGE", "auto")
         if self.mode == "auto":
-            self.mode = "rows" if world >= 4 else "oneshot"
+            self.mode = "rows" if world >= 8 else "oneshot"
         assert self.mode in ("rows", "oneshot"), self.mode
         import ctypes as C
         from ._lib import check, lib
