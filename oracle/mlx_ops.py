@@ -44,11 +44,28 @@ def bf16_from_bits(b: np.ndarray) -> np.ndarray:
     return (b.astype(np.uint32) << 16).view(np.float32)
 
 
+def e4m3_round(x: np.ndarray) -> np.ndarray:
+    """float32 -> nearest OCP FP8 E4M3 value (round-half-even, 3 mantissa bits, normals 2^-6 .. 448, subnormals in steps
+    of 2^-9, saturating), returned as float32.  Not a reference format: the reference stores K/V in float32 (base.py:111-112);
+    this exists to QUANTIFY what an fp8 KV cache would cost against the 1e-2 logits budget."""
+    x = np.asarray(x, dtype=np.float32)
+    a = np.abs(x).astype(np.float64)
+    with np.errstate(divide="ignore"):
+        e = np.floor(np.log2(np.where(a > 0, a, 1.0)))
+    e = np.clip(e, -6, 8)
+    step = np.exp2(e - 3)                                 # spacing of the 3-bit mantissa at this exponent
+    q = np.rint(a / step) * step                          # rint = half-to-even
+    q = np.minimum(q, 448.0)
+    return (np.sign(x) * q).astype(np.float32)
+
+
 def round_to(x: np.ndarray, dtype: str) -> np.ndarray:
     """Round float32 values to ``dtype`` storage precision; result stays float32."""
     x = np.asarray(x, dtype=np.float32)
     if dtype == "float32":
         return x
+    if dtype == "float8_e4m3":
+        return e4m3_round(x)
     if dtype == "float16":
         with np.errstate(over="ignore"):
             return x.astype(np.float16).astype(np.float32)

@@ -228,3 +228,15 @@ def test_generate_step_greedy_is_deterministic_and_advances_cache():
     g2 = generate_step(p, om)
     toks2 = [next(g2)[0] for _ in range(4)]
     assert all(np.array_equal(a, b) for a, b in zip(toks, toks2))
+
+
+def test_e4m3_rounding_known_answers():
+    """oracle.mlx_ops.e4m3_round (used only by scripts/fp8_kv_error_study.py): OCP E4M3 grid, half-to-even, saturation,
+    subnormal step 2^-9."""
+    from oracle.mlx_ops import e4m3_round, round_to
+    x = np.array([0, 1, 1.0625, 1.125, 1.1875, 448, 500, -0.3, 2.0 ** -9, 2.0 ** -10, 0.0019, 17, 19, 20.1, -1e9], np.float32)
+    e = np.array([0, 1, 1.0, 1.125, 1.25, 448, 448, -0.3125, 2.0 ** -9, 0, 2.0 ** -9, 16, 20, 20, -448], np.float32)
+    assert np.array_equal(e4m3_round(x), e)
+    grid = e4m3_round(np.linspace(-450, 450, 200001).astype(np.float32))
+    assert len(np.unique(np.abs(grid))) <= 127 and np.array_equal(e4m3_round(grid), grid)      # idempotent, <= 2^7 - 1 magnitudes
+    assert np.array_equal(round_to(x, "float8_e4m3"), e)
