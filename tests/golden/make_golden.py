@@ -39,6 +39,7 @@ def main():
     np.savez_compressed(os.path.join(OUT, "tiny_llama_f16_greedy.npz"), **transcript("tiny-llama", "float16", 4, 12, 32))
     np.savez_compressed(os.path.join(OUT, "tiny_qwen3_bf16_greedy.npz"), **transcript("tiny-qwen3", "bfloat16", 4, 12, 32))
     np.savez_compressed(os.path.join(OUT, "small_llama_f16_greedy.npz"), **transcript("small-llama", "float16", 4, 20, 32))
+    np.savez_compressed(os.path.join(OUT, "small_phi3_f16_greedy.npz"), **transcript("small-phi3", "float16", 4, 20, 32))
     # 2. dequantize bit patterns: every code x random scales, 3 dtypes x 2 widths x 3 modes
     rng = np.random.default_rng(99)
     dq = {}

@@ -11,7 +11,8 @@ from helpers import make_pair
 
 CASES = [("tiny_llama_f16_greedy", "tiny-llama", "float16"),
          ("tiny_qwen3_bf16_greedy", "tiny-qwen3", "bfloat16"),
-         ("small_llama_f16_greedy", "small-llama", "float16")]
+         ("small_llama_f16_greedy", "small-llama", "float16"),
+         ("small_phi3_f16_greedy", "small-phi3", "float16")]
 
 
 @pytest.mark.parametrize("fixture,name,dtype", CASES)
