@@ -58,6 +58,11 @@ enum {
 #define B200P_X_PERM8   0x100   /* x of b200p_qmm is PERM8 (4-bit weights only)                          */
 #define B200P_Y_PERM8   0x200   /* 16-bit y of b200p_qmm (STORE, SILU_MUL) is written PERM8              */
 #define B200P_OUT_PERM8 0x1     /* flags of b200p_rmsnorm / b200p_attn: write the 16-bit output PERM8 */
+/* Caller's promise about the weights of a b200p_qmm call, OR-ed into `epilogue` like the layout flags: every scale of the
+ * matrix satisfies |s| < 0.0625 (checked once at load time by the host: mlx_parallm_b200/models/_transformer.py).  F16
+ * calls then dequantise with ONE half2 FMA per code pair on subnormal operands (csrc/dequant.cuh) -- same rounding of
+ * q*s+b, two thirds of the instructions.  Ignored for BF16 / F32. */
+#define B200P_W_SMALLSCALE 0x400
 
 const char* b200p_version(void);
 const char* b200p_last_error(void);

@@ -16,6 +16,7 @@ F32, F16, BF16 = 0, 1, 2
 DQ_F32_MULADD, DQ_FMA, DQ_T_MULADD = 0, 1, 2
 EPI_STORE, EPI_STORE_F32, EPI_ADD_RESIDUAL, EPI_SILU_MUL = 0, 1, 2, 3
 X_PERM8, Y_PERM8, OUT_PERM8 = 0x100, 0x200, 0x1      # activation-layout flags (include/b200p.h)
+W_SMALLSCALE = 0x400                                 # every |scale| < 0.0625: subnormal-operand dequant (f16 only)
 
 _vp, _i64, _i32, _f32, _u64, _sz = C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_uint64, C.c_size_t
 

@@ -138,7 +138,7 @@ extern "C" int b200p_qmm(const void* x, const uint32_t* w, const void* scales, c
                          int64_t M, int64_t N, int64_t K, int64_t ldx, int64_t ldy, int group_size, int bits,
                          int dtype, int epilogue_flags, void* workspace, size_t workspace_bytes, void* stream) {
   const int epilogue = epilogue_flags & 0xff, flags = epilogue_flags & ~0xff;
-  B200P_REQUIRE((flags & ~(B200P_X_PERM8 | B200P_Y_PERM8)) == 0, B200P_ERR_ARG, "unknown layout flags 0x%x", flags);
+  B200P_REQUIRE((flags & ~(B200P_X_PERM8 | B200P_Y_PERM8 | B200P_W_SMALLSCALE)) == 0, B200P_ERR_ARG, "unknown layout flags 0x%x", flags);
   B200P_REQUIRE(!(flags & B200P_X_PERM8) || (bits == 4 && dtype != B200P_F32), B200P_ERR_ARG,
                 "B200P_X_PERM8 is the layout of 16-bit activations for 4-bit weights");
   B200P_REQUIRE(!(flags & B200P_Y_PERM8) || ((epilogue == B200P_EPI_STORE || epilogue == B200P_EPI_SILU_MUL) && dtype != B200P_F32),

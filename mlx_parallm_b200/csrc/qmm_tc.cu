@@ -14,14 +14,19 @@
 // Scheduling is persistent "stream-K": the work of a launch is the linear sequence of units
 // (output tile, K stage of 128 packed bytes per row = 256 k at 4 bits); CTA c of G takes the contiguous range
 // [c*U/G, (c+1)*U/G), so every SM streams the same number of weight bytes whatever N, K are.  A tile whose K
-// range is shared by several CTAs is summed with fp32 L2 atomics (red.global.add): straight into y for
-// ADD_RESIDUAL, else into a per-boundary fp32 accumulator that the last-arriving CTA reads, applies the epilogue
-// to and re-zeroes.  Split tiles are therefore summed in arrival order (last-bit run-to-run differences).
+// range is shared by several CTAs is finished in two steps, with plain stores and loads only (one SM retires
+// fp32 reds at ~1.3 cycles per lane: a 64 KB partial tile summed with atomics cost ~10 us, more than the main loop):
+//   1. every contributor writes its fp32 partial tile to its own slot of the workspace (coalesced st.global.cg);
+//   2. at the end of the kernel the contributors of a tile meet on an arrival counter (all CTAs of the grid are
+//      co-resident: grid <= #SMs, one CTA per SM) and SHARE the reduction: contributor j sums token groups
+//      j, j+S, ... of all S slots in CTA order and applies the fused epilogue to them.
+// Sums are therefore taken in a fixed order: results are bit-reproducible run to run.
 //
 // warp roles (736 threads):
 //   warps 0..15  dequantisers: 4 groups of 4 warps, group g handles weight block g&1 on k-blocks of parity g>>1;
 //                a thread owns one weight row: LDS packed codes -> 16-bit q*s+b -> tcgen05.st into the A ring;
-//   warps 16..19 epilogue: TMEM -> registers -> global (lanes along n: coalesced), stream-K fix-up;
+//   warps 16..19 epilogue: TMEM -> registers -> global (thread = output column n: every warp store is one coalesced
+//                line per token), stream-K partial tiles and their final reduction;
 //   warp 20      TMA producer of weights and scale/bias tiles (independent of the previous kernel: starts at once);
 //   warp 21      TMA producer of X tiles (after griddepcontrol.wait);
 //   warp 22      TMEM owner + MMA issuer (elect.sync, operands in uniform registers).
@@ -218,16 +223,20 @@ constexpr int SB_TILE_BYTES = 128 * 16;          // 128 rows x 8 k-blocks x 2 by
 constexpr int SB_SLOT_BYTES = 4 * SB_TILE_BYTES; // block 0 scales, block 0 biases, block 1 scales, block 1 biases
 constexpr int MAX_STAGES = 8;                    // weight ring stages / X ring slots (upper bounds)
 constexpr int X_RING_BYTES = 64 * 1024;
-constexpr int EPI_TOK = 16;                      // tokens per epilogue staging tile
-constexpr int EPI_NBUF = 2;
-constexpr int EPI_BUF_BYTES = EPI_TOK * 128 * 4; // [16 tokens x 128 rows] fp32 (16-bit tiles use the first half)
+constexpr int EPI_TOK = 8;                       // tokens per epilogue step = work item of the shared split-tile reduction
+// Profiling build only (-DB200P_TC_DEBUG=mask): 1 no X loads, 2 no MMA issue, 4 no epilogue, 8 no A stores, 32 no
+// scale/bias loads.  The shipped kernel is compiled with 0: every branch below folds away.
+#ifndef B200P_TC_DEBUG
+#define B200P_TC_DEBUG 0
+#endif
+constexpr int kDebug = B200P_TC_DEBUG;
 
 struct TcParams {
   const void* scales;
   const void* biases;
   void* y;
-  float* ws_acc;       // one fp32 [2*TN x 128] accumulator per CTA boundary (zero on entry, left zero)
-  int* ws_counter;     // one arrival counter per output tile (zero on entry, left zero)
+  float* ws_part;      // stream-K partial tiles: [grid][2 slots][2 blocks][TN tokens][128 rows] fp32 (no initial state)
+  int* ws_counter;     // {arrived, done} per output tile (zero on entry, left zero)
   int M_tok, N, K, TN;
   int64_t ldy;
   int epi;
@@ -235,21 +244,21 @@ struct TcParams {
   int num_kb;          // K / 64
   int num_st;          // stages along K = ceil(num_kb / KPS)
   int pairs, tiles_m;  // output tile t = pair * tiles_m + token tile
-  long long U;         // total units = pairs * tiles_m * num_st
+  int U;               // total units = pairs * tiles_m * num_st (the host checks U * (grid + 1) < 2^31: 32-bit unit arithmetic)
   int sb_tma;          // 1: scale/bias tiles come through TMA (num_kb % 8 == 0)
   int w_stages;        // weight ring depth
   int x_slots;         // X ring depth (4 or 8; one slot = the [TN x 64] tile of one k-block)
-  int debug;           // B200P_TC_DEBUG (profiling only): 1 no X loads, 2 no MMA issue, 4 no epilogue, 8 no A stores, 16 no TMA stores
 };
 
 // CTA that owns linear unit x when U units are dealt to G CTAs as [c*U/G, (c+1)*U/G)
-__device__ __forceinline__ int owner_of(long long x, long long U, int G) { return (int)(((x + 1) * G - 1) / U); }
+__device__ __forceinline__ int owner_of(int x, int U, int G) { return ((x + 1) * G - 1) / U; }
 
-template <typename T, int BITS, bool XPERM>
+// FAST: the small-scale dequant of dequant.cuh (f16, caller promised B200P_W_SMALLSCALE): A and D are produced at 1/16.
+template <typename T, int BITS, bool XPERM, bool FAST>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x,
-              const __grid_constant__ CUtensorMap tm_s, const __grid_constant__ CUtensorMap tm_b,
-              const __grid_constant__ CUtensorMap tm_y, const __grid_constant__ CUtensorMap tm_acc, const TcParams p) {
+              const __grid_constant__ CUtensorMap tm_s, const __grid_constant__ CUtensorMap tm_b, const TcParams p) {
+  static_assert(!FAST || std::is_same<T, __half>::value, "the subnormal-operand dequant is an f16 trick");
   constexpr int PKB = 64 * BITS / 8;            // packed bytes per row per k-block
   constexpr int KPS = 128 / PKB;                // k-blocks per stage (a stage row is one 128-byte line)
   constexpr int SPG = 8 / KPS;                  // stages per scale/bias group of 8 k-blocks
@@ -262,8 +271,7 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
   const uint32_t x_mask = (uint32_t)(p.x_slots - 1);
   const int x_shift = p.x_slots == 8 ? 3 : 2;
   const uint32_t sb_ring = x_ring + p.x_slots * x_slot_bytes;
-  const uint32_t epi_ring = sb_ring + NSB * SB_SLOT_BYTES;
-  const uint32_t bar_base = epi_ring + EPI_NBUF * EPI_BUF_BYTES;
+  const uint32_t bar_base = sb_ring + NSB * SB_SLOT_BYTES;
   const int NBUF = TN > 64 ? 1 : 2;              // D buffers: buffer d, block b at columns d*128 + b*64 (TN <= 64) / b*128
   auto full_w = [&](int s) { return bar_base + 8u * s; };
   auto empty_w = [&](int s) { return bar_base + 8u * (MAX_STAGES + s); };
@@ -276,12 +284,11 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
   auto accum_full = [&](int d) { return bar_base + 8u * (4 * MAX_STAGES + 2 * NSLOT + 2 * NSB + d); };
   auto accum_empty = [&](int d) { return bar_base + 8u * (4 * MAX_STAGES + 2 * NSLOT + 2 * NSB + 2 + d); };
   const uint32_t tmem_slot = bar_base + 8u * (4 * MAX_STAGES + 2 * NSLOT + 2 * NSB + 4);
-  const uint32_t flag_slot = tmem_slot + 4u;
   auto d_col = [&](int d, int b) { return (uint32_t)(TN > 64 ? b * 128 : d * 128 + b * 64); };
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int G = (int)gridDim.x, cta = (int)blockIdx.x;
-  const long long u_begin = (p.U * cta) / G, u_end = (p.U * (cta + 1)) / G;
+  const int u_begin = (int)(((long long)p.U * cta) / G), u_end = (int)(((long long)p.U * (cta + 1)) / G);
   const bool silu = p.epi == B200P_EPI_SILU_MUL;
 
   if (threadIdx.x == 0) {
@@ -294,8 +301,6 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     tma_prefetch_desc(&tm_w);
     tma_prefetch_desc(&tm_x);
     if (p.sb_tma) { tma_prefetch_desc(&tm_s); tma_prefetch_desc(&tm_b); }
-    tma_prefetch_desc(&tm_y);
-    tma_prefetch_desc(&tm_acc);
   }
   if (warp == WARP_MMA) tmem_alloc(tmem_slot, TMEM_COLS);
   tc_fence_before();
@@ -310,8 +315,8 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     // Weights and scale/bias tiles do not depend on the previous kernel: no griddepcontrol.wait here, so under
     // programmatic dependent launch the HBM stream of this kernel starts while the previous kernel drains.
     int si = 0, ph = 0, sbi = 0, sbph = 0;
-    for (long long u = u_begin; u < u_end; ++u) {
-      const int tile = (int)(u / p.num_st), st = (int)(u % p.num_st);
+    for (int u = u_begin; u < u_end; ++u) {
+      const int tile = u / p.num_st, st = u % p.num_st;
       const int pair = tile / p.tiles_m;
       const int rowA0 = silu ? pair * 128 : pair * 256;
       const int rowB0 = silu ? p.N / 2 + pair * 128 : pair * 256 + 128;
@@ -320,7 +325,7 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
         if (elect_one()) {
           const uint32_t sdst = sb_ring + sbi * SB_SLOT_BYTES;
           const int kb0 = (st / SPG) * 8;
-          if (p.debug & 32) {
+          if (kDebug & 32) {
             mbar_arrive(sb_full(sbi));
           } else {
             mbar_arrive_expect_tx(sb_full(sbi), (uint32_t)SB_SLOT_BYTES);
@@ -347,15 +352,15 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     // ===================================== activation producer ==============================
     pdl_wait();                                      // X is the previous kernel's output
     uint32_t it = 0;
-    for (long long u = u_begin; u < u_end; ++u) {
-      const int tile = (int)(u / p.num_st), st = (int)(u % p.num_st);
+    for (int u = u_begin; u < u_end; ++u) {
+      const int tile = u / p.num_st, st = u % p.num_st;
       const int tm = tile % p.tiles_m;
 #pragma unroll
       for (int jj = 0; jj < KPS; ++jj, ++it) {
         const uint32_t xs = it & x_mask;
         mbar_wait(empty_x(xs), ((it >> x_shift) & 1u) ^ 1u);
         if (elect_one()) {
-          if (p.debug & 1) {
+          if (kDebug & 1) {
             mbar_arrive(full_x(xs));
           } else {
             mbar_arrive_expect_tx(full_x(xs), x_slot_bytes);
@@ -373,9 +378,9 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(TN >> 3) << 17) | ((128u >> 4) << 24);
     int seg = 0;
     uint32_t it = 0;
-    for (long long u = u_begin; u < u_end; ++seg) {
-      const int s0 = (int)(u % p.num_st);
-      const int ns = (int)min((long long)(p.num_st - s0), u_end - u);
+    for (int u = u_begin; u < u_end; ++seg) {
+      const int s0 = u % p.num_st;
+      const int ns = min(p.num_st - s0, u_end - u);
       const int buf = NBUF == 2 ? (seg & 1) : 0;
       if (seg >= NBUF) {                               // the epilogue of the segment that last used this D buffer has drained it
         mbar_wait(accum_empty(buf), (uint32_t)(((seg / NBUF) - 1) & 1));
@@ -390,7 +395,7 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
         tc_fence_after();
         if (elect_one()) {
           const uint32_t xsm = x_ring + xs * x_slot_bytes;
-          if (!(p.debug & 2))
+          if (!(kDebug & 2))
 #pragma unroll
           for (int blk = 0; blk < 2; ++blk) {
 #pragma unroll
@@ -445,12 +450,18 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     auto kblock = [&](int j2, uint32_t s2, uint32_t b2) {
       uint32_t o[32];
       const uint32_t* pw = reinterpret_cast<const uint32_t*>(pk + j2 * CPK);
+      if constexpr (FAST) {
+        const SmallScale sc = small_scale_prep(s2, b2);
 #pragma unroll
-      for (int c = 0; c < 8; ++c) dequant8<T, BITS, XPERM>(pw + c * (BITS / 4), s2, b2, o + 4 * c);
+        for (int c = 0; c < 8; ++c) dequant8_small<BITS, XPERM>(pw + c * (BITS / 4), sc, o + 4 * c);
+      } else {
+#pragma unroll
+        for (int c = 0; c < 8; ++c) dequant8<T, BITS, XPERM>(pw + c * (BITS / 4), s2, b2, o + 4 * c);
+      }
       const uint32_t slot = it & (NSLOT - 1);
       mbar_wait(empty_a(slot), ((it >> 2) & 1u) ^ 1u);
       tc_fence_after();
-      if (!(p.debug & 8)) {
+      if (!(kDebug & 8)) {
         tmem_st32(a_dst + slot * 64, o);
         tmem_st_wait();
       }
@@ -460,9 +471,9 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
       it += 2;
     };
 
-    for (long long u = u_begin; u < u_end;) {
-      const int tile = (int)(u / p.num_st), s0 = (int)(u % p.num_st);
-      const int ns = (int)min((long long)(p.num_st - s0), u_end - u);
+    for (int u = u_begin; u < u_end;) {
+      const int tile = u / p.num_st, s0 = u % p.num_st;
+      const int ns = min(p.num_st - s0, u_end - u);
       if (p.sb_tma) {
         for (int st = s0; st < s0 + ns; ++st) {
           if (st == s0 || (st % SPG) == 0) {             // next group of 8 k-blocks: scales / biases of this row
@@ -516,145 +527,184 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     }
   } else {
     // ===================================== epilogue warps ===================================
-    // TMEM -> registers -> a [16 tokens x 128 rows] staging tile in shared memory (the transpose is free: thread = row
-    // writes column r of every token line, bank = lane) -> ONE TMA tensor store / reduce-add per tile.  Stream-K
-    // partial tiles are summed by the TMA unit (cp.reduce.async.bulk .add.f32) instead of 16K scalar atomics per
-    // segment, which kept the LSU busy for ~10 us.
+    // Thread = one output column n (weight row r of block A and of block B), EPI_TOK tokens per step: every warp-level
+    // load / store below touches one contiguous line per token (32 lanes x 4 B, or x 2 B for 16-bit outputs -- whole
+    // sectors either way), so nothing is staged through shared memory and no store is atomic.
     const int e = warp - DQ_WARPS;                     // == warp % 4: the TMEM lane quarter this warp may read
     const int r = e * 32 + lane;                     // output row (weight row) within the 128-row block
     const uint32_t lane_base = tmem_base + ((uint32_t)(e * 32) << 16);
     const int et = threadIdx.x - DQ_THREADS;         // 0..127
-    const bool out16 = p.epi == B200P_EPI_STORE || p.epi == B200P_EPI_SILU_MUL;
-    const int rp = p.y_perm ? perm8_pos(r) : r;      // column inside a 16-bit staging line
-    pdl_wait();                                      // y (residual) belongs to the previous kernels
-    int seg = 0;
-    uint32_t nchunk = 0;
-    // claim staging buffer (nchunk & 1): the bulk group that last read it must be done with shared memory
-    auto stage_begin = [&]() -> uint32_t {
-      if (et == 0) bulk_wait_read<EPI_NBUF - 1>();
-      named_bar_sync(1, EPI_THREADS);
-      return epi_ring + (nchunk & (EPI_NBUF - 1)) * EPI_BUF_BYTES;
-    };
-    // the tile is written: hand it to the TMA unit
-    auto stage_end = [&](uint32_t buf, const CUtensorMap* tm, int cx, int cy, bool reduce) {
-      fence_proxy_async_smem();
-      named_bar_sync(2, EPI_THREADS);
-      if (et == 0 && !(p.debug & 16)) {
-        if (reduce) tma_reduce_add_2d(tm, cx, cy, buf);
-        else tma_store_2d(tm, cx, cy, buf);
-        bulk_commit();
+    constexpr float DSCALE = FAST ? 16.f : 1.f;      // FAST: A (hence D) was produced at 1/16
+    const int64_t slot_elems = (int64_t)2 * TN * 128;   // one partial tile: [2 blocks][TN tokens][128 rows] fp32
+
+    // fused epilogue of EPI_TOK tokens of this thread's two output columns (a: block A, b: block B)
+    auto emit = [&](const float (&a)[EPI_TOK], const float (&b)[EPI_TOK], int rowA0, int rowB0, int tokb) {
+      const int n0 = rowA0 + r, n1 = rowB0 + r;
+      if (p.epi == B200P_EPI_ADD_RESIDUAL) {
+        // every element of y is owned by exactly one thread of the launch: plain read-modify-write
+        float* y = reinterpret_cast<float*>(p.y);
+        const bool ok0 = n0 < p.N, ok1 = n1 < p.N;
+        float ha[EPI_TOK], hb[EPI_TOK];
+#pragma unroll
+        for (int j = 0; j < EPI_TOK; ++j) {
+          const bool okt = tokb + j < p.M_tok;
+          const float* yr = y + (int64_t)(tokb + j) * p.ldy;
+          ha[j] = (ok0 && okt) ? __ldcg(yr + n0) : 0.f;
+          hb[j] = (ok1 && okt) ? __ldcg(yr + n1) : 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < EPI_TOK; ++j) {
+          const bool okt = tokb + j < p.M_tok;
+          float* yr = y + (int64_t)(tokb + j) * p.ldy;
+          if (ok0 && okt) __stcg(yr + n0, ha[j] + a[j]);
+          if (ok1 && okt) __stcg(yr + n1, hb[j] + b[j]);
+        }
+      } else if (p.epi == B200P_EPI_STORE_F32) {
+        float* y = reinterpret_cast<float*>(p.y);
+#pragma unroll
+        for (int j = 0; j < EPI_TOK; ++j) {
+          if (tokb + j < p.M_tok) {
+            float* yr = y + (int64_t)(tokb + j) * p.ldy;
+            if (n0 < p.N) __stcg(yr + n0, a[j]);
+            if (n1 < p.N) __stcg(yr + n1, b[j]);
+          }
+        }
+      } else if (p.epi == B200P_EPI_STORE) {
+        T* y = reinterpret_cast<T*>(p.y);
+        const int c0 = p.y_perm ? perm8_pos(n0) : n0, c1 = p.y_perm ? perm8_pos(n1) : n1;
+#pragma unroll
+        for (int j = 0; j < EPI_TOK; ++j) {
+          if (tokb + j < p.M_tok) {
+            T* yr = y + (int64_t)(tokb + j) * p.ldy;
+            if (n0 < p.N) yr[c0] = Tr<T>::from_f(a[j]);
+            if (n1 < p.N) yr[c1] = Tr<T>::from_f(b[j]);
+          }
+        }
+      } else {                                         // SILU_MUL: block A = gate rows, block B = the matching up rows
+        T* y = reinterpret_cast<T*>(p.y);
+        const int c0 = p.y_perm ? perm8_pos(n0) : n0;
+        if (n0 < p.N / 2) {
+#pragma unroll
+          for (int j = 0; j < EPI_TOK; ++j)
+            if (tokb + j < p.M_tok) y[(int64_t)(tokb + j) * p.ldy + c0] = Tr<T>::from_f(silu_tc(a[j]) * b[j]);
+        }
       }
-      ++nchunk;
     };
-    for (long long u = u_begin; u < u_end; ++seg) {
-      const int tile = (int)(u / p.num_st), s0 = (int)(u % p.num_st);
-      const int ns = (int)min((long long)(p.num_st - s0), u_end - u);
+
+    pdl_wait();                                      // y and the workspace belong to the previous kernels until here
+    int seg = 0;
+    int def0 = -1, def1 = -1;                        // split tiles this CTA contributed to (its first / its last segment)
+    for (int u = u_begin; u < u_end; ++seg) {
+      const int tile = u / p.num_st, s0 = u % p.num_st;
+      const int ns = min(p.num_st - s0, u_end - u);
       const int pair = tile / p.tiles_m, tm = tile % p.tiles_m;
       const int rowA0 = silu ? pair * 128 : pair * 256;
       const int rowB0 = silu ? p.N / 2 + pair * 128 : pair * 256 + 128;
       const int tok0 = tm * TN;
       const int buf = NBUF == 2 ? (seg & 1) : 0;
       const bool full = (s0 == 0 && ns == p.num_st);
-      // a tile shared by several CTAs is summed in L2: straight into y for ADD_RESIDUAL, else into the fp32
-      // accumulator owned by the tile's first CTA; the last CTA to arrive applies the epilogue and re-zeroes it
-      const bool via_acc = !full && p.epi != B200P_EPI_ADD_RESIDUAL;
-      const int c_first = via_acc ? owner_of((long long)tile * p.num_st, p.U, G) : cta;
-      const int acc_row0 = c_first * 2 * TN;           // first line of this boundary's accumulator in tm_acc
 
       mbar_wait(accum_full(buf), (uint32_t)((seg / NBUF) & 1));
       tc_fence_after();
       const uint32_t dA = lane_base + d_col(buf, 0), dB = lane_base + d_col(buf, 1);
-      for (int t0 = 0; t0 < TN && !(p.debug & 4); t0 += EPI_TOK) {
-        if (via_acc || !out16) {
-          // fp32 tiles, one per block: reduce-add (split tile / residual) or plain store (whole STORE_F32 tile)
-#pragma unroll
-          for (int blk = 0; blk < 2; ++blk) {
-            float v[EPI_TOK];
-            tmem_ld16((blk ? dB : dA) + (uint32_t)t0, v);
+      if (!(kDebug & 4)) {
+        if (full) {
+          for (int t0 = 0; t0 < TN; t0 += EPI_TOK) {
+            float a[EPI_TOK], b[EPI_TOK];
+            tmem_ld8(dA + (uint32_t)t0, a);
+            tmem_ld8(dB + (uint32_t)t0, b);
             tmem_ld_wait();
-            const uint32_t sb = stage_begin();
+            if constexpr (FAST) {
 #pragma unroll
-            for (int j = 0; j < EPI_TOK; ++j) sts32(sb + (uint32_t)(j * 128 + r) * 4u, __float_as_uint(v[j]));
-            if (via_acc) stage_end(sb, &tm_acc, 0, acc_row0 + blk * TN + t0, true);
-            else stage_end(sb, &tm_y, blk ? rowB0 : rowA0, tok0 + t0, p.epi == B200P_EPI_ADD_RESIDUAL);
+              for (int j = 0; j < EPI_TOK; ++j) { a[j] *= DSCALE; b[j] *= DSCALE; }
+            }
+            emit(a, b, rowA0, rowB0, tok0 + t0);
           }
-        } else if (silu) {
-          float g[EPI_TOK], uu[EPI_TOK];
-          tmem_ld16(dA + (uint32_t)t0, g);
-          tmem_ld16(dB + (uint32_t)t0, uu);
-          tmem_ld_wait();
-          const uint32_t sb = stage_begin();
-#pragma unroll
-          for (int j = 0; j < EPI_TOK; ++j) sts16(sb + (uint32_t)(j * 128 + rp) * 2u, Tr<T>::from_f(silu_tc(g[j]) * uu[j]));
-          stage_end(sb, &tm_y, rowA0, tok0 + t0, false);
         } else {
-#pragma unroll
-          for (int blk = 0; blk < 2; ++blk) {
-            float v[EPI_TOK];
-            tmem_ld16((blk ? dB : dA) + (uint32_t)t0, v);
+          // partial tile: slot 1 if this CTA owns the tile's first stage (then it is this CTA's LAST segment), else slot 0
+          // (its FIRST segment) -- a CTA never needs the same slot twice
+          const int slot = (s0 == 0) ? 1 : 0;
+          float* part = p.ws_part + ((int64_t)cta * 2 + slot) * slot_elems;
+          for (int t0 = 0; t0 < TN; t0 += EPI_TOK) {
+            float a[EPI_TOK], b[EPI_TOK];
+            tmem_ld8(dA + (uint32_t)t0, a);
+            tmem_ld8(dB + (uint32_t)t0, b);
             tmem_ld_wait();
-            const uint32_t sb = stage_begin();
 #pragma unroll
-            for (int j = 0; j < EPI_TOK; ++j) sts16(sb + (uint32_t)(j * 128 + rp) * 2u, Tr<T>::from_f(v[j]));
-            stage_end(sb, &tm_y, blk ? rowB0 : rowA0, tok0 + t0, false);
+            for (int j = 0; j < EPI_TOK; ++j) {
+              __stcg(part + (int64_t)(t0 + j) * 128 + r, a[j] * DSCALE);
+              __stcg(part + (int64_t)(TN + t0 + j) * 128 + r, b[j] * DSCALE);
+            }
           }
+          if (slot) def1 = tile; else def0 = tile;
         }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(accum_empty(buf));    // this D buffer may be overwritten by a later segment's MMAs
-      if (via_acc && !(p.debug & 4)) {
-        const int nseg = owner_of((long long)tile * p.num_st + p.num_st - 1, p.U, G) - c_first + 1;
-        float* acc = p.ws_acc + (int64_t)acc_row0 * 128;
-        const int n0 = rowA0 + r, n1 = rowB0 + r;      // output columns of this thread (block 0 / block 1)
-        const int c0 = p.y_perm ? perm8_pos(n0) : n0, c1 = p.y_perm ? perm8_pos(n1) : n1;
-        if (et == 0) {
-          bulk_wait_all();                             // our reduce-adds have been performed ...
-          __threadfence();                             // ... and are visible before the arrival is counted
-          const int old = atomicAdd(p.ws_counter + tile, 1);
-          const int last = (old == nseg - 1);
-          if (last) p.ws_counter[tile] = 0;            // self-cleaning for the next launch
-          asm volatile("st.shared.u32 [%0], %1;" ::"r"(flag_slot), "r"(last) : "memory");
-        }
-        named_bar_sync(1, EPI_THREADS);
-        int last;
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(last) : "r"(flag_slot));
-        if (last) {
-          __threadfence();
-          for (int t = 0; t < TN; t += 8) {
-            float v0[8], v1[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {               // 16 independent L2 loads in flight
-              v0[j] = __ldcg(acc + (int64_t)(t + j) * 128 + r);
-              v1[j] = __ldcg(acc + ((int64_t)TN + t + j) * 128 + r);
-            }
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const int tok = tok0 + t + j;
-              if (tok < p.M_tok) {
-                if (p.epi == B200P_EPI_STORE) {
-                  T* y = reinterpret_cast<T*>(p.y) + (int64_t)tok * p.ldy;
-                  if (n0 < p.N) y[c0] = Tr<T>::from_f(v0[j]);
-                  if (n1 < p.N) y[c1] = Tr<T>::from_f(v1[j]);
-                } else if (p.epi == B200P_EPI_STORE_F32) {
-                  float* y = reinterpret_cast<float*>(p.y) + (int64_t)tok * p.ldy;
-                  if (n0 < p.N) y[n0] = v0[j];
-                  if (n1 < p.N) y[n1] = v1[j];
-                } else {
-                  T* y = reinterpret_cast<T*>(p.y) + (int64_t)tok * p.ldy;
-                  if (n0 < p.N / 2) y[c0] = Tr<T>::from_f(silu_tc(v0[j]) * v1[j]);
-                }
-              }
-              __stcg(acc + (int64_t)(t + j) * 128 + r, 0.f);
-              __stcg(acc + ((int64_t)TN + t + j) * 128 + r, 0.f);
-            }
-          }
-        }
-        named_bar_sync(2, EPI_THREADS);                // flag_slot is reused by the next segment
-      }
       u += ns;
     }
-    if (et == 0) bulk_wait_all();                      // staging memory and outputs are settled before the CTA retires
+
+    // ---- split tiles: meet the other contributors, then reduce and finish a share of each tile
+    if (def0 >= 0 || def1 >= 0) {
+      __threadfence();                                 // this thread's partial stores are performed device-wide ...
+      named_bar_sync(1, EPI_THREADS);                  // ... for all 128 epilogue threads before the arrival is published
+      if (et == 0) {
+        if (def0 >= 0) atomicAdd(p.ws_counter + 2 * def0, 1);
+        if (def1 >= 0) atomicAdd(p.ws_counter + 2 * def1, 1);
+      }
+      for (int i = 0; i < 2; ++i) {
+        const int tile = i ? def1 : def0;
+        if (tile < 0) continue;
+        const int c_first = owner_of(tile * p.num_st, p.U, G);
+        const int c_last = owner_of(tile * p.num_st + p.num_st - 1, p.U, G);
+        const int S = c_last - c_first + 1, me = cta - c_first;
+        if (et == 0) {
+          const volatile int* cnt = p.ws_counter + 2 * tile;
+          unsigned long long t_start;
+          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
+          while (*cnt < S) {
+            __nanosleep(40);
+            unsigned long long t_now;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_now));
+            if (t_now - t_start > 4000000000ull) __trap();      // a contributor never arrived: fail loudly, do not hang
+          }
+          __threadfence();
+        }
+        named_bar_sync(2, EPI_THREADS);
+        const int pair = tile / p.tiles_m, tm = tile % p.tiles_m;
+        const int rowA0 = silu ? pair * 128 : pair * 256;
+        const int rowB0 = silu ? p.N / 2 + pair * 128 : pair * 256 + 128;
+        const int tok0 = tm * TN;
+        for (int t0 = me * EPI_TOK; t0 < TN; t0 += S * EPI_TOK) {
+          if (tok0 + t0 >= p.M_tok) break;             // padding tokens of the last token tile
+          float a[EPI_TOK], b[EPI_TOK];
+#pragma unroll
+          for (int j = 0; j < EPI_TOK; ++j) a[j] = b[j] = 0.f;
+#pragma unroll 2
+          for (int c = c_first; c <= c_last; ++c) {     // fixed order: bit-reproducible sums
+            const float* part = p.ws_part + ((int64_t)c * 2 + (c == c_first ? 1 : 0)) * slot_elems;
+            float va[EPI_TOK], vb[EPI_TOK];
+#pragma unroll
+            for (int j = 0; j < EPI_TOK; ++j) {         // 16 independent L2 loads in flight
+              va[j] = __ldcg(part + (int64_t)(t0 + j) * 128 + r);
+              vb[j] = __ldcg(part + (int64_t)(TN + t0 + j) * 128 + r);
+            }
+#pragma unroll
+            for (int j = 0; j < EPI_TOK; ++j) { a[j] += va[j]; b[j] += vb[j]; }
+          }
+          emit(a, b, rowA0, rowB0, tok0 + t0);
+        }
+        // the last contributor to finish re-arms the tile's counters for the next launch (all S have passed the wait)
+        if (et == 0) {
+          const int old = atomicAdd(p.ws_counter + 2 * tile + 1, 1);
+          if (old == S - 1) {
+            p.ws_counter[2 * tile] = 0;
+            p.ws_counter[2 * tile + 1] = 0;
+          }
+        }
+      }
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -681,7 +731,7 @@ static EncodeTiledFn get_encode() {
 }
 
 constexpr int SMEM_BUDGET = 227 * 1024;
-constexpr int SMEM_FIXED = 1024 /*align*/ + NSB * SB_SLOT_BYTES + EPI_NBUF * EPI_BUF_BYTES + 512 /*barriers*/;
+constexpr int SMEM_FIXED = 1024 /*align*/ + NSB * SB_SLOT_BYTES + 512 /*barriers*/;
 static_assert(8 * (4 * MAX_STAGES + 2 * NSLOT + 2 * NSB + 4) + 8 <= 512, "barrier block overflows its slot");
 // smallest M that may take the tensor path.  1: the tile kernel beats the CUDA-core GEMV at EVERY M (8.4 vs 10.2 us at
 // M = 1 on q|k|v, 22.5 vs 33.0 us on gate|up: profiles/r1_run11_qmm_sweep_gemv_vs_tensor.txt), so the CUDA-core GEMV only
@@ -704,7 +754,7 @@ static TcPlan make_plan(int64_t M, int64_t N, int64_t K, int bits, int epi) {
   pl.pairs = (int)(epi == B200P_EPI_SILU_MUL ? (N / 2 + 127) / 128 : (N + 255) / 256);
   const int kps = bits == 4 ? 4 : 2;                       // k-blocks per 128-byte stage row
   const int num_st = (int)((K / 64 + kps - 1) / kps);
-  pl.U = (long long)pl.pairs * pl.tiles_m * num_st;
+  pl.U = (long long)pl.pairs * pl.tiles_m * num_st;     // qmm_tc_supported bounds it to 32-bit unit arithmetic
   long long g = (pl.U + MIN_UNITS_PER_CTA - 1) / MIN_UNITS_PER_CTA;
   const int sms = sm_count();
   pl.grid = (int)(g > sms ? sms : (g < 1 ? 1 : g));
@@ -733,21 +783,21 @@ bool qmm_tc_supported(int64_t M, int64_t N, int64_t K, int gs, int bits, int dty
 static size_t ws_counter_bytes(int64_t M, int64_t N) {
   const int64_t tn = M >= MAX_TN ? MAX_TN : ((M + 15) / 16) * 16;
   const int64_t tiles_m = (M + tn - 1) / tn;
-  return ((size_t)(tiles_m * ((N + 255) / 256 + 1)) * sizeof(int) + 255) & ~(size_t)255;
+  return ((size_t)(tiles_m * ((N + 255) / 256 + 1)) * 2 * sizeof(int) + 255) & ~(size_t)255;   // {arrived, done} per tile
 }
 
 size_t qmm_tc_workspace_bytes(int64_t M, int64_t N, int64_t K) {
   (void)K;
   if (M < 1) return 0;
   const int64_t tn = M >= MAX_TN ? MAX_TN : ((M + 15) / 16) * 16;
-  // per-tile arrival counters + one fp32 [2*TN x 128] accumulator per CTA boundary; all must be ZERO on first use
-  // (the kernel leaves them zero)
-  return ws_counter_bytes(M, N) + (size_t)sm_count() * 2 * tn * 128 * sizeof(float);
+  // per-tile counters (ZERO on first use; the kernel leaves them zero) + two fp32 [2*TN x 128] partial-tile slots per CTA
+  // (a CTA's first and last segment; no initial state)
+  return ws_counter_bytes(M, N) + (size_t)sm_count() * 2 * 2 * tn * 128 * sizeof(float);
 }
 
-template <typename T, int BITS, bool XPERM>
+template <typename T, int BITS, bool XPERM, bool FAST>
 static int launch_tc(const CUtensorMap* tms, const TcParams& p, const TcPlan& pl, cudaStream_t st) {
-  auto kern = qmm_tc_kernel<T, BITS, XPERM>;
+  auto kern = qmm_tc_kernel<T, BITS, XPERM, FAST>;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET);
@@ -764,7 +814,7 @@ static int launch_tc(const CUtensorMap* tms, const TcParams& p, const TcPlan& pl
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled_gemm() ? 1 : 0;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tms[0], tms[1], tms[2], tms[3], tms[4], tms[5], p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tms[0], tms[1], tms[2], tms[3], p);
   if (e != cudaSuccess) return cuda_fail(e, "qmm_tc_kernel launch");
   return B200P_OK;
 }
@@ -795,7 +845,8 @@ int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b
   const int num_kb = (int)(K / 64);
   const bool sb_tma = (num_kb % 8) == 0 && aligned(s, 16) && aligned(b, 16);
   const CUtensorMapDataType dt16 = dtype == B200P_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
-  CUtensorMap tms[6];
+  const bool fast = (flags & B200P_W_SMALLSCALE) != 0 && dtype == B200P_F16;
+  CUtensorMap tms[4];
   int rc = encode_2d(enc, &tms[0], CU_TENSOR_MAP_DATA_TYPE_UINT8, w, (uint64_t)(K * bits / 8), (uint64_t)N,
                      (uint64_t)(K * bits / 8), 128u, 128u, CU_TENSOR_MAP_SWIZZLE_128B, "weights");
   if (rc) return rc;
@@ -816,37 +867,28 @@ int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b
   TcParams p;
   p.scales = s; p.biases = b; p.y = y;
   const size_t counters = ws_counter_bytes(M, N);
-  const size_t need = counters + (size_t)pl.grid * 2 * pl.TN * 128 * sizeof(float);
+  const size_t need = counters + (size_t)pl.grid * 2 * 2 * pl.TN * 128 * sizeof(float);
   B200P_REQUIRE(ws_bytes >= need && aligned(ws, 16), B200P_ERR_ARG, "qmm workspace too small (%zu < %zu)", ws_bytes, need);
   {
-    // output tensor: [M tokens x n_out columns]; staging tiles are [16 tokens x 128 columns]
     const bool f32out = epi == B200P_EPI_STORE_F32 || epi == B200P_EPI_ADD_RESIDUAL;
-    const uint64_t n_out = (uint64_t)(epi == B200P_EPI_SILU_MUL ? N / 2 : N);
-    const size_t esz = f32out ? 4 : 2;
-    B200P_REQUIRE(aligned(y, 16) && (ldy * esz) % 16 == 0, B200P_ERR_ALIGN, "y rows must be 16-byte aligned for the tensor path (ldy=%lld)",
+    B200P_REQUIRE(aligned(y, 4) && (f32out || ldy % 2 == 0), B200P_ERR_ALIGN, "y rows must be 4-byte aligned for the tensor path (ldy=%lld)",
                   (long long)ldy);
-    rc = encode_2d(enc, &tms[4], f32out ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : dt16, y, n_out, (uint64_t)M, (uint64_t)ldy * esz, 128u,
-                   (uint32_t)EPI_TOK, CU_TENSOR_MAP_SWIZZLE_NONE, "y");
-    if (rc) return rc;
-    // stream-K accumulators: one fp32 [2*TN x 128] block per CTA boundary
-    rc = encode_2d(enc, &tms[5], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, reinterpret_cast<char*>(ws) + counters, 128u,
-                   (uint64_t)pl.grid * 2 * pl.TN, 512u, 128u, (uint32_t)EPI_TOK, CU_TENSOR_MAP_SWIZZLE_NONE, "acc");
-    if (rc) return rc;
   }
   p.ws_counter = reinterpret_cast<int*>(ws);
-  p.ws_acc = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + counters);
+  p.ws_part = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + counters);
   p.M_tok = (int)M; p.N = (int)N; p.K = (int)K; p.TN = pl.TN; p.ldy = ldy; p.epi = epi; p.y_perm = y_perm ? 1 : 0;
-  p.num_kb = num_kb; p.pairs = pl.pairs; p.tiles_m = pl.tiles_m; p.U = pl.U;
+  B200P_REQUIRE(pl.U * (pl.grid + 1) < (1ll << 31), B200P_ERR_ARG, "problem too large for the tensor path (%lld units)", pl.U);
+  p.num_kb = num_kb; p.pairs = pl.pairs; p.tiles_m = pl.tiles_m; p.U = (int)pl.U;
   p.num_st = (p.num_kb + (bits == 4 ? 4 : 2) - 1) / (bits == 4 ? 4 : 2);
   p.sb_tma = sb_tma ? 1 : 0;
   p.w_stages = pl.w_stages; p.x_slots = pl.x_slots;
-  { const char* d = getenv("B200P_TC_DEBUG"); p.debug = d ? atoi(d) : 0; }
   if (dtype == B200P_F16) {
-    if (bits == 8) return launch_tc<__half, 8, false>(tms, p, pl, st);
-    return x_perm ? launch_tc<__half, 4, true>(tms, p, pl, st) : launch_tc<__half, 4, false>(tms, p, pl, st);
+    if (bits == 8) return fast ? launch_tc<__half, 8, false, true>(tms, p, pl, st) : launch_tc<__half, 8, false, false>(tms, p, pl, st);
+    if (fast) return x_perm ? launch_tc<__half, 4, true, true>(tms, p, pl, st) : launch_tc<__half, 4, false, true>(tms, p, pl, st);
+    return x_perm ? launch_tc<__half, 4, true, false>(tms, p, pl, st) : launch_tc<__half, 4, false, false>(tms, p, pl, st);
   } else {
     B200P_REQUIRE(bits == 4, B200P_ERR_ARG, "bf16 8-bit is not on the tensor path");
-    return x_perm ? launch_tc<__nv_bfloat16, 4, true>(tms, p, pl, st) : launch_tc<__nv_bfloat16, 4, false>(tms, p, pl, st);
+    return x_perm ? launch_tc<__nv_bfloat16, 4, true, false>(tms, p, pl, st) : launch_tc<__nv_bfloat16, 4, false, false>(tms, p, pl, st);
   }
 }
 

@@ -22,6 +22,7 @@ applied at load time by ``tp.shard_*`` and adds one all-reduce after each row-sp
 """
 from __future__ import annotations
 
+import threading
 from typing import Dict, List, Optional
 
 import torch
@@ -31,13 +32,10 @@ from .._lib import EPI_ADD_RESIDUAL, EPI_SILU_MUL, EPI_STORE, EPI_STORE_F32
 from .base import BatchedKVCache, PagedKVCache
 
 MAX_TOKENS_PER_FORWARD = 8192     # chunk size (B*L) of one prefill pass through the layers
-# Up to this many rows the fused q|k|v and gate|up projections accumulate in fp32 buffers (stream-K partial tiles are summed
-# by TMA reduce-adds, the consumer kernel rounds and re-zeroes).  Above it (prefill) few tiles are split, the fp32 buffers
-# would be HBM traffic (235 MB per layer at 2048 rows: silu_mul alone took 245 us), so the 16-bit fused epilogues are used.
-# 128, not 64: a decode batch of 128 rows is still ONE row tile split over all SMs, and the 16-bit epilogues' fix-up of
-# the split tiles through the workspace cost 2.3x there (profiles/r1_run29_tp_shard_proxy.txt: q|k|v 39.5 vs 15.3 us).
-ACC32_MAX_ROWS = 128
 USE_PERM8 = True                  # 4-bit 16-bit models: GEMM inputs in the PERM8 column order (include/b200p.h)
+# |scale| bound under which an f16 matrix may take the subnormal-operand dequant (B200P_W_SMALLSCALE, csrc/dequant.cuh):
+# the kernel needs s * 2^20 finite in half precision, i.e. |s| < 0.0625; checked once per matrix at load time.
+SMALL_SCALE_BOUND = 0.06
 
 
 class QuantizedLinear:
@@ -47,16 +45,21 @@ class QuantizedLinear:
         self.in_features, self.out_features = in_features, out_features
         self.group_size, self.bits = group_size, bits
         self.weight = self.scales = self.biases = None
+        self.small_scale = False
 
-    def set(self, weight, scales, biases):
+    def set(self, weight, scales, biases, small_scale: Optional[bool] = None):
         self.weight, self.scales, self.biases = weight, scales, biases
         self.out_features = weight.shape[0]
         self.in_features = weight.shape[1] * 32 // self.bits
+        if small_scale is None:      # one reduction + host read per matrix, at load time only
+            small_scale = (scales.dtype == torch.float16 and scales.is_cuda and scales.numel() > 0
+                           and float(scales.abs().max()) < SMALL_SCALE_BOUND)
+        self.small_scale = bool(small_scale)
 
     def __call__(self, x, epilogue=EPI_STORE, out=None, workspace=None, x_perm=False, y_perm=False):
         lead = x.shape[:-1]
         y = ops.qmm(x.reshape(-1, x.shape[-1]), self.weight, self.scales, self.biases, self.group_size,
-                    self.bits, epilogue, out, workspace, x_perm=x_perm, y_perm=y_perm)
+                    self.bits, epilogue, out, workspace, x_perm=x_perm, y_perm=y_perm, small_scale=self.small_scale)
         return y if out is not None else y.reshape(*lead, -1)
 
 
@@ -132,11 +135,12 @@ def _fuse_rows(parts: List[QuantizedLinear], fused: QuantizedLinear):
     w = torch.cat([p.weight for p in parts], 0).contiguous()
     s = torch.cat([p.scales for p in parts], 0).contiguous()
     b = torch.cat([p.biases for p in parts], 0).contiguous()
-    fused.set(w, s, b)
+    flags = [p.small_scale for p in parts]
+    fused.set(w, s, b, small_scale=all(flags))
     r = 0
-    for p in parts:
+    for p, fl in zip(parts, flags):
         n = p.weight.shape[0]
-        p.set(w[r:r + n], s[r:r + n], b[r:r + n])
+        p.set(w[r:r + n], s[r:r + n], b[r:r + n], small_scale=fl)
         r += n
 
 
@@ -160,6 +164,11 @@ class DecoderModel:
         self.dtype: Optional[torch.dtype] = None
         self.device: Optional[torch.device] = None
         self._arenas: Dict[int, dict] = {}
+        # One forward at a time per model instance (SURVEY 8b "Threading"): the scratch arenas, the self-cleaning qmm
+        # workspace and the fp32 accumulators are shared by every caller of this model, and the reference server runs
+        # generate_step from an executor thread and from the event loop at once (utils.py:1345 vs server/main.py:1358).
+        # Held around every eager forward, every decode-step replay and every graph capture.
+        self._lock = threading.RLock()
         self.tp_rank, self.tp_world, self.tp_group = 0, 1, None
         self._allreduce = None
         rs = getattr(args, "rope_scaling", None)
@@ -330,10 +339,6 @@ class DecoderModel:
                 h=torch.empty((M, args.hidden_size), dtype=torch.float32, device=dev),
                 x=torch.empty((M, args.hidden_size), dtype=dt, device=dev),
                 qkv=torch.empty((M, nqkv), dtype=dt, device=dev),
-                # fp32 split-K accumulation buffers of the fused q|k|v and gate|up projections (16-bit models): zero
-                # once, the consumer kernels (rope_kv_append, silu_mul) re-zero them behind their reads
-                qkv32=torch.zeros((M, nqkv), dtype=torch.float32, device=dev) if self._fast16 and M <= ACC32_MAX_ROWS else None,
-                gu32=torch.zeros((M, 2 * inter_local), dtype=torch.float32, device=dev) if self._fast16 and M <= ACC32_MAX_ROWS else None,
                 q=torch.empty((M, att.n_heads * att.head_dim), dtype=dt, device=dev),
                 att=torch.empty((M, att.n_heads * att.head_dim), dtype=dt, device=dev),
                 act=torch.empty((M, inter_local), dtype=dt, device=dev),
@@ -356,10 +361,9 @@ class DecoderModel:
         args = self.args
         self.model.embed_tokens.embed(ids_i32, out=a["h"])
         tp = self.tp_world > 1
-        # 16-bit models: (i) the fused projections accumulate in fp32 (stream-K partial tiles are summed by TMA
-        # reduce-adds, no second pass) and the consumer kernel rounds to the storage type; (ii) with 4-bit weights the
-        # GEMM inputs travel in the PERM8 column order the tensor path unpacks nibbles in.
-        f16 = self._fast16 and a["qkv32"] is not None
+        # 16-bit models with 4-bit weights: GEMM inputs travel in the PERM8 column order the tensor path unpacks nibbles
+        # in.  q|k|v leaves its GEMM in the storage type (what nn.QuantizedLinear returns, llama.py:93) and gate|up as
+        # silu(gate)*up: split-K tiles are reduced inside the GEMM kernel, there is no fp32 side buffer.
         pm = self._perm8
         fx = getattr(self, "_tp_fused", None) if tp else None      # peer-memory exchange (tp.PeerExchange) or NCCL
         layers = self.model.layers
@@ -371,16 +375,12 @@ class DecoderModel:
             lengths = c.lengths(self.device)
             if fx is None or li == 0:      # with the fused exchange the previous layer's down_proj exchange wrote x
                 ops.rmsnorm(a["h"], layer.input_layernorm.weight, layer.input_layernorm.eps, out=a["x"], out_perm=pm)
-            if f16:
-                at.qkv_proj(a["x"], EPI_ADD_RESIDUAL, out=a["qkv32"], workspace=a["ws"], x_perm=pm)
-            else:
-                at.qkv_proj(a["x"], EPI_STORE, out=a["qkv"], workspace=a["ws"], x_perm=pm)
+            at.qkv_proj(a["x"], EPI_STORE, out=a["qkv"], workspace=a["ws"], x_perm=pm)
             if at.lora:                    # LoRA on q_proj / v_proj (A.9): low-rank update of the q / v column blocks
-                qkv_buf = a["qkv32"] if f16 else a["qkv"]
                 for name, (At, Bt, scale) in at.lora.items():
                     col0 = 0 if name == "q_proj" else (at.n_heads + at.n_kv_heads) * at.head_dim
-                    ops.lora_add(a["x"], At, Bt, qkv_buf, col0, scale)
-            ops.rope_kv_append(a["qkv32"] if f16 else a["qkv"], a["q"], c.keys, c.values, lengths, B, L, at.n_heads,
+                    ops.lora_add(a["x"], At, Bt, a["qkv"], col0, scale)
+            ops.rope_kv_append(a["qkv"], a["q"], c.keys, c.values, lengths, B, L, at.n_heads,
                                at.n_kv_heads, at.head_dim, args.rope_theta, self.rope_scale,
                                at.q_norm.weight if at.q_norm else None, at.k_norm.weight if at.k_norm else None,
                                args.rms_norm_eps)
@@ -403,11 +403,7 @@ class DecoderModel:
                     self._allreduce(a["h"])
                 ops.rmsnorm(a["h"], layer.post_attention_layernorm.weight, layer.post_attention_layernorm.eps, out=a["x"],
                             out_perm=pm)
-            if f16:
-                mlp.gate_up_proj(a["x"], EPI_ADD_RESIDUAL, out=a["gu32"], workspace=a["ws"], x_perm=pm)
-                ops.silu_mul(a["gu32"], a["act"], out_perm=pm)
-            else:
-                mlp.gate_up_proj(a["x"], EPI_SILU_MUL, out=a["act"], workspace=a["ws"], x_perm=pm, y_perm=pm)
+            mlp.gate_up_proj(a["x"], EPI_SILU_MUL, out=a["act"], workspace=a["ws"], x_perm=pm, y_perm=pm)
             if fx is not None:
                 mlp.down_proj(a["act"], EPI_ADD_RESIDUAL, out=fx.partial(1, M), workspace=a["ws"], x_perm=pm)
                 nxt = layers[li + 1].input_layernorm if li + 1 < len(layers) else None
@@ -443,6 +439,10 @@ class DecoderModel:
     def __call__(self, inputs, cache: Optional[List[BatchedKVCache]] = None, last_only: bool = False):
         """inputs int [B, L] -> logits float32 [B, L, V] (or [B, 1, V] with last_only, the only rows
         generate_step reads, utils.py:404 / SURVEY B10).  Under TP the vocab axis is this rank's shard."""
+        with self._lock:
+            return self._forward_locked(inputs, cache, last_only)
+
+    def _forward_locked(self, inputs, cache, last_only):
         if not isinstance(inputs, torch.Tensor):
             inputs = torch.as_tensor(inputs)
         inputs = inputs.to(self.device)

@@ -102,10 +102,11 @@ def qmm_workspace_bytes(M, N, K) -> int:
 
 
 def qmm(x, w, scales, biases, group_size=64, bits=4, epilogue=EPI_STORE, out=None, workspace=None,
-        x_perm=False, y_perm=False):
+        x_perm=False, y_perm=False, small_scale=False):
     """quantized_matmul(x, w, scales, biases, transpose=True) with a fused epilogue.
 
     ``x_perm`` / ``y_perm``: x arrives / the 16-bit y leaves in the PERM8 column order (include/b200p.h).
+    ``small_scale``: the caller has checked max|scales| < 0.0625 (B200P_W_SMALLSCALE).
 
     x [M, K] (row stride = x.stride(0)); out per epilogue:
       EPI_STORE -> [M, N] x.dtype; EPI_STORE_F32 -> [M, N] float32; EPI_ADD_RESIDUAL -> out (float32
@@ -124,7 +125,8 @@ def qmm(x, w, scales, biases, group_size=64, bits=4, epilogue=EPI_STORE, out=Non
             out = torch.empty((M, N // 2), dtype=x.dtype, device=x.device)
         else:
             raise ValueError("EPI_ADD_RESIDUAL needs the residual tensor as `out`")
-    epi_flags = epilogue | (_lib.X_PERM8 if x_perm else 0) | (_lib.Y_PERM8 if y_perm else 0)
+    epi_flags = (epilogue | (_lib.X_PERM8 if x_perm else 0) | (_lib.Y_PERM8 if y_perm else 0)
+                 | (_lib.W_SMALLSCALE if small_scale else 0))
     ws_ptr, ws_bytes = (0, 0) if workspace is None else (workspace.data_ptr(), workspace.numel() * workspace.element_size())
     _call(("b200p_qmm", N, K), lambda: lib().b200p_qmm(_p(x), _p(w), _p(scales), _p(biases), _p(out), M, N, K, x.stride(0), out.stride(0),
                           group_size, bits, dtype_code(x.dtype), epi_flags, ws_ptr, ws_bytes, _stream()))

@@ -5,6 +5,7 @@ import torch
 from mlx_parallm_b200 import ops, _lib
 L = _lib.lib(); _lib.require_device()
 M, N, K, epi = [int(v) for v in sys.argv[1:5]]
+small = len(sys.argv) > 5 and sys.argv[5] == "small"
 dt = torch.float16
 g = torch.Generator(device="cuda"); g.manual_seed(1)
 mats = []
@@ -21,7 +22,7 @@ evs = []
 for i in range(8):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    ops.qmm(x, *mats[i % 4], 64, 4, epi, out=out, workspace=ws)
+    ops.qmm(x, *mats[i % 4], 64, 4, epi, out=out, workspace=ws, x_perm=True, y_perm=epi in (0, 3), small_scale=small)
     e1.record()
     evs.append((e0, e1))
 torch.cuda.synchronize()

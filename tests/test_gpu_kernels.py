@@ -111,7 +111,7 @@ def test_quantize_dequantize_roundtrip_full_size(ops):
 
 
 # ---------------------------------------------------------------- quantized matmul
-def qmm_case(ops, M, N, K, bits, dtype, epi, seed=0, path=0, ragged_ld=False):
+def qmm_case(ops, M, N, K, bits, dtype, epi, seed=0, path=0, ragged_ld=False, small_scale=False):
     from mlx_parallm_b200 import _lib
     rng = np.random.default_rng(seed)
     wq = rng.integers(0, 2 ** 32, (N, K * bits // 32), dtype=np.uint32)
@@ -132,10 +132,10 @@ def qmm_case(ops, M, N, K, bits, dtype, epi, seed=0, path=0, ragged_ld=False):
         if epi == _lib.EPI_ADD_RESIDUAL:
             res = rng.standard_normal((M, N)).astype(np.float32)
             out = torch.from_numpy(res.copy()).cuda()
-            ops.qmm(xt, w_(wq), t_(s, dtype), t_(b, dtype), 64, bits, epi, out=out, workspace=ws)
+            ops.qmm(xt, w_(wq), t_(s, dtype), t_(b, dtype), 64, bits, epi, out=out, workspace=ws, small_scale=small_scale)
             exp = res + acc
         else:
-            out = ops.qmm(xt, w_(wq), t_(s, dtype), t_(b, dtype), 64, bits, epi, workspace=ws)
+            out = ops.qmm(xt, w_(wq), t_(s, dtype), t_(b, dtype), 64, bits, epi, workspace=ws, small_scale=small_scale)
             if epi == _lib.EPI_SILU_MUL:
                 g, u = acc[:, :N // 2], acc[:, N // 2:]
                 exp = g / (1 + np.exp(-g)) * u
@@ -414,14 +414,78 @@ def test_qmm_tensor_path_matches_oracle(ops, M, N, K, bits, dtype, epi):
     assert rel_err(got, exp) < tol
 
 
-def test_qmm_tensor_path_is_repeatable_and_matches_gemv(ops):
-    # stream-K tiles shared by several CTAs are summed with fp32 L2 atomics in arrival order: two runs agree to
-    # fp32 rounding of the partial sums (not bit for bit), and both agree with the CUDA-core GEMV path
-    a1, _ = qmm_case(ops, 64, 512, 4096, 4, "float16", 1, seed=3, path=2)
-    a2, _ = qmm_case(ops, 64, 512, 4096, 4, "float16", 1, seed=3, path=2)
+def test_qmm_tensor_path_is_bit_reproducible_and_matches_gemv(ops):
+    # stream-K tiles shared by several CTAs are reduced from per-CTA partial tiles in CTA order (no atomics): two runs
+    # agree bit for bit, and both agree with the CUDA-core GEMV path
+    for epi in (1, 2, 3, 0):
+        a1, _ = qmm_case(ops, 64, 512, 4096, 4, "float16", epi, seed=3, path=2)
+        a2, _ = qmm_case(ops, 64, 512, 4096, 4, "float16", epi, seed=3, path=2)
+        assert np.array_equal(a1, a2), epi
     g, _ = qmm_case(ops, 64, 512, 4096, 4, "float16", 1, seed=3, path=1)
-    assert rel_err(a1, a2) < 1e-5
+    a1, _ = qmm_case(ops, 64, 512, 4096, 4, "float16", 1, seed=3, path=2)
     assert rel_err(a1, g) < 1e-3
+
+
+SPLIT_CASES = [  # every CTA holds a head AND a tail partial tile, tiles shared by 2..8 CTAs, ragged token / row edges
+    (64, 4096, 4096, 4, "float16", 2), (64, 6144, 4096, 4, "float16", 0), (64, 28672 // 4, 4096, 4, "float16", 3),
+    (64, 4096, 14336 // 2, 4, "float16", 2), (37, 1000, 2048, 4, "bfloat16", 1), (128, 1024, 4096, 4, "float16", 3),
+    (130, 520, 1536, 4, "float16", 0), (8, 4096, 4096, 8, "float16", 2), (1, 768, 8192, 4, "float16", 1),
+]
+
+
+@pytest.mark.parametrize("M,N,K,bits,dtype,epi", SPLIT_CASES)
+def test_qmm_tensor_path_split_tiles(ops, M, N, K, bits, dtype, epi):
+    """Layer-sized shapes where stream-K splits every tile: partial tiles through the workspace, shared final reduction,
+    counters left re-armed (the second call reuses the same workspace inside qmm_case's fresh allocation, the third
+    test below reuses one workspace across shapes)."""
+    got, exp = qmm_case(ops, M, N, K, bits, dtype, epi, seed=M + N + K, path=2)
+    tol = {"float16": 3e-3, "bfloat16": 2e-2}[dtype]
+    assert rel_err(got, exp) < tol
+
+
+def test_qmm_tensor_path_workspace_is_left_rearmed(ops):
+    """One workspace, many launches of different shapes back to back (what a decode step does): the per-tile counters
+    must be back at zero after every launch, stale partial tiles must never be read."""
+    from mlx_parallm_b200 import _lib
+    rng = np.random.default_rng(5)
+    shapes = [(64, 4096, 4096, 2), (64, 6144, 4096, 0), (64, 2048, 1024, 3), (16, 512, 8192, 1), (64, 4096, 4096, 2)]
+    ws = torch.zeros((max(ops.qmm_workspace_bytes(64, n, k) for _, n, k, _ in shapes),), dtype=torch.uint8, device="cuda")
+    _lib.check(_lib.lib().b200p_qmm_set_path(2))
+    try:
+        for rep in range(3):
+            for M, N, K, epi in shapes:
+                wq = rng.integers(0, 2 ** 32, (N, K // 8), dtype=np.uint32)
+                s = ref.round_to(rng.uniform(0.5, 1.5, (N, K // 64)) * (2 / 15) / np.sqrt(K), "float16")
+                b = ref.round_to(-s * 7.5, "float16")
+                x = ref.round_to(rng.standard_normal((M, K)), "float16")
+                acc = ref.quantized_matmul(x, wq, s, b, 64, 4).astype(np.float64)
+                if epi == 2:
+                    out = torch.zeros((M, N), dtype=torch.float32, device="cuda")
+                    ops.qmm(t_(x, "float16"), w_(wq), t_(s, "float16"), t_(b, "float16"), 64, 4, epi, out=out, workspace=ws)
+                    exp = acc
+                else:
+                    out = ops.qmm(t_(x, "float16"), w_(wq), t_(s, "float16"), t_(b, "float16"), 64, 4, epi, workspace=ws)
+                    exp = acc if epi != 3 else acc[:, :N // 2] / (1 + np.exp(-acc[:, :N // 2])) * acc[:, N // 2:]
+                assert rel_err(out.float().cpu().numpy(), exp) < 3e-3, (rep, M, N, K, epi)
+        torch.cuda.synchronize()
+        ncnt = 2 * ((4096 + 255) // 256 + 1)
+        assert int(ws[:ncnt * 4].view(torch.int32).abs().sum()) == 0
+    finally:
+        _lib.lib().b200p_qmm_set_path(0)
+
+
+@pytest.mark.parametrize("M,N,K,bits,epi", [(64, 2048, 1024, 4, 3), (64, 4096, 4096, 4, 2), (8, 256, 256, 4, 1), (16, 512, 1024, 4, 0),
+                                            (64, 512, 2048, 8, 1), (5, 1000, 192, 4, 1), (200, 512, 512, 4, 0)])
+def test_qmm_small_scale_dequant_is_bit_identical(ops, M, N, K, bits, epi):
+    """B200P_W_SMALLSCALE (one half2 FMA per code pair on subnormal operands, accumulator rescaled by 16) rounds q*s+b at
+    the same point as the 3-op dequant: identical outputs wherever the operand / 16 stays a normal half."""
+    a, exp = qmm_case(ops, M, N, K, bits, "float16", epi, seed=11, path=2, small_scale=False)
+    f, _ = qmm_case(ops, M, N, K, bits, "float16", epi, seed=11, path=2, small_scale=True)
+    assert rel_err(f, exp) < 3e-3
+    if bits == 4 and K <= 1024:
+        assert np.array_equal(a, f)          # every |q*s+b| / 16 is a normal half here
+    else:
+        assert rel_err(a, f) < 2e-5          # operands below 2^-10 round as subnormals at 1/16: absolute error <= 2^-21
 
 
 # ---------------------------------------------------------------- mma.sync register GEMV of b200p_qmm (M <= 16)
