@@ -11,6 +11,8 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200parallm.so")
+# profiling builds only (scripts/tc_bisect.py): a library compiled with -DB200P_TC_DEBUG=<mask> under build/
+LIB_PATH = os.environ.get("B200P_LIB", LIB_PATH)
 
 F32, F16, BF16 = 0, 1, 2
 DQ_F32_MULADD, DQ_FMA, DQ_T_MULADD = 0, 1, 2

@@ -28,6 +28,9 @@ int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b
                   int64_t K, int64_t ldx, int64_t ldy, int bits, int dtype, int epi, int flags, void* ws, size_t ws_bytes,
                   cudaStream_t st);
 size_t qmm_tc_workspace_bytes(int64_t M, int64_t N, int64_t K);
+bool qmm_sk_supported(int64_t M, int64_t N, int64_t K, int bits, int epi, const void* y, int64_t ldy);
+int qmm_sk_launch(const void* x, const uint32_t* w, const void* s, const void* b, void* y, int64_t M, int64_t N,
+                  int64_t K, int64_t ldx, int64_t ldy, int bits, int dtype, int flags, cudaStream_t st);
 void qmm_tc_set_min_m(int m);
 bool qmv_mma_supported(int64_t M, int64_t N, int64_t K, int gs, int bits, int dtype, int epi);
 int qmv_mma_launch(const void* x, const uint32_t* w, const void* s, const void* b, void* y, int64_t M, int64_t N, int64_t K,
@@ -44,6 +47,7 @@ bool attn_prefill_supported(int64_t L, int Hq, int Hkv, int D, int dtype);
 int attn_prefill_launch(const void* q, const void* kc, const void* vc, const int32_t* lengths, void* out, int64_t B, int64_t L,
                         int Hq, int Hkv, int D, int64_t Tcap, float scale, int dtype, int out_perm, cudaStream_t st);
 
+static const bool g_use_sk = [] { const char* e = getenv("B200P_QMM_SK"); return !e || atoi(e) != 0; }();
 static int g_qmm_path = 0;   // 0 auto, 1 CUDA-core gemv, 2 tcgen05 tiles, 3 mma.sync gemv
 // Auto rule for the mma.sync GEMV, from the measured three-way sweep (profiles/r1_run12_qmm_sweep_three_paths.txt, us per
 // launch in a CUDA graph): it wins where the tile kernel's fixed cost dominates -- M <= 4 and matrices up to ~32 M weights
@@ -172,6 +176,10 @@ extern "C" int b200p_qmm(const void* x, const uint32_t* w, const void* scales, c
   if (g_qmm_path == 2) {
     B200P_REQUIRE(tc_ok, B200P_ERR_ARG, "tensor path forced but unsupported for this call");
   }
+  // fp32 accumulate epilogue: the stream-K kernel (partial tiles summed by TMA reduce-adds, no workspace, no tail);
+  // B200P_QMM_SK=0 keeps everything on the whole-tile kernel (A/B measurements)
+  if (tc_ok && g_qmm_path != 1 && g_use_sk && qmm_sk_supported(M, N, K, bits, epilogue, y, ldy))
+    return qmm_sk_launch(x, w, scales, biases, y, M, N, K, ldx, ldy, bits, dtype, flags, st);
   if (tc_ok && g_qmm_path != 1) {
     B200P_REQUIRE(workspace && workspace_bytes >= qmm_tc_workspace_bytes(M, N, K), B200P_ERR_ARG,
                   "tensor path needs a workspace of %zu bytes", qmm_tc_workspace_bytes(M, N, K));

@@ -51,157 +51,19 @@
 #include <cuda.h>
 
 #include <stdlib.h>
+#include <initializer_list>
+#include <mutex>
 #include <type_traits>
+#include <unordered_map>
 
 #include "common.cuh"
 #include "dequant.cuh"
+#include "tc_ptx.cuh"
 
 namespace b200p {
 
 int sm_count();
 bool pdl_enabled_gemm();
-
-// ------------------------------------------------------------------------------------------------ PTX
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "WAIT_LOOP:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra WAIT_DONE;\n"
-      "bra WAIT_LOOP;\n"
-      "WAIT_DONE:\n"
-      "}\n" ::"r"(bar),
-      "r"(parity)
-      : "memory");
-}
-// one lane of a CONVERGED warp; unlike `lane == 0` the compiler knows the guarded code is warp-uniform, so tcgen05 /
-// TMA operands go straight to uniform registers (no per-instruction uniformisation loop)
-__device__ __forceinline__ bool elect_one() {
-  uint32_t pred;
-  asm volatile(
-      "{\n"
-      ".reg .pred P1;\n"
-      "elect.sync _|P1, 0xffffffff;\n"
-      "selp.b32 %0, 1, 0, P1;\n"
-      "}\n"
-      : "=r"(pred));
-  return pred != 0;
-}
-__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
-      "l"(map), "r"(c0), "r"(c1), "r"(bar)
-      : "memory");
-}
-__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
-  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
-}
-
-__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
-  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
-  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
-}
-// D[tmem] (+)= A[tmem] * B[smem desc]^T ; kind::f16 covers f16 and bf16 inputs with fp32 accumulation
-__device__ __forceinline__ void umma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accum) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "setp.ne.b32 p, %4, 0;\n"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n"
-      "}\n" ::"r"(d_tmem),
-      "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accum)
-      : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void tmem_ld8(uint32_t taddr, float (&v)[8]) {
-  uint32_t r[8];
-  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
-               : "r"(taddr));
-#pragma unroll
-  for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[i]);
-}
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
-  uint32_t r[16];
-  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-                 "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-               : "r"(taddr));
-#pragma unroll
-  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-__device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
-template <typename T> __device__ __forceinline__ void sts16(uint32_t addr, T v) {
-  asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"(*reinterpret_cast<uint16_t*>(&v)) : "memory");
-}
-// generic-proxy writes to shared memory -> visible to the async proxy (TMA store / reduce reads them)
-__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-// shared-memory tile -> global tensor (rows / columns outside the tensor are clipped by the TMA unit)
-__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, int c0, int c1, uint32_t src) {
-  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];" ::"l"(map), "r"(c0), "r"(c1), "r"(src)
-               : "memory");
-}
-// the same with an element-wise atomic add performed at the destination (fp32 tensor map)
-__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* map, int c0, int c1, uint32_t src) {
-  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%1, %2}], [%3];" ::"l"(map), "r"(c0),
-               "r"(c1), "r"(src)
-               : "memory");
-}
-__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-template <int N> __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
-__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
-// each lane writes 32 consecutive 32-bit columns of ITS TMEM lane (= 64 consecutive 16-bit k of one A row)
-__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
-  asm volatile(
-      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,"
-      "%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};" ::"r"(taddr),
-      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
-      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
-      "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
-      "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
-      : "memory");
-}
-__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-
-__device__ __forceinline__ uint4 lds128(uint32_t addr) {
-  uint4 r;
-  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr));
-  return r;
-}
-__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
-  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
-}
-
-// K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor):
-//   [0,14) start>>4 | [16,30) LBO>>4 (=1, unused for swizzled K-major) | [32,46) SBO>>4 (8 rows * 128 B = 1024)
-//   | [46,48) version = 1 | [61,64) layout = 2 (SWIZZLE_128B)
-__device__ __forceinline__ uint64_t make_desc_sw128(uint32_t smem_addr) {
-  return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
-}
-
-__device__ __forceinline__ float silu_tc(float g) { return g / (1.0f + __expf(-g)); }
 
 // ------------------------------------------------------------------------------------------------ kernel
 constexpr int DQ_WARPS = 16;
@@ -214,10 +76,8 @@ constexpr int WARP_MMA = WARP_X + 1;
 constexpr int TC_THREADS = (WARP_MMA + 1) * 32;
 constexpr int TMEM_COLS = 512;
 constexpr int MAX_TN = 128;
-constexpr int W_TILE_BYTES = 128 * 128;          // one weight block of one stage: 128 rows x 128 packed bytes
-constexpr int W_STAGE_BYTES = 2 * W_TILE_BYTES;
-constexpr int NSLOT = 4;                         // A ring slots (each: 2 blocks x 32 TMEM columns)
-constexpr uint32_t A_COL0 = 256;                 // TMEM columns [0,256) hold D, [256,512) the A ring
+constexpr int NSLOT = 8;                         // upper bound of A ring slots (each: 2 blocks x 32 TMEM columns); a launch
+                                                 // uses p.a_slots (even) = what the D buffers leave of the 512 TMEM columns
 constexpr int NSB = 2;                           // scale/bias ring slots
 constexpr int SB_TILE_BYTES = 128 * 16;          // 128 rows x 8 k-blocks x 2 bytes
 constexpr int SB_SLOT_BYTES = 4 * SB_TILE_BYTES; // block 0 scales, block 0 biases, block 1 scales, block 1 biases
@@ -230,6 +90,32 @@ constexpr int EPI_TOK = 8;                       // tokens per epilogue step = w
 #define B200P_TC_DEBUG 0
 #endif
 constexpr int kDebug = B200P_TC_DEBUG;
+// Profiling build only (-DB200P_TC_TIMING=1): CTA 0 accumulates the cycles each role spends in each barrier wait into
+// g_tc_timing (read back with b200p_debug_tc_timing); slots are listed in scripts/tc_timing.py.
+#ifndef B200P_TC_TIMING
+#define B200P_TC_TIMING 0
+#endif
+#if B200P_TC_TIMING
+__device__ unsigned long long g_tc_timing[32];
+#define TWAIT(slot, bar, par)                                   \
+  do {                                                          \
+    const long long t0_ = clock64();                            \
+    mbar_wait(bar, par);                                        \
+    tacc[slot] += (unsigned long long)(clock64() - t0_);        \
+  } while (0)
+#define TDECL unsigned long long tacc[4] = {0ull, 0ull, 0ull, 0ull}; const long long tstart_ = clock64()
+#define TFLUSH(base, n, cond)                                                                                   \
+  do {                                                                                                          \
+    if (blockIdx.x == 0 && (cond)) {                                                                            \
+      for (int i_ = 0; i_ < (n); ++i_) g_tc_timing[(base) + i_] = tacc[i_];                                     \
+      g_tc_timing[(base) + (n)] = (unsigned long long)(clock64() - tstart_);                                    \
+    }                                                                                                           \
+  } while (0)
+#else
+#define TWAIT(slot, bar, par) mbar_wait(bar, par)
+#define TDECL
+#define TFLUSH(base, n, cond)
+#endif
 
 struct TcParams {
   const void* scales;
@@ -244,14 +130,34 @@ struct TcParams {
   int num_kb;          // K / 64
   int num_st;          // stages along K = ceil(num_kb / KPS)
   int pairs, tiles_m;  // output tile t = pair * tiles_m + token tile
-  int U;               // total units = pairs * tiles_m * num_st (the host checks U * (grid + 1) < 2^31: 32-bit unit arithmetic)
+  int R;               // weight rows per MMA block of a tile (multiple of 8, <= 128): a tile is R + R rows
+  int S;               // K splits per tile (1: whole tiles; > 1 only when tiles * S <= grid, one item per CTA)
+  int items;           // work items = tiles * S; CTA c takes items c, c + G, c + 2G, ...
+  int rotate;          // 1: an item's stages are visited in rotated order (seg_of)
+  int nbuf;            // D buffers (2: the epilogue of one item overlaps the main loop of the next; 1 frees TMEM for the A ring)
+  int a_slots;         // A ring depth: (512 - D columns) / 64, even
   int sb_tma;          // 1: scale/bias tiles come through TMA (num_kb % 8 == 0)
   int w_stages;        // weight ring depth
   int x_slots;         // X ring depth (4 or 8; one slot = the [TN x 64] tile of one k-block)
 };
 
-// CTA that owns linear unit x when U units are dealt to G CTAs as [c*U/G, (c+1)*U/G)
-__device__ __forceinline__ int owner_of(int x, int U, int G) { return ((x + 1) * G - 1) / U; }
+// work item -> (output tile, stage range): item = tile * S + split, split covers stages [split*num_st/S, (split+1)*num_st/S)
+// The stages of an item are visited in ROTATED order, starting at stage s0 + rot: CTAs that walk K in lockstep (all at the
+// same 128-byte column of their 2 KB rows) camp on a few HBM channels -- measured 1.0 instead of 2.6 TB/s on gate|up.
+struct TcSeg { int tile, s0, ns, rot; };
+__device__ __forceinline__ TcSeg seg_of(const TcParams& p, int item) {
+  TcSeg g;
+  g.tile = item / p.S;
+  const int split = item - g.tile * p.S;
+  g.s0 = (split * p.num_st) / p.S;
+  g.ns = ((split + 1) * p.num_st) / p.S - g.s0;
+  g.rot = p.rotate ? item % g.ns : 0;
+  return g;
+}
+__device__ __forceinline__ int seg_stage(const TcSeg& g, int i) {
+  const int j = i + g.rot;
+  return g.s0 + (j >= g.ns ? j - g.ns : j);
+}
 
 // FAST: the small-scale dequant of dequant.cuh (f16, caller promised B200P_W_SMALLSCALE): A and D are produced at 1/16.
 template <typename T, int BITS, bool XPERM, bool FAST>
@@ -266,13 +172,18 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
   const uint32_t w_ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int S = p.w_stages;
   const int TN = p.TN;
-  const uint32_t x_ring = w_ring + S * W_STAGE_BYTES;
+  const uint32_t w_tile_bytes = (uint32_t)p.R * 128u;          // one block of one stage: R rows x 128 packed bytes
+  const uint32_t w_stage_bytes = 2u * w_tile_bytes;
+  const uint32_t x_ring = w_ring + S * w_stage_bytes;
   const uint32_t x_slot_bytes = (uint32_t)(TN * 128);
   const uint32_t x_mask = (uint32_t)(p.x_slots - 1);
   const int x_shift = p.x_slots == 8 ? 3 : 2;
   const uint32_t sb_ring = x_ring + p.x_slots * x_slot_bytes;
   const uint32_t bar_base = sb_ring + NSB * SB_SLOT_BYTES;
-  const int NBUF = TN > 64 ? 1 : 2;              // D buffers: buffer d, block b at columns d*128 + b*64 (TN <= 64) / b*128
+  const int NBUF = p.nbuf;                       // D buffers: buffer d, block b at columns (2d + b) * d_stride
+  const uint32_t d_stride = TN <= 32 ? 32u : (TN <= 64 ? 64u : 128u);
+  const uint32_t A_COL0 = 512u - (uint32_t)p.a_slots * 64u;   // the A ring sits at the top of TMEM
+  const uint32_t a_slots = (uint32_t)p.a_slots;
   auto full_w = [&](int s) { return bar_base + 8u * s; };
   auto empty_w = [&](int s) { return bar_base + 8u * (MAX_STAGES + s); };
   auto full_x = [&](int s) { return bar_base + 8u * (2 * MAX_STAGES + s); };
@@ -284,17 +195,16 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
   auto accum_full = [&](int d) { return bar_base + 8u * (4 * MAX_STAGES + 2 * NSLOT + 2 * NSB + d); };
   auto accum_empty = [&](int d) { return bar_base + 8u * (4 * MAX_STAGES + 2 * NSLOT + 2 * NSB + 2 + d); };
   const uint32_t tmem_slot = bar_base + 8u * (4 * MAX_STAGES + 2 * NSLOT + 2 * NSB + 4);
-  auto d_col = [&](int d, int b) { return (uint32_t)(TN > 64 ? b * 128 : d * 128 + b * 64); };
+  auto d_col = [&](int d, int b) { return (uint32_t)(2 * d + b) * d_stride; };
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int G = (int)gridDim.x, cta = (int)blockIdx.x;
-  const int u_begin = (int)(((long long)p.U * cta) / G), u_end = (int)(((long long)p.U * (cta + 1)) / G);
   const bool silu = p.epi == B200P_EPI_SILU_MUL;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < S; ++s) { mbar_init(full_w(s), 1); mbar_init(empty_w(s), DQ_WARPS); }
     for (int s = 0; s < p.x_slots; ++s) { mbar_init(full_x(s), 1); mbar_init(empty_x(s), 1); }
-    for (int s = 0; s < NSLOT; ++s) { mbar_init(full_a(s), 8); mbar_init(empty_a(s), 1); }
+    for (int s = 0; s < p.a_slots; ++s) { mbar_init(full_a(s), 8); mbar_init(empty_a(s), 1); }
     for (int s = 0; s < NSB; ++s) { mbar_init(sb_full(s), 1); mbar_init(sb_empty(s), DQ_WARPS); }
     for (int d = 0; d < 2; ++d) { mbar_init(accum_full(d), 1); mbar_init(accum_empty(d), EPI_WARPS); }
     fence_barrier_init();
@@ -315,20 +225,23 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     // Weights and scale/bias tiles do not depend on the previous kernel: no griddepcontrol.wait here, so under
     // programmatic dependent launch the HBM stream of this kernel starts while the previous kernel drains.
     int si = 0, ph = 0, sbi = 0, sbph = 0;
-    for (int u = u_begin; u < u_end; ++u) {
-      const int tile = u / p.num_st, st = u % p.num_st;
-      const int pair = tile / p.tiles_m;
-      const int rowA0 = silu ? pair * 128 : pair * 256;
-      const int rowB0 = silu ? p.N / 2 + pair * 128 : pair * 256 + 128;
-      if (p.sb_tma && (u == u_begin || (st % SPG) == 0)) {     // a new group of 8 k-blocks starts with this stage
-        mbar_wait(sb_empty(sbi), sbph ^ 1);
+    TDECL;
+    for (int item = cta; item < p.items; item += G) {
+     const TcSeg sg = seg_of(p, item);
+     const int pair = sg.tile / p.tiles_m;
+     const int rowA0 = silu ? pair * p.R : pair * 2 * p.R;
+     const int rowB0 = silu ? p.N / 2 + pair * p.R : pair * 2 * p.R + p.R;
+     for (int i = 0; i < sg.ns; ++i) {
+      const int st = seg_stage(sg, i);
+      if (p.sb_tma && (i == 0 || st == sg.s0 || (st % SPG) == 0)) {     // a new group of 8 k-blocks starts with this stage
+        TWAIT(1, sb_empty(sbi), sbph ^ 1);
         if (elect_one()) {
           const uint32_t sdst = sb_ring + sbi * SB_SLOT_BYTES;
           const int kb0 = (st / SPG) * 8;
           if (kDebug & 32) {
             mbar_arrive(sb_full(sbi));
           } else {
-            mbar_arrive_expect_tx(sb_full(sbi), (uint32_t)SB_SLOT_BYTES);
+            mbar_arrive_expect_tx(sb_full(sbi), (uint32_t)(4 * p.R * 16));
             tma_load_2d(sdst, &tm_s, kb0, rowA0, sb_full(sbi));
             tma_load_2d(sdst + SB_TILE_BYTES, &tm_b, kb0, rowA0, sb_full(sbi));
             tma_load_2d(sdst + 2 * SB_TILE_BYTES, &tm_s, kb0, rowB0, sb_full(sbi));
@@ -338,27 +251,32 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
         __syncwarp();
         if (++sbi == NSB) { sbi = 0; sbph ^= 1; }
       }
-      mbar_wait(empty_w(si), ph ^ 1);
+      TWAIT(0, empty_w(si), ph ^ 1);
       if (elect_one()) {
-        const uint32_t dst = w_ring + si * W_STAGE_BYTES;
-        mbar_arrive_expect_tx(full_w(si), (uint32_t)W_STAGE_BYTES);
+        const uint32_t dst = w_ring + si * w_stage_bytes;
+        mbar_arrive_expect_tx(full_w(si), w_stage_bytes);
         tma_load_2d(dst, &tm_w, st * 128, rowA0, full_w(si));
-        tma_load_2d(dst + W_TILE_BYTES, &tm_w, st * 128, rowB0, full_w(si));
+        tma_load_2d(dst + w_tile_bytes, &tm_w, st * 128, rowB0, full_w(si));
       }
       __syncwarp();
       if (++si == S) { si = 0; ph ^= 1; }
+     }
     }
+    TFLUSH(0, 2, lane == 0);                         // 0 empty_w, 1 sb_empty, 2 total
   } else if (warp == WARP_X) {
     // ===================================== activation producer ==============================
     pdl_wait();                                      // X is the previous kernel's output
     uint32_t it = 0;
-    for (int u = u_begin; u < u_end; ++u) {
-      const int tile = u / p.num_st, st = u % p.num_st;
-      const int tm = tile % p.tiles_m;
+    TDECL;
+    for (int item = cta; item < p.items; item += G) {
+     const TcSeg sg = seg_of(p, item);
+     const int tm = sg.tile % p.tiles_m;
+     for (int i = 0; i < sg.ns; ++i) {
+      const int st = seg_stage(sg, i);
 #pragma unroll
       for (int jj = 0; jj < KPS; ++jj, ++it) {
         const uint32_t xs = it & x_mask;
-        mbar_wait(empty_x(xs), ((it >> x_shift) & 1u) ^ 1u);
+        TWAIT(0, empty_x(xs), ((it >> x_shift) & 1u) ^ 1u);
         if (elect_one()) {
           if (kDebug & 1) {
             mbar_arrive(full_x(xs));
@@ -369,7 +287,9 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
         }
         __syncwarp();
       }
+     }
     }
+    TFLUSH(3, 1, lane == 0);                         // 3 empty_x, 4 total
   } else if (warp == WARP_MMA) {
     // ===================================== MMA issuer =======================================
     // instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32 (1<<4), a/b format (0 f16, 1 bf16) at
@@ -377,41 +297,38 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     const uint32_t fmt = std::is_same<T, __nv_bfloat16>::value ? 1u : 0u;
     const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(TN >> 3) << 17) | ((128u >> 4) << 24);
     int seg = 0;
-    uint32_t it = 0;
-    for (int u = u_begin; u < u_end; ++seg) {
-      const int s0 = u % p.num_st;
-      const int ns = min(p.num_st - s0, u_end - u);
+    uint32_t slot = 0, aph = 0, xs = 0, xph = 0;
+    TDECL;
+    const uint64_t xdesc0 = make_desc_sw128(x_ring);            // X slot 0, first 16 k; slot s adds s * (slot bytes >> 4)
+    const uint32_t xdesc_step = x_slot_bytes >> 4;
+    const uint32_t a_base = tmem_base + A_COL0;
+    const uint32_t x_slots = (uint32_t)p.x_slots;
+    for (int item = cta; item < p.items; item += G, ++seg) {
+      const int ns = seg_of(p, item).ns;
       const int buf = NBUF == 2 ? (seg & 1) : 0;
       if (seg >= NBUF) {                               // the epilogue of the segment that last used this D buffer has drained it
-        mbar_wait(accum_empty(buf), (uint32_t)(((seg / NBUF) - 1) & 1));
+        TWAIT(2, accum_empty(buf), (uint32_t)(((seg / NBUF) - 1) & 1));
         tc_fence_after();
       }
       const uint32_t d0 = tmem_base + d_col(buf, 0), d1 = tmem_base + d_col(buf, 1);
       const int nkb = ns * KPS;
-      for (int j = 0; j < nkb; ++j, ++it) {
-        const uint32_t slot = it & (NSLOT - 1), xs = it & x_mask;
-        mbar_wait(full_x(xs), (it >> x_shift) & 1u);
-        mbar_wait(full_a(slot), (it >> 2) & 1u);
+      for (int j = 0; j < nkb; ++j) {
+        TWAIT(0, full_x(xs), xph);
+        TWAIT(1, full_a(slot), aph);
         tc_fence_after();
         if (elect_one()) {
-          const uint32_t xsm = x_ring + xs * x_slot_bytes;
           if (!(kDebug & 2))
-#pragma unroll
-          for (int blk = 0; blk < 2; ++blk) {
-#pragma unroll
-            for (int k4 = 0; k4 < 4; ++k4) {
-              const uint32_t at = tmem_base + A_COL0 + slot * 64 + (uint32_t)(blk * 32 + k4 * 8);
-              umma_f16_ts(blk ? d1 : d0, at, make_desc_sw128(xsm + k4 * 32), idesc, (j > 0 || k4 > 0) ? 1u : 0u);
-            }
-          }
+            umma_kblock_f16_ts(d0, d1, a_base + slot * 64, xdesc0 + (uint64_t)(xs * xdesc_step), idesc, j > 0 ? 1u : 0u);
           umma_commit(empty_a(slot));
           umma_commit(empty_x(xs));
           if (j == nkb - 1) umma_commit(accum_full(buf));
         }
         __syncwarp();
+        if (++slot == a_slots) { slot = 0; aph ^= 1u; }
+        if (++xs == x_slots) { xs = 0; xph ^= 1u; }
       }
-      u += ns;
     }
+    TFLUSH(5, 3, lane == 0);                         // 5 full_x, 6 full_a, 7 accum_empty, 8 total
   } else if (warp < DQ_WARPS) {
     // ===================================== dequantisers =====================================
     const int grp = warp >> 2;                         // 0..3
@@ -420,14 +337,18 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     const int r = q * 32 + lane;                     // weight row within the 128-row block
     const uint32_t a_dst = tmem_base + ((uint32_t)(q * 32) << 16) + A_COL0 + (uint32_t)(blk * 32);
     // SWIZZLE_128B tile [128 rows x 128 B]: row r at (r/8)*1024 + (r%8)*128, 16-byte chunk c at (c ^ (r%8))
-    const uint32_t w_row_off = (uint32_t)(blk * W_TILE_BYTES + (r >> 3) * 1024 + (r & 7) * 128);
+    const uint32_t w_row_off = (uint32_t)blk * w_tile_bytes + (uint32_t)((r >> 3) * 1024 + (r & 7) * 128);
+    // rows r >= R of a block carry no weights: a warp with none of them skips the math and the TMEM store (its D rows are
+    // never read) but keeps every barrier protocol; single idle lanes of an active warp compute on stale shared memory
+    const bool warp_active = q * 32 < p.R;
     const uint32_t w_xor = (uint32_t)(r & 7);
     const uint32_t sb_off = (uint32_t)(blk * 2 * SB_TILE_BYTES + r * 16);
     const uint32_t half_sel = kpar ? 0x3232u : 0x1010u;   // which 16-bit half of a scale word is this thread's k-block
 
     int si = 0, ph = 0, sbi = 0, sbph = 0;
-    uint32_t it = (uint32_t)kpar;                    // global k-block counter of this thread (slot = it % 4)
+    uint32_t slot = (uint32_t)kpar, aph = 0;         // A ring slot of this thread's next k-block (it advances by 2) + phase
     uint4 s8 = make_uint4(0u, 0u, 0u, 0u), b8 = s8;
+    TDECL;
 
     constexpr int CPK = PKB / 16;                    // 16-byte chunks of packed codes per k-block
     constexpr int KPT = KPS / 2;                     // k-blocks per thread per stage
@@ -435,8 +356,8 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     // wait for the stage's weights, pull this thread's codes into registers and hand the slot straight back to the
     // producer: the HBM stream then only waits for LDS, not for the dequant math or the MMAs
     auto fetch_stage = [&]() {
-      mbar_wait(full_w(si), (uint32_t)ph);
-      const uint32_t wsrc = w_ring + si * W_STAGE_BYTES + w_row_off;
+      TWAIT(0, full_w(si), (uint32_t)ph);
+      const uint32_t wsrc = w_ring + si * w_stage_bytes + w_row_off;
 #pragma unroll
       for (int j2 = 0; j2 < KPT; ++j2)
 #pragma unroll
@@ -458,8 +379,7 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
 #pragma unroll
         for (int c = 0; c < 8; ++c) dequant8<T, BITS, XPERM>(pw + c * (BITS / 4), s2, b2, o + 4 * c);
       }
-      const uint32_t slot = it & (NSLOT - 1);
-      mbar_wait(empty_a(slot), ((it >> 2) & 1u) ^ 1u);
+      TWAIT(2, empty_a(slot), aph ^ 1u);
       tc_fence_after();
       if (!(kDebug & 8)) {
         tmem_st32(a_dst + slot * 64, o);
@@ -468,16 +388,44 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(full_a(slot));
-      it += 2;
+      slot += 2;
+      if (slot >= a_slots) { slot -= a_slots; aph ^= 1u; }
     };
 
-    for (int u = u_begin; u < u_end;) {
-      const int tile = u / p.num_st, s0 = u % p.num_st;
-      const int ns = min(p.num_st - s0, u_end - u);
-      if (p.sb_tma) {
-        for (int st = s0; st < s0 + ns; ++st) {
-          if (st == s0 || (st % SPG) == 0) {             // next group of 8 k-blocks: scales / biases of this row
+    if (!warp_active) {
+      // barrier protocol only: this warp's 32 rows are beyond the R rows of a block
+      for (int item = cta; item < p.items; item += G) {
+        const TcSeg sg = seg_of(p, item);
+        for (int i = 0; i < sg.ns; ++i) {
+          const int st = seg_stage(sg, i);
+          if (p.sb_tma && (i == 0 || st == sg.s0 || (st % SPG) == 0)) {
             mbar_wait(sb_full(sbi), (uint32_t)sbph);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sb_empty(sbi));
+            if (++sbi == NSB) { sbi = 0; sbph ^= 1; }
+          }
+          mbar_wait(full_w(si), (uint32_t)ph);
+          __syncwarp();
+          if (lane == 0) mbar_arrive(empty_w(si));
+          if (++si == S) { si = 0; ph ^= 1; }
+          for (int j2 = 0; j2 < KPS / 2; ++j2) {
+            mbar_wait(empty_a(slot), aph ^ 1u);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(full_a(slot));
+            slot += 2;
+            if (slot >= a_slots) { slot -= a_slots; aph ^= 1u; }
+          }
+        }
+      }
+    } else
+    for (int item = cta; item < p.items; item += G) {
+      const TcSeg sg = seg_of(p, item);
+      const int tile = sg.tile, s0 = sg.s0, ns = sg.ns;
+      if (p.sb_tma) {
+        for (int i = 0; i < ns; ++i) {
+          const int st = seg_stage(sg, i);
+          if (i == 0 || st == s0 || (st % SPG) == 0) {   // next group of 8 k-blocks: scales / biases of this row
+            TWAIT(1, sb_full(sbi), (uint32_t)sbph);
             const uint32_t src = sb_ring + sbi * SB_SLOT_BYTES + sb_off;
             s8 = lds128(src);
             b8 = lds128(src + SB_TILE_BYTES);
@@ -504,12 +452,13 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
       } else {
         // scale rows are not 16-byte multiples (K % 512 != 0, e.g. a TP shard): read them from global memory
         const int pair = tile / p.tiles_m;
-        const int grow = (blk ? (silu ? p.N / 2 + pair * 128 : pair * 256 + 128) : (silu ? pair * 128 : pair * 256)) + r;
-        const bool row_ok = grow < p.N;
+        const int grow = (blk ? (silu ? p.N / 2 + pair * p.R : pair * 2 * p.R + p.R) : (silu ? pair * p.R : pair * 2 * p.R)) + r;
+        const bool row_ok = grow < p.N && r < p.R;
         const T* sp = reinterpret_cast<const T*>(p.scales) + (int64_t)(row_ok ? grow : 0) * p.num_kb;
         const T* bp = reinterpret_cast<const T*>(p.biases) + (int64_t)(row_ok ? grow : 0) * p.num_kb;
         const T zero = Tr<T>::from_f(0.f);
-        for (int st = s0; st < s0 + ns; ++st) {
+        for (int i = 0; i < ns; ++i) {
+          const int st = seg_stage(sg, i);
           T sv[KPS / 2], bv[KPS / 2];
 #pragma unroll
           for (int j2 = 0; j2 < KPS / 2; ++j2) {
@@ -523,10 +472,11 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
           for (int j2 = 0; j2 < KPS / 2; ++j2) kblock(j2, dup16(sv[j2]), dup16(bv[j2]));
         }
       }
-      u += ns;
     }
+    TFLUSH(9, 3, threadIdx.x == 0);                  // 9 full_w, 10 sb_full, 11 empty_a, 12 total (dequant warp 0)
   } else {
     // ===================================== epilogue warps ===================================
+    TDECL;
     // Thread = one output column n (weight row r of block A and of block B), EPI_TOK tokens per step: every warp-level
     // load / store below touches one contiguous line per token (32 lanes x 4 B, or x 2 B for 16-bit outputs -- whole
     // sectors either way), so nothing is staged through shared memory and no store is atomic.
@@ -539,7 +489,8 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
 
     // fused epilogue of EPI_TOK tokens of this thread's two output columns (a: block A, b: block B)
     auto emit = [&](const float (&a)[EPI_TOK], const float (&b)[EPI_TOK], int rowA0, int rowB0, int tokb) {
-      const int n0 = rowA0 + r, n1 = rowB0 + r;
+      // rows r >= R are not part of this tile (their TMEM lanes hold garbage): pushing n past N disables every store below
+      const int n0 = r < p.R ? rowA0 + r : p.N, n1 = r < p.R ? rowB0 + r : p.N;
       if (p.epi == B200P_EPI_ADD_RESIDUAL) {
         // every element of y is owned by exactly one thread of the launch: plain read-modify-write
         float* y = reinterpret_cast<float*>(p.y);
@@ -593,18 +544,18 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
 
     pdl_wait();                                      // y and the workspace belong to the previous kernels until here
     int seg = 0;
-    int def0 = -1, def1 = -1;                        // split tiles this CTA contributed to (its first / its last segment)
-    for (int u = u_begin; u < u_end; ++seg) {
-      const int tile = u / p.num_st, s0 = u % p.num_st;
-      const int ns = min(p.num_st - s0, u_end - u);
+    int def0 = -1;                                   // the split tile this CTA contributed to (S > 1: one item per CTA)
+    for (int item = cta; item < p.items; item += G, ++seg) {
+      const TcSeg sg = seg_of(p, item);
+      const int tile = sg.tile;
       const int pair = tile / p.tiles_m, tm = tile % p.tiles_m;
-      const int rowA0 = silu ? pair * 128 : pair * 256;
-      const int rowB0 = silu ? p.N / 2 + pair * 128 : pair * 256 + 128;
+      const int rowA0 = silu ? pair * p.R : pair * 2 * p.R;
+      const int rowB0 = silu ? p.N / 2 + pair * p.R : pair * 2 * p.R + p.R;
       const int tok0 = tm * TN;
       const int buf = NBUF == 2 ? (seg & 1) : 0;
-      const bool full = (s0 == 0 && ns == p.num_st);
+      const bool full = p.S == 1;
 
-      mbar_wait(accum_full(buf), (uint32_t)((seg / NBUF) & 1));
+      TWAIT(0, accum_full(buf), (uint32_t)((seg / NBUF) & 1));
       tc_fence_after();
       const uint32_t dA = lane_base + d_col(buf, 0), dB = lane_base + d_col(buf, 1);
       if (!(kDebug & 4)) {
@@ -621,10 +572,8 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
             emit(a, b, rowA0, rowB0, tok0 + t0);
           }
         } else {
-          // partial tile: slot 1 if this CTA owns the tile's first stage (then it is this CTA's LAST segment), else slot 0
-          // (its FIRST segment) -- a CTA never needs the same slot twice
-          const int slot = (s0 == 0) ? 1 : 0;
-          float* part = p.ws_part + ((int64_t)cta * 2 + slot) * slot_elems;
+          // partial tile of a K split: one slot per CTA (the host plans S > 1 only with one item per CTA)
+          float* part = p.ws_part + (int64_t)cta * slot_elems;
           for (int t0 = 0; t0 < TN; t0 += EPI_TOK) {
             float a[EPI_TOK], b[EPI_TOK];
             tmem_ld8(dA + (uint32_t)t0, a);
@@ -636,72 +585,65 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
               __stcg(part + (int64_t)(TN + t0 + j) * 128 + r, b[j] * DSCALE);
             }
           }
-          if (slot) def1 = tile; else def0 = tile;
+          def0 = tile;
         }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(accum_empty(buf));    // this D buffer may be overwritten by a later segment's MMAs
-      u += ns;
     }
 
-    // ---- split tiles: meet the other contributors, then reduce and finish a share of each tile
-    if (def0 >= 0 || def1 >= 0) {
+    TFLUSH(13, 1, et == 0);                          // 13 accum_full, 14 total up to the end of the tile epilogues
+    // ---- split tile: meet the S - 1 other contributors (CTAs tile*S .. tile*S + S - 1: equal work, they arrive together),
+    // then reduce and finish a share of the tile
+    if (def0 >= 0) {
       __threadfence();                                 // this thread's partial stores are performed device-wide ...
       named_bar_sync(1, EPI_THREADS);                  // ... for all 128 epilogue threads before the arrival is published
+      const int tile = def0;
+      const int S = p.S, c_first = tile * S, me = cta - c_first;
       if (et == 0) {
-        if (def0 >= 0) atomicAdd(p.ws_counter + 2 * def0, 1);
-        if (def1 >= 0) atomicAdd(p.ws_counter + 2 * def1, 1);
+        atomicAdd(p.ws_counter + 2 * tile, 1);
+        const volatile int* cnt = p.ws_counter + 2 * tile;
+        unsigned long long t_start;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
+        while (*cnt < S) {
+          __nanosleep(20);
+          unsigned long long t_now;
+          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_now));
+          if (t_now - t_start > 4000000000ull) __trap();      // a contributor never arrived: fail loudly, do not hang
+        }
+        __threadfence();
       }
-      for (int i = 0; i < 2; ++i) {
-        const int tile = i ? def1 : def0;
-        if (tile < 0) continue;
-        const int c_first = owner_of(tile * p.num_st, p.U, G);
-        const int c_last = owner_of(tile * p.num_st + p.num_st - 1, p.U, G);
-        const int S = c_last - c_first + 1, me = cta - c_first;
-        if (et == 0) {
-          const volatile int* cnt = p.ws_counter + 2 * tile;
-          unsigned long long t_start;
-          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
-          while (*cnt < S) {
-            __nanosleep(40);
-            unsigned long long t_now;
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_now));
-            if (t_now - t_start > 4000000000ull) __trap();      // a contributor never arrived: fail loudly, do not hang
-          }
-          __threadfence();
-        }
-        named_bar_sync(2, EPI_THREADS);
-        const int pair = tile / p.tiles_m, tm = tile % p.tiles_m;
-        const int rowA0 = silu ? pair * 128 : pair * 256;
-        const int rowB0 = silu ? p.N / 2 + pair * 128 : pair * 256 + 128;
-        const int tok0 = tm * TN;
-        for (int t0 = me * EPI_TOK; t0 < TN; t0 += S * EPI_TOK) {
-          if (tok0 + t0 >= p.M_tok) break;             // padding tokens of the last token tile
-          float a[EPI_TOK], b[EPI_TOK];
+      named_bar_sync(2, EPI_THREADS);
+      const int pair = tile / p.tiles_m, tm = tile % p.tiles_m;
+      const int rowA0 = silu ? pair * p.R : pair * 2 * p.R;
+      const int rowB0 = silu ? p.N / 2 + pair * p.R : pair * 2 * p.R + p.R;
+      const int tok0 = tm * TN;
+      for (int t0 = me * EPI_TOK; t0 < TN; t0 += S * EPI_TOK) {
+        if (tok0 + t0 >= p.M_tok) break;               // padding tokens of the last token tile
+        float a[EPI_TOK], b[EPI_TOK];
 #pragma unroll
-          for (int j = 0; j < EPI_TOK; ++j) a[j] = b[j] = 0.f;
+        for (int j = 0; j < EPI_TOK; ++j) a[j] = b[j] = 0.f;
 #pragma unroll 2
-          for (int c = c_first; c <= c_last; ++c) {     // fixed order: bit-reproducible sums
-            const float* part = p.ws_part + ((int64_t)c * 2 + (c == c_first ? 1 : 0)) * slot_elems;
-            float va[EPI_TOK], vb[EPI_TOK];
+        for (int c = c_first; c < c_first + S; ++c) {   // fixed order: bit-reproducible sums
+          const float* part = p.ws_part + (int64_t)c * slot_elems;
+          float va[EPI_TOK], vb[EPI_TOK];
 #pragma unroll
-            for (int j = 0; j < EPI_TOK; ++j) {         // 16 independent L2 loads in flight
-              va[j] = __ldcg(part + (int64_t)(t0 + j) * 128 + r);
-              vb[j] = __ldcg(part + (int64_t)(TN + t0 + j) * 128 + r);
-            }
-#pragma unroll
-            for (int j = 0; j < EPI_TOK; ++j) { a[j] += va[j]; b[j] += vb[j]; }
+          for (int j = 0; j < EPI_TOK; ++j) {           // 16 independent L2 loads in flight
+            va[j] = __ldcg(part + (int64_t)(t0 + j) * 128 + r);
+            vb[j] = __ldcg(part + (int64_t)(TN + t0 + j) * 128 + r);
           }
-          emit(a, b, rowA0, rowB0, tok0 + t0);
+#pragma unroll
+          for (int j = 0; j < EPI_TOK; ++j) { a[j] += va[j]; b[j] += vb[j]; }
         }
-        // the last contributor to finish re-arms the tile's counters for the next launch (all S have passed the wait)
-        if (et == 0) {
-          const int old = atomicAdd(p.ws_counter + 2 * tile + 1, 1);
-          if (old == S - 1) {
-            p.ws_counter[2 * tile] = 0;
-            p.ws_counter[2 * tile + 1] = 0;
-          }
+        emit(a, b, rowA0, rowB0, tok0 + t0);
+      }
+      // the last contributor to finish re-arms the tile's counters for the next launch (all S have passed the wait)
+      if (et == 0) {
+        const int old = atomicAdd(p.ws_counter + 2 * tile + 1, 1);
+        if (old == S - 1) {
+          p.ws_counter[2 * tile] = 0;
+          p.ws_counter[2 * tile + 1] = 0;
         }
       }
     }
@@ -715,17 +657,13 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
 }
 
 // ------------------------------------------------------------------------------------------------ host
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn get_encode() {
-  static EncodeTiledFn fn = nullptr;
+TcEncodeFn tc_get_encode() {
+  static TcEncodeFn fn = nullptr;
   if (!fn) {
     void* p = nullptr;
     cudaDriverEntryPointQueryResult q;
     if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-      fn = (EncodeTiledFn)p;
+      fn = (TcEncodeFn)p;
   }
   return fn;
 }
@@ -739,32 +677,76 @@ static_assert(8 * (4 * MAX_STAGES + 2 * NSLOT + 2 * NSB + 4) + 8 <= 512, "barrie
 // B200P_MIN_TC_M / b200p_qmm_set_min_tensor_m override it.
 static int g_min_tc_m = [] { const char* e = getenv("B200P_MIN_TC_M"); return e ? atoi(e) : 1; }();
 void qmm_tc_set_min_m(int m) { g_min_tc_m = m < 1 ? 1 : m; }
-constexpr int MIN_UNITS_PER_CTA = 2;
-
+// A launch is cut into work items (output tile, K split).  An output tile is a PAIR of row blocks of R <= 128 weight rows
+// each (for SILU_MUL: R gate rows and the matching R up rows) times one token tile; R is chosen per matrix so that the tiles
+// fill the SMs evenly with WHOLE tiles wherever the matrix has enough rows (gate|up of Llama-3-8B: R = 104 -> 138 tiles on
+// 148 SMs; lm_head: R = 88 -> 5 tiles per SM) -- no partial tiles, the fused epilogue goes straight from TMEM to global
+// memory.  Only matrices with too few rows for that (o_proj, down_proj, q|k|v at decode) split K S ways, S * tiles <= #SMs,
+// and sum the S partial tiles through the workspace (kernel tail).
 struct TcPlan {
-  int TN, tiles_m, pairs, grid, w_stages, x_slots, smem_bytes;
-  long long U;
+  int TN, tiles_m, pairs, R, S, items, grid, w_stages, x_slots, smem_bytes, nbuf, a_slots;
 };
+
+static int env_int(const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; }
+static const int g_force_R = env_int("B200P_TC_R", 0);       // experiments: force the plan
+static const int g_force_S = env_int("B200P_TC_S", 0);
+static const int g_rotate = env_int("B200P_TC_ROT", 1);
+static const int g_force_nbuf = env_int("B200P_TC_NBUF", 0);
 
 static TcPlan make_plan(int64_t M, int64_t N, int64_t K, int bits, int epi) {
   TcPlan pl;
   const int tn = (int)(M >= MAX_TN ? MAX_TN : ((M + 15) / 16) * 16);
   pl.TN = tn;
   pl.tiles_m = (int)((M + tn - 1) / tn);
-  pl.pairs = (int)(epi == B200P_EPI_SILU_MUL ? (N / 2 + 127) / 128 : (N + 255) / 256);
   const int kps = bits == 4 ? 4 : 2;                       // k-blocks per 128-byte stage row
   const int num_st = (int)((K / 64 + kps - 1) / kps);
-  pl.U = (long long)pl.pairs * pl.tiles_m * num_st;     // qmm_tc_supported bounds it to 32-bit unit arithmetic
-  long long g = (pl.U + MIN_UNITS_PER_CTA - 1) / MIN_UNITS_PER_CTA;
   const int sms = sm_count();
-  pl.grid = (int)(g > sms ? sms : (g < 1 ? 1 : g));
+  const bool silu = epi == B200P_EPI_SILU_MUL;
+  const int64_t rows = silu ? N / 2 : N;                   // rows to deal out (silu: gate rows; each brings its up row)
+  // cost model in units of (weight rows x stages) streamed by the busiest CTA.  A stage never costs less than ~96 rows'
+  // worth of time (the dequant -> tcgen05.st -> MMA chain of one k-block is latency-bound below that), lanes of a
+  // partly filled warp still cost issue slots, and a K split pays for writing + re-reading its fp32 partial tile.
+  double best = 1e30;
+  pl.R = 128; pl.S = 1;
+  for (int R = 8; R <= 128; R += 8) {
+    if (g_force_R && R != g_force_R) continue;
+    const int64_t pairs = silu ? (rows + R - 1) / R : (rows + 2 * R - 1) / (2 * R);
+    const int64_t tiles = pairs * pl.tiles_m;
+    const int max_s = tiles <= sms ? (int)(sms / tiles) : 1;
+    for (int S = 1; S <= max_s && S <= num_st && S <= 16; ++S) {
+      if (g_force_S && S != g_force_S) continue;
+      const int64_t items = tiles * S;
+      const int64_t per_cta = (items + sms - 1) / sms;
+      const int st_max = (num_st + S - 1) / S;
+      const int r32 = ((R + 31) / 32) * 32;
+      double row_cost = 0.5 * (2 * R) + 0.5 * (2 * r32);
+      if (row_cost < 192.0) row_cost = 192.0;
+      double cost = (double)per_cta * st_max * row_cost;
+      if (S > 1) cost += 16.0 * tn + 256.0;
+      cost += 64.0 * per_cta;                              // per-tile epilogue
+      if (cost < best) { best = cost; pl.R = R; pl.S = S; }
+    }
+  }
+  const int64_t pairs = silu ? (rows + pl.R - 1) / pl.R : (rows + 2 * pl.R - 1) / (2 * pl.R);
+  pl.pairs = (int)pairs;
+  const int64_t items = pairs * pl.tiles_m * pl.S;
+  pl.items = (int)items;
+  pl.grid = (int)(items > sms ? sms : (items < 1 ? 1 : items));
+  // TMEM: D buffers first, the A ring takes the rest.  A second D buffer only pays when a CTA runs several items
+  // (the epilogue of one overlaps the main loop of the next); with one item per CTA the columns deepen the A ring.
+  const int d_stride = tn <= 32 ? 32 : (tn <= 64 ? 64 : 128);
+  pl.nbuf = (tn > 64 || items <= sms) ? 1 : 2;
+  if (g_force_nbuf && tn <= 64) pl.nbuf = g_force_nbuf;
+  pl.a_slots = ((512 - pl.nbuf * 2 * d_stride) / 64) & ~1;
+  if (pl.a_slots > NSLOT) pl.a_slots = NSLOT;
   // X ring: one [TN x 64] tile per k-block, 8 slots (4 at TN = 128) -- about 1 us of MMA work in flight, enough to
   // cover the L2 latency of the tile loads; the weight ring gets the rest of shared memory
   pl.x_slots = tn * 128 * 8 <= X_RING_BYTES ? 8 : 4;
-  int st = (SMEM_BUDGET - SMEM_FIXED - pl.x_slots * tn * 128) / W_STAGE_BYTES;
+  const int stage_bytes = 2 * pl.R * 128;
+  int st = (SMEM_BUDGET - SMEM_FIXED - pl.x_slots * tn * 128) / stage_bytes;
   if (st > MAX_STAGES) st = MAX_STAGES;
   pl.w_stages = st;
-  pl.smem_bytes = SMEM_FIXED + pl.x_slots * tn * 128 + st * W_STAGE_BYTES;
+  pl.smem_bytes = SMEM_FIXED + pl.x_slots * tn * 128 + st * stage_bytes;
   return pl;
 }
 
@@ -780,19 +762,16 @@ bool qmm_tc_supported(int64_t M, int64_t N, int64_t K, int gs, int bits, int dty
   return true;
 }
 
-static size_t ws_counter_bytes(int64_t M, int64_t N) {
-  const int64_t tn = M >= MAX_TN ? MAX_TN : ((M + 15) / 16) * 16;
-  const int64_t tiles_m = (M + tn - 1) / tn;
-  return ((size_t)(tiles_m * ((N + 255) / 256 + 1)) * 2 * sizeof(int) + 255) & ~(size_t)255;   // {arrived, done} per tile
-}
+// {arrived, done} per split tile: K splits are planned only when tiles * S <= #SMs, so there are never more than #SMs of them
+static size_t ws_counter_bytes(int64_t, int64_t) { return 4096; }
 
 size_t qmm_tc_workspace_bytes(int64_t M, int64_t N, int64_t K) {
   (void)K;
   if (M < 1) return 0;
   const int64_t tn = M >= MAX_TN ? MAX_TN : ((M + 15) / 16) * 16;
-  // per-tile counters (ZERO on first use; the kernel leaves them zero) + two fp32 [2*TN x 128] partial-tile slots per CTA
-  // (a CTA's first and last segment; no initial state)
-  return ws_counter_bytes(M, N) + (size_t)sm_count() * 2 * 2 * tn * 128 * sizeof(float);
+  // per-tile counters (ZERO on first use; the kernel leaves them zero) + one fp32 [2*TN x 128] partial-tile slot per CTA
+  // (no initial state)
+  return ws_counter_bytes(M, N) + (size_t)sm_count() * 2 * tn * 128 * sizeof(float);
 }
 
 template <typename T, int BITS, bool XPERM, bool FAST>
@@ -819,8 +798,46 @@ static int launch_tc(const CUtensorMap* tms, const TcParams& p, const TcPlan& pl
   return B200P_OK;
 }
 
-static int encode_2d(EncodeTiledFn enc, CUtensorMap* tm, CUtensorMapDataType dt, const void* base, uint64_t d0, uint64_t d1,
+// Tensor maps are pure functions of (base, dims, stride, box, type, swizzle): encode each distinct one once per process
+// (a decode step replays a graph and never gets here; an eager prefill GEMM used to pay four driver calls per launch).
+struct TmKey {
+  const void* base; uint64_t d0, d1, stride; uint32_t b0, b1; int dt, sw;
+  bool operator==(const TmKey& o) const {
+    return base == o.base && d0 == o.d0 && d1 == o.d1 && stride == o.stride && b0 == o.b0 && b1 == o.b1 && dt == o.dt && sw == o.sw;
+  }
+};
+struct TmKeyHash {
+  size_t operator()(const TmKey& k) const {
+    uint64_t h = (uint64_t)(uintptr_t)k.base * 0x9E3779B97F4A7C15ull;
+    for (uint64_t v : {k.d0, k.d1, k.stride, (uint64_t)k.b0, (uint64_t)k.b1, (uint64_t)k.dt, (uint64_t)k.sw})
+      h = (h ^ v) * 0x100000001B3ull + (h >> 29);
+    return (size_t)h;
+  }
+};
+static std::mutex g_tm_mutex;
+static std::unordered_map<TmKey, CUtensorMap, TmKeyHash> g_tm_cache;
+
+static int encode_2d_raw(TcEncodeFn enc, CUtensorMap* tm, CUtensorMapDataType dt, const void* base, uint64_t d0, uint64_t d1,
+                         uint64_t stride_bytes, uint32_t b0, uint32_t b1, CUtensorMapSwizzle sw, const char* what);
+
+int tc_encode_2d(TcEncodeFn enc, CUtensorMap* tm, CUtensorMapDataType dt, const void* base, uint64_t d0, uint64_t d1,
                      uint64_t stride_bytes, uint32_t b0, uint32_t b1, CUtensorMapSwizzle sw, const char* what) {
+  const TmKey key{base, d0, d1, stride_bytes, b0, b1, (int)dt, (int)sw};
+  {
+    std::lock_guard<std::mutex> lk(g_tm_mutex);
+    auto it = g_tm_cache.find(key);
+    if (it != g_tm_cache.end()) { *tm = it->second; return B200P_OK; }
+  }
+  const int rc = encode_2d_raw(enc, tm, dt, base, d0, d1, stride_bytes, b0, b1, sw, what);
+  if (rc) return rc;
+  std::lock_guard<std::mutex> lk(g_tm_mutex);
+  if (g_tm_cache.size() > 8192) g_tm_cache.clear();
+  g_tm_cache.emplace(key, *tm);
+  return B200P_OK;
+}
+
+static int encode_2d_raw(TcEncodeFn enc, CUtensorMap* tm, CUtensorMapDataType dt, const void* base, uint64_t d0, uint64_t d1,
+                         uint64_t stride_bytes, uint32_t b0, uint32_t b1, CUtensorMapSwizzle sw, const char* what) {
   cuuint64_t dims[2] = {(cuuint64_t)d0, (cuuint64_t)d1};
   cuuint64_t strides[1] = {(cuuint64_t)stride_bytes};
   cuuint32_t box[2] = {b0, b1};
@@ -834,7 +851,7 @@ static int encode_2d(EncodeTiledFn enc, CUtensorMap* tm, CUtensorMapDataType dt,
 int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b, void* y, int64_t M, int64_t N,
                   int64_t K, int64_t ldx, int64_t ldy, int bits, int dtype, int epi, int flags, void* ws, size_t ws_bytes,
                   cudaStream_t st) {
-  EncodeTiledFn enc = get_encode();
+  TcEncodeFn enc = tc_get_encode();
   B200P_REQUIRE(enc != nullptr, B200P_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
   TcPlan pl = make_plan(M, N, K, bits, epi);
   B200P_REQUIRE(pl.w_stages >= 2, B200P_ERR_ARG, "shared memory too small for the tensor path");
@@ -847,17 +864,17 @@ int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b
   const CUtensorMapDataType dt16 = dtype == B200P_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   const bool fast = (flags & B200P_W_SMALLSCALE) != 0 && dtype == B200P_F16;
   CUtensorMap tms[4];
-  int rc = encode_2d(enc, &tms[0], CU_TENSOR_MAP_DATA_TYPE_UINT8, w, (uint64_t)(K * bits / 8), (uint64_t)N,
-                     (uint64_t)(K * bits / 8), 128u, 128u, CU_TENSOR_MAP_SWIZZLE_128B, "weights");
+  int rc = tc_encode_2d(enc, &tms[0], CU_TENSOR_MAP_DATA_TYPE_UINT8, w, (uint64_t)(K * bits / 8), (uint64_t)N,
+                     (uint64_t)(K * bits / 8), 128u, (uint32_t)pl.R, CU_TENSOR_MAP_SWIZZLE_128B, "weights");
   if (rc) return rc;
-  rc = encode_2d(enc, &tms[1], dt16, x, (uint64_t)K, (uint64_t)M, (uint64_t)(ldx * 2), 64u, (uint32_t)pl.TN,
+  rc = tc_encode_2d(enc, &tms[1], dt16, x, (uint64_t)K, (uint64_t)M, (uint64_t)(ldx * 2), 64u, (uint32_t)pl.TN,
                  CU_TENSOR_MAP_SWIZZLE_128B, "x");
   if (rc) return rc;
   if (sb_tma) {
-    rc = encode_2d(enc, &tms[2], dt16, s, (uint64_t)num_kb, (uint64_t)N, (uint64_t)num_kb * 2, 8u, 128u,
+    rc = tc_encode_2d(enc, &tms[2], dt16, s, (uint64_t)num_kb, (uint64_t)N, (uint64_t)num_kb * 2, 8u, (uint32_t)pl.R,
                    CU_TENSOR_MAP_SWIZZLE_NONE, "scales");
     if (rc) return rc;
-    rc = encode_2d(enc, &tms[3], dt16, b, (uint64_t)num_kb, (uint64_t)N, (uint64_t)num_kb * 2, 8u, 128u,
+    rc = tc_encode_2d(enc, &tms[3], dt16, b, (uint64_t)num_kb, (uint64_t)N, (uint64_t)num_kb * 2, 8u, (uint32_t)pl.R,
                    CU_TENSOR_MAP_SWIZZLE_NONE, "biases");
     if (rc) return rc;
   } else {
@@ -867,7 +884,7 @@ int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b
   TcParams p;
   p.scales = s; p.biases = b; p.y = y;
   const size_t counters = ws_counter_bytes(M, N);
-  const size_t need = counters + (size_t)pl.grid * 2 * 2 * pl.TN * 128 * sizeof(float);
+  const size_t need = counters + (pl.S > 1 ? (size_t)pl.grid * 2 * pl.TN * 128 * sizeof(float) : 0);
   B200P_REQUIRE(ws_bytes >= need && aligned(ws, 16), B200P_ERR_ARG, "qmm workspace too small (%zu < %zu)", ws_bytes, need);
   {
     const bool f32out = epi == B200P_EPI_STORE_F32 || epi == B200P_EPI_ADD_RESIDUAL;
@@ -877,8 +894,8 @@ int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b
   p.ws_counter = reinterpret_cast<int*>(ws);
   p.ws_part = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + counters);
   p.M_tok = (int)M; p.N = (int)N; p.K = (int)K; p.TN = pl.TN; p.ldy = ldy; p.epi = epi; p.y_perm = y_perm ? 1 : 0;
-  B200P_REQUIRE(pl.U * (pl.grid + 1) < (1ll << 31), B200P_ERR_ARG, "problem too large for the tensor path (%lld units)", pl.U);
-  p.num_kb = num_kb; p.pairs = pl.pairs; p.tiles_m = pl.tiles_m; p.U = (int)pl.U;
+  B200P_REQUIRE((int64_t)pl.pairs * pl.tiles_m * pl.S < (1ll << 30), B200P_ERR_ARG, "problem too large for the tensor path");
+  p.num_kb = num_kb; p.pairs = pl.pairs; p.tiles_m = pl.tiles_m; p.R = pl.R; p.S = pl.S; p.items = pl.items; p.rotate = g_rotate; p.nbuf = pl.nbuf; p.a_slots = pl.a_slots;
   p.num_st = (p.num_kb + (bits == 4 ? 4 : 2) - 1) / (bits == 4 ? 4 : 2);
   p.sb_tma = sb_tma ? 1 : 0;
   p.w_stages = pl.w_stages; p.x_slots = pl.x_slots;
@@ -893,3 +910,9 @@ int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b
 }
 
 }  // namespace b200p
+
+#if B200P_TC_TIMING
+extern "C" int b200p_debug_tc_timing(unsigned long long* out32) {
+  return cudaMemcpyFromSymbol(out32, b200p::g_tc_timing, sizeof(unsigned long long) * 32) == cudaSuccess ? 0 : -1;
+}
+#endif

@@ -32,6 +32,11 @@ from .._lib import EPI_ADD_RESIDUAL, EPI_SILU_MUL, EPI_STORE, EPI_STORE_F32
 from .base import BatchedKVCache, PagedKVCache
 
 MAX_TOKENS_PER_FORWARD = 8192     # chunk size (B*L) of one prefill pass through the layers
+# Up to this many rows the fused q|k|v projection accumulates in an fp32 buffer through the stream-K kernel (csrc/qmm_sk.cu:
+# partial tiles summed by TMA reduce-adds, no tail; rope_kv_append rounds to the storage type and re-zeroes the buffer).
+# q|k|v has 24 output tiles for 148 SMs, so it must split K; measured at 64 rows (profiles/r2_run11_*): 16.8 us through the
+# whole-tile kernel's workspace split against 8-10 us this way.  Above it (prefill) whole 16-bit tiles are stored directly.
+ACC32_MAX_ROWS = 128
 USE_PERM8 = True                  # 4-bit 16-bit models: GEMM inputs in the PERM8 column order (include/b200p.h)
 # |scale| bound under which an f16 matrix may take the subnormal-operand dequant (B200P_W_SMALLSCALE, csrc/dequant.cuh):
 # the kernel needs s * 2^20 finite in half precision, i.e. |s| < 0.0625; checked once per matrix at load time.
@@ -322,7 +327,9 @@ class DecoderModel:
 
     # -- scratch ---------------------------------------------------------------------------------
     def _arena(self, M: int, B: int) -> dict:
-        key = (M, B)
+        # keyed by the launching stream as well: callers on different streams (threads that set their own) must not share
+        # scratch; callers on ONE stream are serialised by self._lock (launch order == execution order)
+        key = (M, B, torch.cuda.current_stream(self.device).cuda_stream)
         a = self._arenas.get(key)
         if a is None:
             dev, dt, args = self.device, self.dtype, self.args
@@ -339,6 +346,8 @@ class DecoderModel:
                 h=torch.empty((M, args.hidden_size), dtype=torch.float32, device=dev),
                 x=torch.empty((M, args.hidden_size), dtype=dt, device=dev),
                 qkv=torch.empty((M, nqkv), dtype=dt, device=dev),
+                # zero once: the consumer kernel (rope_kv_append) re-zeroes it behind its reads
+                qkv32=torch.zeros((M, nqkv), dtype=torch.float32, device=dev) if self._fast16 and M <= ACC32_MAX_ROWS else None,
                 q=torch.empty((M, att.n_heads * att.head_dim), dtype=dt, device=dev),
                 att=torch.empty((M, att.n_heads * att.head_dim), dtype=dt, device=dev),
                 act=torch.empty((M, inter_local), dtype=dt, device=dev),
@@ -362,8 +371,9 @@ class DecoderModel:
         self.model.embed_tokens.embed(ids_i32, out=a["h"])
         tp = self.tp_world > 1
         # 16-bit models with 4-bit weights: GEMM inputs travel in the PERM8 column order the tensor path unpacks nibbles
-        # in.  q|k|v leaves its GEMM in the storage type (what nn.QuantizedLinear returns, llama.py:93) and gate|up as
-        # silu(gate)*up: split-K tiles are reduced inside the GEMM kernel, there is no fp32 side buffer.
+        # in.  gate|up leaves its GEMM as silu(gate)*up in the storage type (whole output tiles per SM, fused epilogue);
+        # q|k|v accumulates in fp32 at decode sizes (ACC32_MAX_ROWS) and is rounded by rope_kv_append -- one rounding of
+        # the fp32 sum either way, which is what nn.QuantizedLinear returns (llama.py:93).
         pm = self._perm8
         fx = getattr(self, "_tp_fused", None) if tp else None      # peer-memory exchange (tp.PeerExchange) or NCCL
         layers = self.model.layers
@@ -375,12 +385,14 @@ class DecoderModel:
             lengths = c.lengths(self.device)
             if fx is None or li == 0:      # with the fused exchange the previous layer's down_proj exchange wrote x
                 ops.rmsnorm(a["h"], layer.input_layernorm.weight, layer.input_layernorm.eps, out=a["x"], out_perm=pm)
-            at.qkv_proj(a["x"], EPI_STORE, out=a["qkv"], workspace=a["ws"], x_perm=pm)
+            qkv_buf = a["qkv32"] if a["qkv32"] is not None else a["qkv"]
+            at.qkv_proj(a["x"], EPI_ADD_RESIDUAL if qkv_buf.dtype == torch.float32 else EPI_STORE, out=qkv_buf,
+                        workspace=a["ws"], x_perm=pm)
             if at.lora:                    # LoRA on q_proj / v_proj (A.9): low-rank update of the q / v column blocks
                 for name, (At, Bt, scale) in at.lora.items():
                     col0 = 0 if name == "q_proj" else (at.n_heads + at.n_kv_heads) * at.head_dim
-                    ops.lora_add(a["x"], At, Bt, a["qkv"], col0, scale)
-            ops.rope_kv_append(a["qkv"], a["q"], c.keys, c.values, lengths, B, L, at.n_heads,
+                    ops.lora_add(a["x"], At, Bt, qkv_buf, col0, scale)
+            ops.rope_kv_append(qkv_buf, a["q"], c.keys, c.values, lengths, B, L, at.n_heads,
                                at.n_kv_heads, at.head_dim, args.rope_theta, self.rope_scale,
                                at.q_norm.weight if at.q_norm else None, at.k_norm.weight if at.k_norm else None,
                                args.rms_norm_eps)

@@ -112,6 +112,11 @@ class BatchedKVCache:
             return False
         n_steps = (needed + self.step - 1) // self.step
         new_cap = n_steps * self.step
+        if cap > 0 and self.keys is not None and self.keys.dtype == dtype:
+            # growing a live cache: at least 1.5x, so a long generation re-copies its KV (and re-captures its decode graph)
+            # O(log T) times instead of every ``step`` tokens (the reference concatenates a step-sized block each time,
+            # base.py:104-117).  Only ONE layer's old + new buffers are alive at a time.
+            new_cap = max(new_cap, ((cap * 3 // 2 + self.step - 1) // self.step) * self.step)
         shape = (self.batch_size, self.n_kv_heads, new_cap, self.head_dim)
         nk = torch.zeros(shape, dtype=dtype, device=device)
         nv = torch.zeros(shape, dtype=dtype, device=device)

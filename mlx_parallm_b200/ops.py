@@ -8,6 +8,8 @@ from __future__ import annotations
 
 from typing import Optional
 
+import os
+
 import torch
 
 from . import _lib
@@ -101,6 +103,9 @@ def qmm_workspace_bytes(M, N, K) -> int:
     return int(lib().b200p_qmm_workspace_bytes(M, N, K))
 
 
+_SMALLSCALE_OK = os.environ.get("B200P_NO_SMALLSCALE", "0") != "1"      # A/B switch for the subnormal-operand dequant
+
+
 def qmm(x, w, scales, biases, group_size=64, bits=4, epilogue=EPI_STORE, out=None, workspace=None,
         x_perm=False, y_perm=False, small_scale=False):
     """quantized_matmul(x, w, scales, biases, transpose=True) with a fused epilogue.
@@ -126,7 +131,7 @@ def qmm(x, w, scales, biases, group_size=64, bits=4, epilogue=EPI_STORE, out=Non
         else:
             raise ValueError("EPI_ADD_RESIDUAL needs the residual tensor as `out`")
     epi_flags = (epilogue | (_lib.X_PERM8 if x_perm else 0) | (_lib.Y_PERM8 if y_perm else 0)
-                 | (_lib.W_SMALLSCALE if small_scale else 0))
+                 | (_lib.W_SMALLSCALE if (small_scale and _SMALLSCALE_OK) else 0))
     ws_ptr, ws_bytes = (0, 0) if workspace is None else (workspace.data_ptr(), workspace.numel() * workspace.element_size())
     _call(("b200p_qmm", N, K), lambda: lib().b200p_qmm(_p(x), _p(w), _p(scales), _p(biases), _p(out), M, N, K, x.stride(0), out.stride(0),
                           group_size, bits, dtype_code(x.dtype), epi_flags, ws_ptr, ws_bytes, _stream()))

@@ -23,6 +23,7 @@ import json
 import logging
 import threading
 import time
+from collections import OrderedDict
 from pathlib import Path
 from typing import Any, Callable, Dict, Generator, List, Optional, Tuple, Union
 
@@ -64,6 +65,63 @@ def get_model_path(path_or_hf_repo: str, revision: Optional[str] = None) -> Path
     return p
 
 
+# --------------------------------------------------------------------------------- tokenisation / chat-template caches
+class _LRUCache:
+    """utils.py:137-156: the small LRU behind encode_cached / apply_chat_template_cached (pure host code, no MLX)."""
+
+    def __init__(self, max_size: int = 2048):
+        self.max_size = max_size
+        self._store: "OrderedDict[str, Any]" = OrderedDict()
+        self._mu = threading.Lock()            # the server calls these from the event loop and from executor threads
+
+    def get(self, key: str):
+        with self._mu:
+            if key in self._store:
+                self._store.move_to_end(key)
+                return self._store[key]
+            return None
+
+    def set(self, key: str, value: Any):
+        with self._mu:
+            self._store[key] = value
+            self._store.move_to_end(key)
+            if len(self._store) > self.max_size:
+                self._store.popitem(last=False)
+
+
+_encode_lru = _LRUCache(max_size=4096)
+_chat_template_lru = _LRUCache(max_size=2048)
+
+
+def encode_cached(tokenizer: TokenizerWrapper, text: str) -> List[int]:
+    """utils.py:158-172: LRU-cached ``tokenizer.encode`` for single-string prompts, keyed by tokenizer identity + text."""
+    key = f"tok:{id(tokenizer._tokenizer)}:{text}"
+    val = _encode_lru.get(key)
+    if val is not None:
+        return val
+    enc = tokenizer.encode(text)
+    _encode_lru.set(key, enc)
+    return enc
+
+
+def _messages_cache_key(messages: List[Dict[str, Any]]) -> str:
+    """utils.py:174-178: canonical JSON of (role, content) only."""
+    minimal = [{"role": m.get("role"), "content": m.get("content")} for m in messages]
+    return json.dumps(minimal, sort_keys=True, separators=(",", ":"))
+
+
+def apply_chat_template_cached(tokenizer: TokenizerWrapper, messages: List[Dict[str, Any]], *,
+                               add_generation_prompt: bool = True) -> str:
+    """utils.py:180-197 (imported by server/main.py:33): LRU-cached chat templating."""
+    key = f"cht:{id(tokenizer._tokenizer)}:{'1' if add_generation_prompt else '0'}:{_messages_cache_key(messages)}"
+    val = _chat_template_lru.get(key)
+    if val is not None:
+        return val
+    text = tokenizer.apply_chat_template(messages, tokenize=False, add_generation_prompt=add_generation_prompt)
+    _chat_template_lru.set(key, text)
+    return text
+
+
 # --------------------------------------------------------------------------------- KV pool
 class _KVPool:
     """utils.py:199-223.  Keyed additionally by model identity and thread so two generations never share
@@ -71,24 +129,36 @@ class _KVPool:
 
     def __init__(self):
         self._pool: Dict[tuple, List[BatchedKVCache]] = {}
+        self._mu = threading.Lock()
 
     def get(self, head_dim: int, kv_heads: List[int], batch_size: int, *, step: Optional[int] = None,
             paged: bool = True, device=None, owner: int = 0) -> List[BatchedKVCache]:
+        """``step`` sizes the FIRST allocation of a new entry and the growth quantum of a reused one; a reused entry keeps
+        its (possibly larger) buffers, so the decode graph captured over them stays valid across calls."""
         key = (head_dim, tuple(kv_heads), batch_size, owner, threading.get_ident())
-        caches = self._pool.get(key)
-        if caches is None:
-            klass = PagedKVCache if paged else BatchedKVCache
-            caches = [klass(head_dim, n, batch_size) for n in kv_heads]
-            bind_cache_group(caches, device, step)
-            if len(self._pool) > 16:
-                self._pool.clear()
-            self._pool[key] = caches
-        else:
-            for c in caches:
-                c.reset(batch_size)
-                if step is not None:
-                    c.step = step
+        with self._mu:
+            caches = self._pool.get(key)
+            if caches is None:
+                klass = PagedKVCache if paged else BatchedKVCache
+                caches = [klass(head_dim, n, batch_size) for n in kv_heads]
+                bind_cache_group(caches, device, step)
+                if len(self._pool) > 16:
+                    self._pool.clear()
+                self._pool[key] = caches
+                return caches
+        for c in caches:
+            c.reset(batch_size)
+            if step is not None:
+                c.step = step
         return caches
+
+
+def _presized_cache(model: DecoderModel, B: int, total_tokens: int) -> List[BatchedKVCache]:
+    """Pool entry whose buffers take ``total_tokens`` per row in ONE allocation (rounded to 256 like utils.py:1234), so a
+    generation of known length never re-allocates or copies its KV cache and its decode graph is captured once."""
+    step = max(256, ((int(total_tokens) + 255) // 256) * 256)
+    kv_heads = [l.self_attn.n_kv_heads for l in model.layers]
+    return _kv_pool.get(model.head_dim, kv_heads, B, step=step, paged=True, device=model.device, owner=id(model))
 
 
 _kv_pool = _KVPool()
@@ -129,25 +199,46 @@ class _DecodeStep:
             m.greedy_tokens(self.logits, self.tok, self.probs)
 
     def run(self):
-        """Consume self.tok (ids of the previous step), leave logits (+ greedy tokens) for this one."""
-        moved = prepare_cache(self.cache, self.B, 1, self.model.dtype, self.model.device)
-        if not self.use_graph:
-            self._body()
-        else:
-            sig = self._signature()
-            if self.graph is None or moved or sig != self._sig:
-                torch.cuda.current_stream().synchronize()
-                g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g):
-                    self._body()
-                self.graph, self._sig = g, sig
-                # capture does not execute: replay below performs the step
-            self.graph.replay()
-        for c in self.cache:
-            c.advance_host(1)
+        """Consume self.tok (ids of the previous step), leave logits (+ greedy tokens) for this one.  Runs under the
+        model's forward lock: the scratch arena and the GEMM workspace belong to one step at a time, and a capture must
+        not see another thread's launches (capture_error_mode thread_local: other threads may allocate meanwhile)."""
+        with self.model._lock:
+            moved = prepare_cache(self.cache, self.B, 1, self.model.dtype, self.model.device)
+            arena = self.model._arena(self.B, self.B)     # same object unless the model dropped / re-keyed its arenas
+            stale = arena is not self.arena
+            self.arena = arena
+            if not self.use_graph:
+                self._body()
+            else:
+                sig = self._signature()
+                if self.graph is None or moved or stale or sig != self._sig:
+                    torch.cuda.current_stream().synchronize()
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g, capture_error_mode="thread_local"):
+                        self._body()
+                    self.graph, self._sig = g, sig
+                    # capture does not execute: replay below performs the step
+                self.graph.replay()
+            for c in self.cache:
+                c.advance_host(1)
 
 
 DecodeSession = _DecodeStep      # public name: one replayable decode step over a model + cache group
+
+
+def _decode_step_for(model: DecoderModel, cache: List[BatchedKVCache], B: int, graph_greedy: bool) -> _DecodeStep:
+    """The decode step (static buffers + captured graph) lives with the cache group it was captured over: a pooled cache
+    that comes back with the same buffers replays the same graph instead of paying a ~350-node capture per request.
+    ``_DecodeStep.run`` re-captures by itself when a buffer moved."""
+    holder = cache[0]
+    steps = holder.__dict__.setdefault("_decode_steps", {})
+    key = (id(model), B, graph_greedy, len(cache))
+    st = steps.get(key)
+    if st is None or st.model is not model or st.cache is not cache:
+        if len(steps) > 4:
+            steps.clear()
+        st = steps[key] = _DecodeStep(model, cache, B, graph_greedy)
+    return st
 
 
 def generate_step(
@@ -183,18 +274,19 @@ def generate_step(
     if logit_bias:
         bias_idx = torch.tensor(list(logit_bias.keys()), dtype=torch.int64, device=dev)
         bias_val = torch.tensor(list(logit_bias.values()), dtype=torch.float32, device=dev)
-    step = _DecodeStep(model, cache, B, greedy and not logit_bias)
+    step = _decode_step_for(model, cache, B, greedy and not logit_bias)
 
     def sample(logits: torch.Tensor) -> None:
         """utils.py:345-364; writes step.tok / step.probs."""
-        if bias_idx is not None:
-            logits[:, bias_idx] += bias_val
-        if greedy:
-            model.greedy_tokens(logits, step.tok, step.probs)
-        else:
-            p = top_p if (0 < top_p < 1.0) else 1.0
-            model.sample_tokens(logits, temp, p, sample_utils.current_seed(), sample_utils.next_offset(),
-                                step.tok, step.probs)
+        with model._lock:
+            if bias_idx is not None:
+                logits[:, bias_idx] += bias_val
+            if greedy:
+                model.greedy_tokens(logits, step.tok, step.probs)
+            else:
+                p = top_p if (0 < top_p < 1.0) else 1.0
+                model.sample_tokens(logits, temp, p, sample_utils.current_seed(), sample_utils.next_offset(),
+                                    step.tok, step.probs)
 
     # prefill (eager, chunked) + first sample
     logits = model(y, cache=cache, last_only=True)[:, -1, :]

@@ -3,7 +3,7 @@ the small-scale dequant (B200P_W_SMALLSCALE).  Each point is a CUDA graph of 8 x
 larger than L2, device events around 3 replays; prints us per launch, GB/s of algorithmic weight bytes and the fraction of
 the measured HBM peak (MEASURED_PEAKS.json).
 
-    python scripts/qmm_layer_bench.py [Ms=1,8,64] [model=llama3-8b|qwen3-14b|llama3-70b-8bit-tp8] [epilogues=decode]"""
+    python scripts/qmm_layer_bench.py [Ms=1,8,64] [model=llama3-8b|qwen3-14b|llama3-8b-tp8|llama3-70b-8bit-tp8] [only=qkv,o,...]"""
 import json
 import os
 import sys
@@ -18,6 +18,7 @@ dt = torch.float16
 g = torch.Generator(device="cuda").manual_seed(1)
 Ms = [int(v) for v in (sys.argv[1] if len(sys.argv) > 1 else "1,8,64").split(",")]
 model = sys.argv[2] if len(sys.argv) > 2 else "llama3-8b"
+only = set(sys.argv[3].split(",")) if len(sys.argv) > 3 else None
 SHAPES = {   # name, N, K, epilogue (0 store 16-bit, 1 store f32, 2 += f32, 3 silu*mul), bits
     "llama3-8b": [("qkv", 6144, 4096, 0, 4), ("o", 4096, 4096, 2, 4), ("gateup", 28672, 4096, 3, 4), ("down", 4096, 14336, 2, 4),
                   ("head", 128256, 4096, 1, 4)],
@@ -34,6 +35,8 @@ except Exception:
 _lib.check(L.b200p_qmm_set_path(2))
 print(f"model {model}; us per launch (GB/s, fraction of {peak:.0f} GB/s): 3-op dequant | small-scale dequant")
 for name, N, K, epi, bits in SHAPES:
+    if only and name not in only:
+        continue
     wbytes = N * K * bits // 8 + 2 * N * (K // 64) * 2
     ncopy = max(2, min(8, int(4e8 // wbytes) + 1))
     mats = []
