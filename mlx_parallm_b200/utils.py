@@ -161,6 +161,14 @@ def _presized_cache(model: DecoderModel, B: int, total_tokens: int) -> List[Batc
     return _kv_pool.get(model.head_dim, kv_heads, B, step=step, paged=True, device=model.device, owner=id(model))
 
 
+def _presize(kwargs: dict, model: DecoderModel, prompt_tokens, max_tokens: int) -> dict:
+    """generate_step kwargs with a cache that already holds prompt + max_tokens positions (unless the caller brought one)."""
+    if kwargs.get("cache") is None and isinstance(model, DecoderModel):
+        B, L = prompt_tokens.shape
+        kwargs = dict(kwargs, cache=_presized_cache(model, B, L + max_tokens))
+    return kwargs
+
+
 _kv_pool = _KVPool()
 
 
@@ -311,6 +319,7 @@ def stream_generate(model, tokenizer, prompt: str, max_tokens: int = 100, **kwar
     prompt_tokens = torch.tensor(tokenizer.encode(prompt))[None, :]
     detokenizer = tokenizer.detokenizer
     detokenizer.reset()
+    kwargs = _presize(kwargs, model, prompt_tokens, max_tokens)
     for (token, prob), n in zip(generate_step(prompt_tokens, model, **kwargs), range(max_tokens)):
         token_item = token.item()
         if token_item == tokenizer.eos_token_id:
@@ -335,6 +344,7 @@ def generate(model, tokenizer, prompt: str, max_tokens: int = 100, verbose: bool
     detokenizer.reset()
     n = -1
     prompt_time = 0.0
+    kwargs = _presize(kwargs, model, prompt_tokens, max_tokens)
     for (token, prob), n in zip(generate_step(prompt_tokens, model, **kwargs), range(max_tokens)):
         if n == 0:
             prompt_time = time.perf_counter() - tic
@@ -383,6 +393,7 @@ def batch_generate(model, tokenizer, prompts: List[str], max_tokens: int = 100, 
     tic = time.perf_counter()
     output_toks = []
     prompt_time = 0.0
+    kwargs = _presize(kwargs, model, prompts_toks, max_tokens)
     for (tokens, _), n in zip(generate_step(prompts_toks, model, **kwargs), range(max_tokens)):
         if n == 0:
             tokens[0, 0].item()                      # first token materialised = prefill done
@@ -415,7 +426,7 @@ def batch_stream_generate_text(model, tokenizer, prompts_tokens, max_tokens: int
     active = [True] * batch_size
     counts = [0] * batch_size
     eos_token_id = tokenizer.eos_token_id
-    gs_kwargs = {k: v for k, v in kwargs.items() if k != "repetition_penalty"}
+    gs_kwargs = _presize({k: v for k, v in kwargs.items() if k != "repetition_penalty"}, model, prompts_tokens, max_tokens)
     for (batch_next, _), _ in zip(generate_step(prompts_tokens, model, **gs_kwargs), range(max_tokens)):
         ids = batch_next.view(-1).tolist()           # ONE D2H per step (the reference does B .item() syncs)
         deltas: List[Tuple[Optional[str], Optional[str]]] = [(None, None)] * batch_size

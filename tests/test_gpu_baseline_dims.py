@@ -1,0 +1,186 @@
+"""Parity against the CPU oracle AT THE DIMENSIONS THE BENCHMARK IS QUOTED ON: two-layer, full-width,
+full-vocabulary slices of every BASELINE.json architecture -- Mistral-7B, Llama-3-8B, Qwen3-14B (4-bit) and Llama-3-70B-class
+(8-bit) -- with ``synth.random_weights``, compared with ``OracleModel(numerics="reference")`` (what MLX would compute: fp32 KV
+cache, fp32 residual stream):
+
+  * decode logits at B = 64 over a synthetic 2048-token context          <= 1e-2 relative (north star)
+  * prefill logits (last position) at B x L = 4 x 64 = 256 tokens         <= 1e-2 relative
+  * 32 greedy tokens on 128 sequences: every decision the oracle makes with a top-2 margin above the logits tolerance is
+    reproduced; a sequence may leave the oracle's transcript only at a near-tie (see ``greedy_report``)
+  * the tensor-parallel shard shapes of Qwen3-14B at TP = 2 / 4 / 8 (K % 512 != 0: scales and biases read from global memory
+    instead of by TMA, csrc/qmm_tc.cu) and 8-bit shards of the 70B-class config, GEMM against the oracle's quantized_matmul.
+
+Why not "identical on >= 99 % of sequences" as a raw count: a random-init model with V = 128 256 has a top-2 logit margin of
+~0.2 sigma on average, so a 4e-4 relative logits difference flips the argmax on ~2 % of the STEPS and half of all 32-token
+transcripts pass through at least one such near-tie; trained checkpoints are peaked and do not.  The margin-qualified rule
+below is the same statement without that artefact, and the raw fraction is printed for the record."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import rel_err
+from mlx_parallm_b200 import synth
+from oracle.model import OracleConfig, OracleModel
+
+pytestmark = pytest.mark.gpu
+
+LOGIT_TOL = 1e-2
+# greedy transcripts run by default on the headline architecture and its Mistral sibling (~2 min of oracle time together);
+# Qwen3-14B, the 70B-class slice and bf16 take another ~8 min and run with B200P_FULL_PARITY=1
+GREEDY_DEFAULT = {("llama-3-8b", "float16"), ("mistral-7b", "float16")}
+ARCHS = [("mistral-7b", "float16"), ("llama-3-8b", "float16"), ("qwen3-14b", "float16"), ("llama-3-70b", "float16"),
+         ("llama-3-8b", "bfloat16")]
+@pytest.fixture(scope="module", params=ARCHS, ids=[f"{n}-{d}" for n, d in ARCHS])
+def pair(request):
+    """Two full-width layers + embedding + head of one architecture.  Module-scoped and parametrised: pytest groups the
+    tests below by architecture, so each slice is built once and dropped before the next one (the 70B-class slice alone
+    holds ~11 GB of dequantised fp32 weights in the oracle's cache)."""
+    from mlx_parallm_b200.utils import _get_classes
+    name, dtype = request.param
+    cfg = synth.get_config(name, num_hidden_layers=2)
+    w = synth.random_weights(cfg, seed=1234, dtype=dtype, device="cpu")
+    om = OracleModel(OracleConfig.from_hf(cfg, dtype), synth.to_numpy_weights(w), numerics="reference")
+    Model, Args = _get_classes(cfg)
+    gm = Model(Args.from_dict(cfg)).load_weights(w, device="cuda")
+    del w
+    yield name, dtype, cfg, om, gm
+    del om, gm
+    torch.cuda.empty_cache()
+
+
+def filled_caches(om, gm, B, T, seed):
+    """Oracle and CUDA caches holding the SAME synthetic context: values drawn once in the model's 16-bit type, so the
+    oracle's fp32 cache and the engine's 16-bit cache start from identical numbers."""
+    oc = om.make_cache(B)
+    gc = gm.make_cache(B, step=T + 64)
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    for o, c in zip(oc, gc):
+        c.ensure_capacity(T + 1, gm.dtype, gm.device)
+        o.step = T + 64
+        o._ensure(T + 1)
+        for dst_o, dst_c in ((o.keys, c.keys), (o.values, c.values)):
+            t = (torch.randn((B, c.n_kv_heads, T, c.head_dim), generator=g, device="cuda") * 0.5).to(gm.dtype)
+            dst_c[:, :, :T] = t
+            dst_o[:, :, :T] = t.float().cpu().numpy()
+        o.offsets_list = [T] * B
+        c.offsets_list = [T] * B
+    return oc, gc
+
+
+def test_decode_logits_b64_over_a_2k_context(pair):
+    name, dtype, cfg, om, gm = pair
+    B, T = 64, 2048
+    oc, gc = filled_caches(om, gm, B, T, seed=11)
+    ids = np.random.default_rng(5).integers(0, cfg["vocab_size"], (B, 1)).astype(np.int64)
+    exp = om.forward(ids, oc, last_only=True)[:, -1]
+    got = gm(torch.from_numpy(ids), cache=gc, last_only=True)[:, -1].cpu().numpy()
+    err = rel_err(got, exp)
+    print(f"{name} {dtype}: decode logits B={B} T={T} rel err {err:.2e}")
+    assert got.shape == (B, cfg["vocab_size"]) and err < LOGIT_TOL
+    # the step appended exactly one key per row in both caches
+    assert gc[0].offsets == [T + 1] * B and oc[0].offsets == [T + 1] * B
+
+
+def test_prefill_logits_256_tokens(pair):
+    name, dtype, cfg, om, gm = pair
+    B, L = 4, 64
+    ids = np.random.default_rng(6).integers(0, cfg["vocab_size"], (B, L)).astype(np.int64)
+    exp = om.forward(ids, om.make_cache(B), last_only=True)[:, -1]
+    got = gm(torch.from_numpy(ids), cache=gm.make_cache(B), last_only=True)[:, -1].cpu().numpy()
+    err = rel_err(got, exp)
+    print(f"{name} {dtype}: prefill logits {B}x{L} rel err {err:.2e}")
+    assert err < LOGIT_TOL
+
+
+def greedy_report(got, exp, exp_logits, tol_rel):
+    """got / exp: [B, S] token ids; exp_logits: list of S arrays [B, V] (the oracle's logits per step).
+    Returns (identical fraction, near-tie divergences, real divergences).  A sequence is followed up to its first
+    divergence (after it the two contexts differ and nothing can be compared); the divergence is a near-tie when the oracle's
+    logit of the engine's token is within tol_rel * max|logits| of the oracle's maximum."""
+    B, S = exp.shape
+    identical, near, real = 0, 0, []
+    for b in range(B):
+        d = np.nonzero(got[b] != exp[b])[0]
+        if d.size == 0:
+            identical += 1
+            continue
+        s = int(d[0])
+        lg = exp_logits[s][b]
+        margin = float(lg.max() - lg[got[b, s]])
+        if margin <= tol_rel * float(np.abs(exp_logits[s]).max()):
+            near += 1
+        else:
+            real.append((b, s, margin))
+    return identical / B, near, real
+
+
+def test_greedy_32_tokens_on_128_sequences(pair):
+    from mlx_parallm_b200.utils import generate_step
+    from oracle.model import generate_step as oracle_generate_step
+    name, dtype, cfg, om, gm = pair
+    if (name, dtype) not in GREEDY_DEFAULT and os.environ.get("B200P_FULL_PARITY", "0") != "1":
+        pytest.skip("the oracle needs 1.5-4.5 min for this slice (128 x 32 full-vocabulary steps on the host cores): run with "
+                    "B200P_FULL_PARITY=1; the last full run is profiles/r2_baseline_dims_parity.txt")
+    B, L, S = 128, 16, 32
+    ids = np.random.default_rng(9).integers(0, cfg["vocab_size"], (B, L)).astype(np.int64)
+    exp, exp_logits = [], []
+    for _, (y, lg) in zip(range(S), oracle_generate_step(ids, om)):
+        exp.append(y[:, 0])
+        exp_logits.append(lg)
+    exp = np.stack(exp, 1)
+    got = np.stack([y[:, 0].cpu().numpy() for _, (y, _) in zip(range(S), generate_step(torch.from_numpy(ids), gm))], 1)
+    frac, near, real = greedy_report(got, exp, exp_logits, LOGIT_TOL)
+    print(f"{name} {dtype}: {frac:.3f} of {B} transcripts identical over {S} tokens, {near} left at a near-tie, {len(real)} real")
+    assert not real, real[:4]
+    # the first token (one step, no accumulated context difference) agrees on >= 99 % of the sequences outright in f16.
+    # bf16 keeps 8 bits of mantissa: its logits sit 3.4e-3 from the oracle's (inside the 1e-2 bar, 8x the f16 distance), so
+    # more first decisions are near-ties -- all of them are checked to be by the rule above, the raw count is not asserted.
+    if dtype == "float16":
+        assert (got[:, 0] == exp[:, 0]).mean() >= 0.99
+
+
+# ---------------------------------------------------------------------------------------- TP shard shapes, GEMM level
+def _oracle_qmm(M, N, K, bits, dtype, seed):
+    from oracle import mlx_ops as ref
+    rng = np.random.default_rng(seed)
+    wq = rng.integers(0, 2 ** 32, (N, K * bits // 32), dtype=np.uint32)
+    nb = (1 << bits) - 1
+    s = ref.round_to(rng.uniform(0.5, 1.5, (N, K // 64)) * rng.choice([-1, 1], (N, K // 64)) * (2 / nb) / np.sqrt(K), dtype)
+    b = ref.round_to(-s * nb / 2 + rng.normal(0, 0.01 / np.sqrt(K), (N, K // 64)), dtype)
+    x = ref.round_to(rng.standard_normal((M, K)), dtype)
+    return x, wq, s, b, ref.quantized_matmul(x, wq, s, b, 64, bits).astype(np.float64)
+
+
+SHARDS = [  # (what, N, K, bits, epilogue): Qwen3-14B shards (h 5120, inter 17408, 40 q / 8 kv heads of 128) and 70B-class 8-bit
+    ("qwen3-14b o_proj tp2", 5120, 2560, 4, 2), ("qwen3-14b o_proj tp4", 5120, 1280, 4, 2), ("qwen3-14b o_proj tp8", 5120, 640, 4, 2),
+    ("qwen3-14b down tp2", 5120, 8704, 4, 2), ("qwen3-14b down tp4", 5120, 4352, 4, 2), ("qwen3-14b down tp8", 5120, 2176, 4, 2),
+    ("qwen3-14b qkv tp4", 1792, 5120, 4, 0), ("qwen3-14b qkv tp8", 896, 5120, 4, 0),
+    ("qwen3-14b gate|up tp4", 8704, 5120, 4, 3), ("qwen3-14b gate|up tp8", 4352, 5120, 4, 3),
+    ("qwen3-14b head tp8", 18992, 5120, 4, 1),
+    ("llama-3-70b o_proj tp8", 8192, 1024, 8, 2), ("llama-3-70b down tp8", 8192, 3584, 8, 2),
+    ("llama-3-70b qkv tp8", 1280, 8192, 8, 0), ("llama-3-70b gate|up tp8", 7168, 8192, 8, 3),
+]
+
+
+@pytest.mark.parametrize("what,N,K,bits,epi", SHARDS, ids=[s[0] for s in SHARDS])
+@pytest.mark.parametrize("M", [64, 128])
+def test_tp_shard_gemms_match_the_oracle(what, N, K, bits, epi, M):
+    from mlx_parallm_b200 import _lib, ops
+    dtype = "float16"
+    x, wq, s, b, acc = _oracle_qmm(M, N, K, bits, dtype, seed=N + K + M)
+    tt = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(torch.float16).cuda()
+    w = torch.from_numpy(wq.view(np.int32)).cuda()
+    ws = torch.zeros((max(ops.qmm_workspace_bytes(M, N, K), 16),), dtype=torch.uint8, device="cuda")
+    assert _lib.lib().b200p_qmm_tensor_supported(M, N, K, 64, bits, ops.dtype_code(torch.float16), epi) == 1, \
+        "shard shape must stay on the tensor path"
+    if epi == _lib.EPI_ADD_RESIDUAL:
+        res = np.random.default_rng(1).standard_normal((M, N)).astype(np.float32)
+        out = torch.from_numpy(res.copy()).cuda()
+        ops.qmm(tt(x), w, tt(s), tt(b), 64, bits, epi, out=out, workspace=ws)
+        exp = res + acc
+    else:
+        out = ops.qmm(tt(x), w, tt(s), tt(b), 64, bits, epi, workspace=ws)
+        exp = acc if epi != _lib.EPI_SILU_MUL else acc[:, :N // 2] / (1 + np.exp(-acc[:, :N // 2])) * acc[:, N // 2:]
+    assert rel_err(out.float().cpu().numpy(), exp) < 3e-3, what

@@ -148,3 +148,46 @@ def test_compat_install_aliases_the_reference_module_names():
         for k in [k for k in sys.modules if k == "mlx_parallm" or k.startswith("mlx_parallm.")]:
             del sys.modules[k]
         sys.modules.update(saved)
+
+
+def test_encode_and_chat_template_lru_caches():
+    """utils.py:137-197: one tokenizer call per distinct (tokenizer, text) / (tokenizer, messages, flag); LRU eviction."""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from fake_tokenizer import FakeTokenizer
+    from mlx_parallm_b200 import utils
+    tw = TokenizerWrapper(FakeTokenizer(64))
+    assert utils.encode_cached(tw, "w3 w4") == [3, 4] and utils.encode_cached(tw, "w3 w4") == [3, 4]
+    assert tw._tokenizer.encode_calls == 1
+    msgs = [{"role": "user", "content": "w5 w6", "extra": "ignored by the key"}]
+    a = utils.apply_chat_template_cached(tw, msgs)
+    b = utils.apply_chat_template_cached(tw, [{"content": "w5 w6", "role": "user"}])          # same (role, content)
+    c = utils.apply_chat_template_cached(tw, msgs, add_generation_prompt=False)
+    assert a == b == "w1 w5 w6 w2" and c == "w1 w5 w6" and tw._tokenizer.chat_template_calls == 2
+    tw2 = TokenizerWrapper(FakeTokenizer(64))                                                 # another tokenizer: another key
+    utils.apply_chat_template_cached(tw2, msgs)
+    assert tw2._tokenizer.chat_template_calls == 1
+    lru = utils._LRUCache(max_size=2)
+    lru.set("a", 1); lru.set("b", 2); lru.get("a"); lru.set("c", 3)
+    assert lru.get("b") is None and lru.get("a") == 1 and lru.get("c") == 3
+
+
+def test_compat_provides_every_engine_name_the_reference_server_imports():
+    """server/main.py:22-33 and rl_training import these from mlx_parallm.utils / .sample_utils / .models.base; a missing name
+    is an ImportError before the server starts."""
+    import sys
+    import mlx_parallm_b200.compat as compat
+    saved = {k: v for k, v in sys.modules.items() if k == "mlx_parallm" or k.startswith("mlx_parallm.")}
+    try:
+        compat.install()
+        import mlx_parallm.utils as u
+        for name in ("load", "generate", "stream_generate", "batch_generate", "generate_step", "batch_stream_generate_text",
+                     "batch_generate_text", "apply_chat_template_cached", "encode_cached", "load_model", "load_config",
+                     "get_model_path", "load_adapters", "convert", "quantize_model"):
+            assert callable(getattr(u, name)), name
+        from mlx_parallm.sample_utils import top_p_sampling                                    # noqa: F401
+        from mlx_parallm.tokenizer_utils import TokenizerWrapper as TW, load_tokenizer        # noqa: F401
+    finally:
+        for k in [k for k in sys.modules if k == "mlx_parallm" or k.startswith("mlx_parallm.")]:
+            del sys.modules[k]
+        sys.modules.update(saved)
