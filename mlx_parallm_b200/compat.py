@@ -17,7 +17,13 @@ import types
 ENGINE_MODULES = ("utils", "sample_utils", "tokenizer_utils", "models", "models.base", "models.llama", "models.qwen3")
 
 
-def install(force: bool = True) -> types.ModuleType:
+def install(force: bool = True, shim_mlx: bool = False) -> types.ModuleType:
+    """``shim_mlx``: also register the stand-ins of mx_shim.py for the ``mlx.core`` / ``mlx.nn`` / ``mlx_lm.tokenizer_utils``
+    names the reference SERVER uses itself (only when the real packages are not importable), so that
+    ``import mlx_parallm.server.main`` works from a reference checkout on sys.path."""
+    if shim_mlx:
+        from . import mx_shim
+        mx_shim.install()
     pkg = sys.modules.get("mlx_parallm")
     if pkg is None:
         try:

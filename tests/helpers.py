@@ -29,3 +29,25 @@ def rel_err(a, b):
 
 def prompts_for(cfg, B, L, seed=7):
     return np.random.default_rng(seed).integers(0, cfg["vocab_size"], (B, L)).astype(np.int64)
+
+
+def greedy_report(got, exp, exp_logits, tol_rel):
+    """got / exp: [B, S] token ids; exp_logits: list of S arrays [B, V] (the oracle's logits per step).
+    Returns (identical fraction, near-tie divergences, real divergences).  A sequence is followed up to its first
+    divergence (after it the two contexts differ and nothing can be compared); the divergence is a near-tie when the oracle's
+    logit of the engine's token is within tol_rel * max|logits| of the oracle's maximum."""
+    B, S = exp.shape
+    identical, near, real = 0, 0, []
+    for b in range(B):
+        d = np.nonzero(got[b] != exp[b])[0]
+        if d.size == 0:
+            identical += 1
+            continue
+        s = int(d[0])
+        lg = exp_logits[s][b]
+        margin = float(lg.max() - lg[got[b, s]])
+        if margin <= tol_rel * float(np.abs(exp_logits[s]).max()):
+            near += 1
+        else:
+            real.append((b, s, margin))
+    return identical / B, near, real

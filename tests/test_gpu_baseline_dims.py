@@ -20,7 +20,7 @@ import numpy as np
 import pytest
 import torch
 
-from helpers import rel_err
+from helpers import greedy_report, rel_err
 from mlx_parallm_b200 import synth
 from oracle.model import OracleConfig, OracleModel
 
@@ -92,28 +92,6 @@ def test_prefill_logits_256_tokens(pair):
     err = rel_err(got, exp)
     print(f"{name} {dtype}: prefill logits {B}x{L} rel err {err:.2e}")
     assert err < LOGIT_TOL
-
-
-def greedy_report(got, exp, exp_logits, tol_rel):
-    """got / exp: [B, S] token ids; exp_logits: list of S arrays [B, V] (the oracle's logits per step).
-    Returns (identical fraction, near-tie divergences, real divergences).  A sequence is followed up to its first
-    divergence (after it the two contexts differ and nothing can be compared); the divergence is a near-tie when the oracle's
-    logit of the engine's token is within tol_rel * max|logits| of the oracle's maximum."""
-    B, S = exp.shape
-    identical, near, real = 0, 0, []
-    for b in range(B):
-        d = np.nonzero(got[b] != exp[b])[0]
-        if d.size == 0:
-            identical += 1
-            continue
-        s = int(d[0])
-        lg = exp_logits[s][b]
-        margin = float(lg.max() - lg[got[b, s]])
-        if margin <= tol_rel * float(np.abs(exp_logits[s]).max()):
-            near += 1
-        else:
-            real.append((b, s, margin))
-    return identical / B, near, real
 
 
 def test_greedy_32_tokens_on_128_sequences(pair):

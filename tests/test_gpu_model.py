@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 import torch
 
-from helpers import make_pair, prompts_for, rel_err
+from helpers import greedy_report, make_pair, prompts_for, rel_err
 from oracle.model import generate_step as oracle_generate_step
 
 pytestmark = pytest.mark.gpu
@@ -22,7 +22,9 @@ def test_prefill_logits_all_positions(name, dtype):
     exp = om.forward(ids, om.make_cache(3))
     got = gm(torch.from_numpy(ids), cache=None).cpu().numpy()
     assert got.shape == exp.shape == (3, 11, cfg["vocab_size"])
-    assert rel_err(got, exp) < (LOGIT_TOL if dtype != "bfloat16" else 2 * LOGIT_TOL)
+    err = rel_err(got, exp)
+    print(f"{name} {dtype}: logits rel err {err:.2e}")
+    assert err < LOGIT_TOL
 
 
 @pytest.mark.parametrize("name,dtype,B,L", [("small-llama", "float16", 8, 40), ("tiny-qwen3", "bfloat16", 5, 33),
@@ -36,11 +38,15 @@ def test_prefill_above_and_at_the_fp32_accumulator_limit(name, dtype, B, L):
     ids = prompts_for(cfg, B, L, seed=3)
     exp = om.forward(ids, om.make_cache(B), last_only=True)
     got = gm(torch.from_numpy(ids), cache=gm.make_cache(B), last_only=True).cpu().numpy()
-    assert rel_err(got, exp) < (LOGIT_TOL if dtype != "bfloat16" else 2 * LOGIT_TOL)
+    err = rel_err(got, exp)
+    print(f"{name} {dtype}: logits rel err {err:.2e}")
+    assert err < LOGIT_TOL
     from mlx_parallm_b200.utils import generate_step
     g = np.stack([y[:, 0].cpu().numpy() for _, (y, _) in zip(range(4), generate_step(torch.from_numpy(ids), gm))], 1)
-    e = np.stack([y[:, 0] for _, (y, _) in zip(range(4), oracle_generate_step(ids, om))], 1)
-    assert (g == e).all(1).mean() >= 0.8          # bf16 near-ties may flip a row; f16 rows are identical in practice
+    steps = [(y[:, 0], lg) for _, (y, lg) in zip(range(4), oracle_generate_step(ids, om))]
+    e = np.stack([y for y, _ in steps], 1)
+    frac, near, real = greedy_report(g, e, [lg for _, lg in steps], LOGIT_TOL)
+    assert not real, real                         # a row may leave the oracle's transcript at a near-tie only
 
 
 @pytest.mark.parametrize("name,dtype", [("tiny-llama", "float16"), ("small-llama", "float16"), ("tiny-qwen3", "bfloat16")])
@@ -77,18 +83,13 @@ def test_greedy_tokens_match_golden_transcript(golden_dir, fixture, name, dtype)
     got = run_greedy(gm, g["prompts"], 32)
     same = sequences_identical(got, g["tokens"])
     if not same.all():
-        # a disagreement is tolerated only where the oracle itself is at a near-tie (logit gap below the
-        # 1e-2 relative logits tolerance); anything else is a kernel bug
-        gen = oracle_generate_step(g["prompts"], om)
-        for t in range(32):
-            y, lg = next(gen)
-            bad = np.where(got[:, t] != y[:, 0])[0]
-            for b in bad:
-                gap = lg[b, y[b, 0]] - lg[b, got[b, t]]
-                assert gap <= LOGIT_TOL * np.abs(lg[b]).max(), (b, t, gap)
-            if len(bad):
-                break
-    assert same.mean() >= (0.99 if dtype != "bfloat16" else 0.5), same
+        # EVERY row that leaves the golden transcript must do so at a near-tie of the oracle (logit margin of the engine's
+        # token below the 1e-2 relative logits tolerance); anything else is a kernel bug
+        logits = [lg for _, (_, lg) in zip(range(32), oracle_generate_step(g["prompts"], om))]
+        frac, near, real = greedy_report(got, g["tokens"], logits, LOGIT_TOL)
+        assert not real, real
+    if dtype != "bfloat16":            # bf16 (8 mantissa bits) is held to the logits bar and the near-tie rule, see DESIGN 2
+        assert same.mean() >= 0.99, same
 
 
 def test_decode_logits_per_step_and_graph_equals_eager():
