@@ -40,6 +40,10 @@ WORKLOADS = {
     "llama3-8b-4bit-b256-t4096": ("llama-3-8b", 256, 4096),
     "mistral-7b-4bit-b8-t256": ("mistral-7b", 8, 256),
     "qwen3-14b-4bit-b64-t256": ("qwen3-14b", 64, 256),
+    # configs[4]: Llama-3-70B-class 8-bit, batch 128, TP=8.  The quoted 32k context needs 171.8 GB of 16-bit KV per GPU next
+    # to 9.2 GB of weights and does not fit 180 GB; 24 576 tokens (128.8 GB of KV per GPU) is the largest 8k multiple that does
+    "llama3-70b-8bit-b128-t24576": ("llama-3-70b", 128, 24576),
+    "llama3-70b-8bit-b128-t256": ("llama-3-70b", 128, 256),
     "small": ("small-llama", 4, 64),
 }
 HEADLINE = "llama3-8b-4bit-b64-t8192"
