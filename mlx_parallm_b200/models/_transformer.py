@@ -385,9 +385,9 @@ class DecoderModel:
             lengths = c.lengths(self.device)
             if fx is None or li == 0:      # with the fused exchange the previous layer's down_proj exchange wrote x
                 ops.rmsnorm(a["h"], layer.input_layernorm.weight, layer.input_layernorm.eps, out=a["x"], out_perm=pm)
-            qkv_buf = a["qkv32"] if a["qkv32"] is not None else a["qkv"]
-            at.qkv_proj(a["x"], EPI_ADD_RESIDUAL if qkv_buf.dtype == torch.float32 else EPI_STORE, out=qkv_buf,
-                        workspace=a["ws"], x_perm=pm)
+            acc32 = a["qkv32"] is not None                 # 16-bit model at decode sizes: fp32 accumulator (zero on entry)
+            qkv_buf = a["qkv32"] if acc32 else a["qkv"]
+            at.qkv_proj(a["x"], EPI_ADD_RESIDUAL if acc32 else EPI_STORE, out=qkv_buf, workspace=a["ws"], x_perm=pm)
             if at.lora:                    # LoRA on q_proj / v_proj (A.9): low-rank update of the q / v column blocks
                 for name, (At, Bt, scale) in at.lora.items():
                     col0 = 0 if name == "q_proj" else (at.n_heads + at.n_kv_heads) * at.head_dim
