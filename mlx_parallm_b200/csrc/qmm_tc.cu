@@ -159,6 +159,87 @@ __device__ __forceinline__ int seg_stage(const TcSeg& g, int i) {
   return g.s0 + (j >= g.ns ? j - g.ns : j);
 }
 
+// Fused epilogue of EPI_TOK tokens of one thread's two output columns (a: block A row r, b: block B row r).  Thread = one
+// output column, so every warp-level store below is one contiguous line per token (32 lanes x 4 B, or x 2 B for 16-bit
+// outputs -- whole sectors either way): nothing is staged through shared memory and no store is atomic.
+template <typename T>
+__device__ __forceinline__ void tc_emit(const TcParams& p, bool silu, int r, const float (&a)[EPI_TOK], const float (&b)[EPI_TOK],
+                                        int rowA0, int rowB0, int tokb) {
+    // rows r >= R are not part of this tile (their TMEM lanes hold garbage): pushing n past N disables every store below
+    const int n0 = r < p.R ? rowA0 + r : p.N, n1 = r < p.R ? rowB0 + r : p.N;
+    if (p.epi == B200P_EPI_ADD_RESIDUAL) {
+      // every element of y is owned by exactly one thread of the launch: plain read-modify-write
+      float* y = reinterpret_cast<float*>(p.y);
+      const bool ok0 = n0 < p.N, ok1 = n1 < p.N;
+      float ha[EPI_TOK], hb[EPI_TOK];
+#pragma unroll
+      for (int j = 0; j < EPI_TOK; ++j) {
+        const bool okt = tokb + j < p.M_tok;
+        const float* yr = y + (int64_t)(tokb + j) * p.ldy;
+        ha[j] = (ok0 && okt) ? __ldcg(yr + n0) : 0.f;
+        hb[j] = (ok1 && okt) ? __ldcg(yr + n1) : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < EPI_TOK; ++j) {
+        const bool okt = tokb + j < p.M_tok;
+        float* yr = y + (int64_t)(tokb + j) * p.ldy;
+        if (ok0 && okt) __stcg(yr + n0, ha[j] + a[j]);
+        if (ok1 && okt) __stcg(yr + n1, hb[j] + b[j]);
+      }
+    } else if (p.epi == B200P_EPI_STORE_F32) {
+      float* y = reinterpret_cast<float*>(p.y);
+#pragma unroll
+      for (int j = 0; j < EPI_TOK; ++j) {
+        if (tokb + j < p.M_tok) {
+          float* yr = y + (int64_t)(tokb + j) * p.ldy;
+          if (n0 < p.N) __stcg(yr + n0, a[j]);
+          if (n1 < p.N) __stcg(yr + n1, b[j]);
+        }
+      }
+    } else if (p.epi == B200P_EPI_STORE) {
+      T* y = reinterpret_cast<T*>(p.y);
+      const int c0 = p.y_perm ? perm8_pos(n0) : n0, c1 = p.y_perm ? perm8_pos(n1) : n1;
+#pragma unroll
+      for (int j = 0; j < EPI_TOK; ++j) {
+        if (tokb + j < p.M_tok) {
+          T* yr = y + (int64_t)(tokb + j) * p.ldy;
+          if (n0 < p.N) yr[c0] = Tr<T>::from_f(a[j]);
+          if (n1 < p.N) yr[c1] = Tr<T>::from_f(b[j]);
+        }
+      }
+    } else {                                         // SILU_MUL: block A = gate rows, block B = the matching up rows
+      T* y = reinterpret_cast<T*>(p.y);
+      const int c0 = p.y_perm ? perm8_pos(n0) : n0;
+      if (n0 < p.N / 2) {
+#pragma unroll
+        for (int j = 0; j < EPI_TOK; ++j)
+          if (tokb + j < p.M_tok) y[(int64_t)(tokb + j) * p.ldy + c0] = Tr<T>::from_f(silu_tc(a[j]) * b[j]);
+      }
+    }
+  }
+
+// Drain one WHOLE accumulator tile (both blocks) of this thread's TMEM lane through the fused epilogue: token groups
+// worker, worker + nworkers, ... of EPI_TOK tokens each.  The epilogue warps call it with (0, 1); on a CTA's LAST item the
+// dequant warps of the same lane quarter have nothing left to do and join as workers 1..4 (nworkers = 5), which cuts the
+// tail of a one-tile-per-CTA launch (gate|up at 64 rows: 8 groups, 2 per worker instead of 8 in a row).
+template <typename T, bool FAST>
+__device__ __forceinline__ void tc_drain_tile(const TcParams& p, bool silu, int r, uint32_t dA, uint32_t dB, int TN, int rowA0,
+                                              int rowB0, int tok0, int worker, int nworkers) {
+  constexpr float DSCALE = FAST ? 16.f : 1.f;        // FAST: A (hence D) was produced at 1/16
+  for (int t0 = worker * EPI_TOK; t0 < TN; t0 += nworkers * EPI_TOK) {
+    if (tok0 + t0 >= p.M_tok) break;                 // padding tokens of the last token tile
+    float a[EPI_TOK], b[EPI_TOK];
+    tmem_ld8(dA + (uint32_t)t0, a);
+    tmem_ld8(dB + (uint32_t)t0, b);
+    tmem_ld_wait();
+    if constexpr (FAST) {
+#pragma unroll
+      for (int j = 0; j < EPI_TOK; ++j) { a[j] *= DSCALE; b[j] *= DSCALE; }
+    }
+    tc_emit<T>(p, silu, r, a, b, rowA0, rowB0, tok0 + t0);
+  }
+}
+
 // FAST: the small-scale dequant of dequant.cuh (f16, caller promised B200P_W_SMALLSCALE): A and D are produced at 1/16.
 template <typename T, int BITS, bool XPERM, bool FAST>
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -474,6 +555,19 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
       }
     }
     TFLUSH(9, 3, threadIdx.x == 0);                  // 9 full_w, 10 sb_full, 11 empty_a, 12 total (dequant warp 0)
+    // ---- help the epilogue warp of this lane quarter drain the CTA's LAST whole tile (see tc_drain_tile)
+    if (p.S == 1 && warp_active && cta < p.items && !(kDebug & 4)) {
+      const int n_seg = (p.items - cta + G - 1) / G, seg = n_seg - 1, item = cta + seg * G;
+      const TcSeg sg = seg_of(p, item);
+      const int pair = sg.tile / p.tiles_m, tm = sg.tile % p.tiles_m;
+      const int buf = NBUF == 2 ? (seg & 1) : 0;
+      pdl_wait();                                    // y belongs to the previous kernels until here
+      mbar_wait(accum_full(buf), (uint32_t)((seg / NBUF) & 1));
+      tc_fence_after();
+      const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
+      tc_drain_tile<T, FAST>(p, silu, r, lane_base + d_col(buf, 0), lane_base + d_col(buf, 1), TN, silu ? pair * p.R : pair * 2 * p.R,
+                             silu ? p.N / 2 + pair * p.R : pair * 2 * p.R + p.R, tm * TN, 1 + grp, 1 + DQ_WARPS / 4);
+    }
   } else {
     // ===================================== epilogue warps ===================================
     TDECL;
@@ -486,61 +580,6 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     const int et = threadIdx.x - DQ_THREADS;         // 0..127
     constexpr float DSCALE = FAST ? 16.f : 1.f;      // FAST: A (hence D) was produced at 1/16
     const int64_t slot_elems = (int64_t)2 * TN * 128;   // one partial tile: [2 blocks][TN tokens][128 rows] fp32
-
-    // fused epilogue of EPI_TOK tokens of this thread's two output columns (a: block A, b: block B)
-    auto emit = [&](const float (&a)[EPI_TOK], const float (&b)[EPI_TOK], int rowA0, int rowB0, int tokb) {
-      // rows r >= R are not part of this tile (their TMEM lanes hold garbage): pushing n past N disables every store below
-      const int n0 = r < p.R ? rowA0 + r : p.N, n1 = r < p.R ? rowB0 + r : p.N;
-      if (p.epi == B200P_EPI_ADD_RESIDUAL) {
-        // every element of y is owned by exactly one thread of the launch: plain read-modify-write
-        float* y = reinterpret_cast<float*>(p.y);
-        const bool ok0 = n0 < p.N, ok1 = n1 < p.N;
-        float ha[EPI_TOK], hb[EPI_TOK];
-#pragma unroll
-        for (int j = 0; j < EPI_TOK; ++j) {
-          const bool okt = tokb + j < p.M_tok;
-          const float* yr = y + (int64_t)(tokb + j) * p.ldy;
-          ha[j] = (ok0 && okt) ? __ldcg(yr + n0) : 0.f;
-          hb[j] = (ok1 && okt) ? __ldcg(yr + n1) : 0.f;
-        }
-#pragma unroll
-        for (int j = 0; j < EPI_TOK; ++j) {
-          const bool okt = tokb + j < p.M_tok;
-          float* yr = y + (int64_t)(tokb + j) * p.ldy;
-          if (ok0 && okt) __stcg(yr + n0, ha[j] + a[j]);
-          if (ok1 && okt) __stcg(yr + n1, hb[j] + b[j]);
-        }
-      } else if (p.epi == B200P_EPI_STORE_F32) {
-        float* y = reinterpret_cast<float*>(p.y);
-#pragma unroll
-        for (int j = 0; j < EPI_TOK; ++j) {
-          if (tokb + j < p.M_tok) {
-            float* yr = y + (int64_t)(tokb + j) * p.ldy;
-            if (n0 < p.N) __stcg(yr + n0, a[j]);
-            if (n1 < p.N) __stcg(yr + n1, b[j]);
-          }
-        }
-      } else if (p.epi == B200P_EPI_STORE) {
-        T* y = reinterpret_cast<T*>(p.y);
-        const int c0 = p.y_perm ? perm8_pos(n0) : n0, c1 = p.y_perm ? perm8_pos(n1) : n1;
-#pragma unroll
-        for (int j = 0; j < EPI_TOK; ++j) {
-          if (tokb + j < p.M_tok) {
-            T* yr = y + (int64_t)(tokb + j) * p.ldy;
-            if (n0 < p.N) yr[c0] = Tr<T>::from_f(a[j]);
-            if (n1 < p.N) yr[c1] = Tr<T>::from_f(b[j]);
-          }
-        }
-      } else {                                         // SILU_MUL: block A = gate rows, block B = the matching up rows
-        T* y = reinterpret_cast<T*>(p.y);
-        const int c0 = p.y_perm ? perm8_pos(n0) : n0;
-        if (n0 < p.N / 2) {
-#pragma unroll
-          for (int j = 0; j < EPI_TOK; ++j)
-            if (tokb + j < p.M_tok) y[(int64_t)(tokb + j) * p.ldy + c0] = Tr<T>::from_f(silu_tc(a[j]) * b[j]);
-        }
-      }
-    };
 
     pdl_wait();                                      // y and the workspace belong to the previous kernels until here
     int seg = 0;
@@ -560,17 +599,8 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
       const uint32_t dA = lane_base + d_col(buf, 0), dB = lane_base + d_col(buf, 1);
       if (!(kDebug & 4)) {
         if (full) {
-          for (int t0 = 0; t0 < TN; t0 += EPI_TOK) {
-            float a[EPI_TOK], b[EPI_TOK];
-            tmem_ld8(dA + (uint32_t)t0, a);
-            tmem_ld8(dB + (uint32_t)t0, b);
-            tmem_ld_wait();
-            if constexpr (FAST) {
-#pragma unroll
-              for (int j = 0; j < EPI_TOK; ++j) { a[j] *= DSCALE; b[j] *= DSCALE; }
-            }
-            emit(a, b, rowA0, rowB0, tok0 + t0);
-          }
+          const bool last = item + G >= p.items;       // the dequant warps help with this CTA's last tile
+          tc_drain_tile<T, FAST>(p, silu, r, dA, dB, TN, rowA0, rowB0, tok0, 0, last ? 1 + DQ_WARPS / 4 : 1);
         } else {
           // partial tile of a K split: one slot per CTA (the host plans S > 1 only with one item per CTA)
           float* part = p.ws_part + (int64_t)cta * slot_elems;
@@ -636,7 +666,7 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
 #pragma unroll
           for (int j = 0; j < EPI_TOK; ++j) { a[j] += va[j]; b[j] += vb[j]; }
         }
-        emit(a, b, rowA0, rowB0, tok0 + t0);
+        tc_emit<T>(p, silu, r, a, b, rowA0, rowB0, tok0 + t0);
       }
       // the last contributor to finish re-arms the tile's counters for the next launch (all S have passed the wait)
       if (et == 0) {

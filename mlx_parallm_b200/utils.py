@@ -296,12 +296,26 @@ def generate_step(
                 model.sample_tokens(logits, temp, p, sample_utils.current_seed(), sample_utils.next_offset(),
                                     step.tok, step.probs)
 
+    def check_exchange():
+        """Tensor parallelism: a peer that never arrived makes the exchange kernel time out, set a status word and carry
+        on with incomplete sums -- plausible but wrong tokens.  Read the word at generation boundaries (one 4-byte D2H) and
+        fail loudly instead."""
+        fx = getattr(model, "_tp_fused", None)
+        if fx is not None and fx.status() != 0:
+            raise RuntimeError("tensor-parallel exchange timed out waiting for a peer rank (status word "
+                               f"{fx.status()}): results of this generation are invalid")
+
     # prefill (eager, chunked) + first sample
     logits = model(y, cache=cache, last_only=True)[:, -1, :]
     sample(logits)
+    check_exchange()
     out_y = step.tok.to(torch.int64).view(B, 1)
     out_p = step.probs.clone().view(B, 1)
+    n_steps = 0
     while True:
+        n_steps += 1
+        if n_steps % 256 == 0:
+            check_exchange()
         step.run()                                   # launches step n+1 (utils.py:422-423)
         if not step.greedy:
             sample(step.logits)
