@@ -72,11 +72,23 @@ __device__ __forceinline__ void dequant8(const uint32_t* pw, uint32_t s2, uint32
       out[2] = prmt(a04, a15, 0x7632u);   // k4 k5
       out[3] = prmt(a26, a37, 0x7632u);   // k6 k7
     }
-  } else {
+  } else if constexpr (std::is_same<T, __half>::value) {
     out[0] = H::fma(H::q_lo(prmt(pw[0], H::MAGIC_BYTES, 0x4140u)), s2, b2);
     out[1] = H::fma(H::q_lo(prmt(pw[0], H::MAGIC_BYTES, 0x4342u)), s2, b2);
     out[2] = H::fma(H::q_lo(prmt(pw[1], H::MAGIC_BYTES, 0x4140u)), s2, b2);
     out[3] = H::fma(H::q_lo(prmt(pw[1], H::MAGIC_BYTES, 0x4342u)), s2, b2);
+  } else {
+    // bf16 holds 128 + q exactly only for q < 128 (7 mantissa bits), so an 8-bit code goes in as two nibbles:
+    //   q*s + b = lo*s + (hi*(16 s) + b)      (16 s is exact; two bf16 FMAs, i.e. two roundings instead of one --
+    // one more half-ulp of bf16 on the A operand, inside the tolerance bf16 models are held to)
+    const typename H::V s16 = __hmul2(H::as(s2), H::as(0x41804180u));          // 16.0 | 16.0
+    const uint32_t s16u = H::bits(s16);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint32_t x = prmt(pw[i >> 1], 0u, (i & 1) ? 0x4342u : 0x4140u);    // two codes, one per 16-bit lane
+      const uint32_t t = H::fma(H::q_lo(lop3_and_or(x >> 4, 0x000f000fu, H::MAGIC)), s16u, b2);
+      out[i] = H::fma(H::q_lo(lop3_and_or(x, 0x000f000fu, H::MAGIC)), s2, t);
+    }
   }
 }
 

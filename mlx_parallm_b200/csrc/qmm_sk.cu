@@ -506,7 +506,7 @@ int qmm_sk_launch(const void* x, const uint32_t* w, const void* s, const void* b
     if (fast) return x_perm ? launch_sk<__half, 4, true, true>(tms, p, pl, st) : launch_sk<__half, 4, false, true>(tms, p, pl, st);
     return x_perm ? launch_sk<__half, 4, true, false>(tms, p, pl, st) : launch_sk<__half, 4, false, false>(tms, p, pl, st);
   }
-  B200P_REQUIRE(bits == 4, B200P_ERR_ARG, "bf16 8-bit is not on the tensor path");
+  if (bits == 8) return launch_sk<__nv_bfloat16, 8, false, false>(tms, p, pl, st);
   return x_perm ? launch_sk<__nv_bfloat16, 4, true, false>(tms, p, pl, st) : launch_sk<__nv_bfloat16, 4, false, false>(tms, p, pl, st);
 }
 

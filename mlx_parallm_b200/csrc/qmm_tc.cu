@@ -783,7 +783,6 @@ static TcPlan make_plan(int64_t M, int64_t N, int64_t K, int bits, int epi) {
 bool qmm_tc_supported(int64_t M, int64_t N, int64_t K, int gs, int bits, int dtype, int epi) {
   if (gs != 64) return false;
   if (dtype != B200P_F16 && dtype != B200P_BF16) return false;
-  if (bits == 8 && dtype == B200P_BF16) return false;        // 128 + q is not exact in bf16 for q >= 128
   if (M < g_min_tc_m) return false;
   if (K % 64 != 0 || (K * bits / 8) % 16 != 0) return false;
   if (N % 8 != 0) return false;
@@ -934,7 +933,7 @@ int qmm_tc_launch(const void* x, const uint32_t* w, const void* s, const void* b
     if (fast) return x_perm ? launch_tc<__half, 4, true, true>(tms, p, pl, st) : launch_tc<__half, 4, false, true>(tms, p, pl, st);
     return x_perm ? launch_tc<__half, 4, true, false>(tms, p, pl, st) : launch_tc<__half, 4, false, false>(tms, p, pl, st);
   } else {
-    B200P_REQUIRE(bits == 4, B200P_ERR_ARG, "bf16 8-bit is not on the tensor path");
+    if (bits == 8) return launch_tc<__nv_bfloat16, 8, false, false>(tms, p, pl, st);
     return x_perm ? launch_tc<__nv_bfloat16, 4, true, false>(tms, p, pl, st) : launch_tc<__nv_bfloat16, 4, false, false>(tms, p, pl, st);
   }
 }

@@ -274,13 +274,17 @@ class DecoderModel:
     def apply_lora(self, adapters: Dict[str, torch.Tensor], scale: float, keys=("self_attn.q_proj", "self_attn.v_proj")):
         """Attach mlx_lm-format LoRA adapters (``model.layers.{i}.self_attn.q_proj.lora_a [K, r]`` / ``.lora_b [r, N]``;
         lora_init.py:63-73, 140-149) to the attention projections.  Stored transposed and rank-padded to 16 for the
-        mma kernel; lora_a's k axis follows the PERM8 activation layout when the model uses it.  Pass {} to detach."""
-        if self.tp_world > 1:
-            raise NotImplementedError("LoRA under tensor parallelism is not built")
+        mma kernel; lora_a's k axis follows the PERM8 activation layout when the model uses it.  Pass {} to detach.
+
+        Tensor parallelism: q_proj / v_proj are column-parallel, so ``lora_a`` (applied to the replicated input) is used
+        whole and ``lora_b`` is cut to this rank's output columns -- the same row range ``tp.shard_weights`` keeps of the
+        projection.  Hot swap (rl_training/weight_updater.py:66-73): the adapter set is built aside and swapped in under the
+        model's forward lock, so a generation in flight sees either the old or the new set, never a mix."""
         if not self._fast16:
             raise NotImplementedError("LoRA needs a 16-bit model (b200p_lora_add)")
+        new_sets = []
         for i, layer in enumerate(self.model.layers):
-            layer.self_attn.lora = {}
+            new_sets.append({})
             for key in keys:
                 if key not in ("self_attn.q_proj", "self_attn.v_proj"):
                     raise NotImplementedError(f"LoRA on {key} is not built (reference default: q_proj, v_proj)")
@@ -289,6 +293,12 @@ class DecoderModel:
                     continue
                 A = adapters[pa].to(self.device, self.dtype)           # [K, r]
                 Bm = adapters[pb].to(self.device, self.dtype)          # [r, N]
+                n_local = getattr(layer.self_attn, key.split(".")[-1]).weight.shape[0]
+                if Bm.shape[1] != n_local:                             # full-width adapter on a column shard
+                    if Bm.shape[1] != n_local * self.tp_world:
+                        raise ValueError(f"{pb}: {Bm.shape[1]} output columns do not match the projection "
+                                         f"({n_local} x tp {self.tp_world})")
+                    Bm = Bm[:, self.tp_rank * n_local:(self.tp_rank + 1) * n_local]
                 K, r = A.shape
                 if r > 16:
                     raise NotImplementedError(f"LoRA rank {r} > 16")
@@ -298,7 +308,11 @@ class DecoderModel:
                     At = At.view(16, K // 8, 8)[:, :, [0, 4, 1, 5, 2, 6, 3, 7]].reshape(16, K)
                 Bt = torch.zeros((Bm.shape[1], 16), dtype=self.dtype, device=self.device)
                 Bt[:, :r] = Bm.t()
-                layer.self_attn.lora[key.split(".")[-1]] = (At.contiguous(), Bt.contiguous(), float(scale))
+                new_sets[i][key.split(".")[-1]] = (At.contiguous(), Bt.contiguous(), float(scale))
+        with self._lock:
+            for layer, st in zip(self.model.layers, new_sets):
+                layer.self_attn.lora = st
+            self._arenas.clear()          # captured decode graphs hold the old adapter pointers: force a re-capture
         return self
 
     def set_tensor_parallel(self, rank: int, world: int, allreduce):

@@ -403,6 +403,8 @@ TC_CASES = [  # M, N, K, bits, dtype, epilogue
     (64, 2048, 1024, 4, "float16", 3), (5, 1000, 192, 4, "float16", 1), (100, 1000, 448, 4, "bfloat16", 1),
     (300, 512, 512, 4, "float16", 0), (64, 512, 2048, 8, "float16", 1), (33, 768, 640, 4, "bfloat16", 3),
     (64, 256, 4096, 4, "float16", 2),          # deep K with few row blocks -> split-K + last-arriver fix-up
+    # 8-bit bf16: the code goes in as two nibbles (128 + q is exact in bf16 only below 128), two bf16 FMAs
+    (64, 512, 2048, 8, "bfloat16", 1), (8, 1024, 1024, 8, "bfloat16", 2), (40, 768, 512, 8, "bfloat16", 3), (128, 512, 1024, 8, "bfloat16", 0),
 ]
 
 

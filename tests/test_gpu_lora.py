@@ -91,3 +91,67 @@ def test_model_with_lora_matches_oracle_and_loads_from_disk(tmp_path):
     gm.apply_lora({}, scale)                                # detach: back to the base model
     again = gm(torch.from_numpy(ids), cache=gm.make_cache(4), last_only=True).cpu().numpy()
     assert rel_err(again, base) < 1e-3                      # split-K partial sums arrive in any order: equal to fp32 rounding
+
+
+def test_lora_on_a_tensor_parallel_shard_keeps_its_output_columns():
+    """q_proj / v_proj are column-parallel: a rank applies lora_a whole and the columns of lora_b that belong to its rows of
+    the projection (the range tp.shard_weights keeps), so its q|k|v block equals the same columns of the unsharded model."""
+    from mlx_parallm_b200 import ops, synth, tp
+    from mlx_parallm_b200.utils import _get_classes
+    cfg = synth.get_config("small-llama", num_key_value_heads=2)      # the stock config has one kv head: not divisible
+    w = synth.random_weights(cfg, seed=1234, dtype="float16")
+    Model, Args = _get_classes(cfg)
+    full = Model(Args.from_dict(cfg)).load_weights(w, device="cuda")
+    rng = np.random.default_rng(11)
+    ad = _adapters(cfg, 8, rng, layers=[0, 1])
+    full.apply_lora(ad, 10.0)
+    x = (torch.randn((6, cfg["hidden_size"]), generator=torch.Generator().manual_seed(3)) * 0.5).to(torch.float16).cuda()
+    world = 2
+    for rank in range(world):
+        part = Model(Args.from_dict(cfg)).load_weights(tp.shard_weights(w, cfg, rank, world), device="cuda")
+        part.set_tensor_parallel(rank, world, None)
+        part.apply_lora(ad, 10.0)                                   # full-width adapters, cut inside
+        for li in (0, 1):
+            af, ap = full.model.layers[li].self_attn, part.model.layers[li].self_attn
+            for name in ("q_proj", "v_proj"):
+                n_loc = getattr(ap, name).weight.shape[0]
+                Atf, Btf, sf = af.lora[name]
+                Atp, Btp, sp = ap.lora[name]
+                assert torch.equal(Atf, Atp) and sf == sp
+                assert torch.equal(Btp, Btf[rank * n_loc:(rank + 1) * n_loc])
+                yf = torch.zeros((6, Btf.shape[0]), dtype=torch.float32, device="cuda")
+                yp = torch.zeros((6, n_loc), dtype=torch.float32, device="cuda")
+                ops.lora_add(x, Atf, Btf, yf, 0, sf)
+                ops.lora_add(x, Atp, Btp, yp, 0, sp)
+                assert torch.equal(yp, yf[:, rank * n_loc:(rank + 1) * n_loc])
+
+
+def test_lora_hot_swap_recaptures_the_decode_graph():
+    """weight_updater.py:66-73: adapters are swapped while the server keeps generating.  The captured decode graph holds the
+    old adapter pointers; after a swap the next generation must run on the new set (graph re-captured), and detaching must
+    give the base model back."""
+    from mlx_parallm_b200 import utils
+    cfg, om, gm = make_pair("small-llama", dtype="float16")
+    ids = torch.from_numpy(prompts_for(cfg, 2, 12, seed=4))
+
+    def run():
+        return np.stack([y[:, 0].cpu().numpy() for _, (y, _) in zip(range(8), utils.generate_step(ids, gm))], 1)
+
+    def logits():
+        return gm(ids, cache=gm.make_cache(2), last_only=True).cpu().numpy()
+
+    base_t, base_l = run(), logits()
+    rng = np.random.default_rng(7)
+    ad1, ad2 = _adapters(cfg, 8, rng, layers=[0, 1]), _adapters(cfg, 16, rng, layers=[1])
+    gm.apply_lora(ad1, 10.0)
+    l1, t1 = logits(), run()
+    gm.apply_lora(ad2, 10.0)
+    l2, t2 = logits(), run()
+    assert rel_err(l1, base_l) > 1e-3 and rel_err(l2, base_l) > 1e-3 and rel_err(l1, l2) > 1e-3
+    fresh = make_pair("small-llama", dtype="float16")[2].apply_lora(ad2, 10.0)
+    tf = np.stack([y[:, 0].cpu().numpy() for _, (y, _) in zip(range(8), utils.generate_step(ids, fresh))], 1)
+    lf = fresh(ids, cache=fresh.make_cache(2), last_only=True).cpu().numpy()
+    assert rel_err(l2, lf) < 1e-4 and (t2[:, 0] == tf[:, 0]).all()          # same set on a fresh model (fp32 order aside)
+    gm.apply_lora({}, 10.0)
+    assert rel_err(logits(), base_l) < 1e-3
+    del t1, base_t
