@@ -37,6 +37,12 @@ MAX_TOKENS_PER_FORWARD = 8192     # chunk size (B*L) of one prefill pass through
 # q|k|v has 24 output tiles for 148 SMs, so it must split K; measured at 64 rows (profiles/r2_run11_*): 16.8 us through the
 # whole-tile kernel's workspace split against 8-10 us this way.  Above it (prefill) whole 16-bit tiles are stored directly.
 ACC32_MAX_ROWS = 128
+# gate|up: one GPU's full matrix (117 M weights on Llama-3-8B) goes through the whole-tile kernel with the fused silu*mul
+# epilogue (27.9 us at 64 rows; stream-K into fp32 + the silu_mul kernel: 22.7 + 5.9 us, and 22 MB of fp32 round trip).  A
+# tensor-parallel SHARD of it has too few rows to fill 148 SMs with whole tiles and is latency-bound there, so up to this
+# many weights it takes the stream-K accumulate path + silu_mul (profiles/r2_run17_*, r2_run18_*, 64 rows: TP=2 shard
+# 14.9 + 4.2 vs 23.5 us, TP=4 10.8 + 3.5 vs 17.3, TP=8 7.4 + 3.1 vs 13.7).
+GATE_UP_ACC32_MAX_WEIGHTS = 100 * 1000 * 1000
 USE_PERM8 = True                  # 4-bit 16-bit models: GEMM inputs in the PERM8 column order (include/b200p.h)
 # |scale| bound under which an f16 matrix may take the subnormal-operand dequant (B200P_W_SMALLSCALE, csrc/dequant.cuh):
 # the kernel needs s * 2^20 finite in half precision, i.e. |s| < 0.0625; checked once per matrix at load time.
@@ -362,6 +368,9 @@ class DecoderModel:
                 qkv=torch.empty((M, nqkv), dtype=dt, device=dev),
                 # zero once: the consumer kernel (rope_kv_append) re-zeroes it behind its reads
                 qkv32=torch.zeros((M, nqkv), dtype=torch.float32, device=dev) if self._fast16 and M <= ACC32_MAX_ROWS else None,
+                gu32=(torch.zeros((M, 2 * inter_local), dtype=torch.float32, device=dev)
+                      if self._fast16 and M <= ACC32_MAX_ROWS and 2 * inter_local * args.hidden_size <= GATE_UP_ACC32_MAX_WEIGHTS
+                      else None),
                 q=torch.empty((M, att.n_heads * att.head_dim), dtype=dt, device=dev),
                 att=torch.empty((M, att.n_heads * att.head_dim), dtype=dt, device=dev),
                 act=torch.empty((M, inter_local), dtype=dt, device=dev),
@@ -429,7 +438,11 @@ class DecoderModel:
                     self._allreduce(a["h"])
                 ops.rmsnorm(a["h"], layer.post_attention_layernorm.weight, layer.post_attention_layernorm.eps, out=a["x"],
                             out_perm=pm)
-            mlp.gate_up_proj(a["x"], EPI_SILU_MUL, out=a["act"], workspace=a["ws"], x_perm=pm, y_perm=pm)
+            if a["gu32"] is not None:      # small (sharded) gate|up: fp32 accumulator, silu_mul rounds and re-zeroes it
+                mlp.gate_up_proj(a["x"], EPI_ADD_RESIDUAL, out=a["gu32"], workspace=a["ws"], x_perm=pm)
+                ops.silu_mul(a["gu32"], a["act"], out_perm=pm)
+            else:
+                mlp.gate_up_proj(a["x"], EPI_SILU_MUL, out=a["act"], workspace=a["ws"], x_perm=pm, y_perm=pm)
             if fx is not None:
                 mlp.down_proj(a["act"], EPI_ADD_RESIDUAL, out=fx.partial(1, M), workspace=a["ws"], x_perm=pm)
                 nxt = layers[li + 1].input_layernorm if li + 1 < len(layers) else None

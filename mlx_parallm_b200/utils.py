@@ -17,6 +17,7 @@ from __future__ import annotations
 
 import asyncio
 import copy
+import gc
 import glob
 import importlib
 import json
@@ -221,9 +222,22 @@ class _DecodeStep:
                 sig = self._signature()
                 if self.graph is None or moved or stale or sig != self._sig:
                     torch.cuda.current_stream().synchronize()
+                    self.graph = None
                     g = torch.cuda.CUDAGraph()
-                    with torch.cuda.graph(g, capture_error_mode="thread_local"):
-                        self._body()
+                    # No cyclic garbage collection inside the capture: a dead Python cycle that owns a CUDA graph or device
+                    # memory (an old decode step and its cache group reference each other) would be finalised by whatever
+                    # allocation happens to trigger the collector, and a cudaFree / cudaGraphExecDestroy on the capturing
+                    # thread invalidates the capture.  Collect first (captures are rare: one per pooled cache group),
+                    # then keep the collector off until the capture has ended.
+                    gc_was_on = gc.isenabled()
+                    gc.collect()
+                    gc.disable()
+                    try:
+                        with torch.cuda.graph(g, capture_error_mode="thread_local"):
+                            self._body()
+                    finally:
+                        if gc_was_on:
+                            gc.enable()
                     self.graph, self._sig = g, sig
                     # capture does not execute: replay below performs the step
                 self.graph.replay()

@@ -1,0 +1,16 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_model.py tests/test_gpu_frontends.py tests/test_gpu_lora.py -x -q --timeout 300 -p no:cacheprovider 2>&1 | tail -4
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511"
+timeout 600 $TR bench.py --gpus 2 --steps 16 --warmup 3 --sweep=llama3-8b-4bit-b64-t256 --no-prefill > gpurun_out/r2_tp2b_bench_headline.json 2> gpurun_out/r2_tp2b_bench_headline.err
+python - <<'PY'
+import json
+d=json.load(open('gpurun_out/r2_tp2b_bench_headline.json'))
+print('tp2 headline ms/step', round(d['ms_per_step'],3), 'tok/s', round(d['value']), 'selfcheck ok', d['tp_selfcheck']['ok'], 'sweep', d['sweep'])
+PY
+timeout 600 $TR bench.py --gpus 2 --workload qwen3-14b-4bit-b64-t256 --steps 16 --warmup 3 --sweep= --no-prefill > gpurun_out/r2_tp2b_bench_qwen3.json 2> gpurun_out/r2_tp2b_bench_qwen3.err
+python - <<'PY'
+import json
+d=json.load(open('gpurun_out/r2_tp2b_bench_qwen3.json'))
+print('tp2 qwen3-14b b64 t256 ms/step', round(d['ms_per_step'],3), 'tok/s', round(d['value']), 'selfcheck ok', d['tp_selfcheck']['ok'])
+PY

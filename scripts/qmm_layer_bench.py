@@ -23,6 +23,13 @@ SHAPES = {   # name, N, K, epilogue (0 store 16-bit, 1 store f32, 2 += f32, 3 si
     "llama3-8b": [("qkv", 6144, 4096, 0, 4), ("o", 4096, 4096, 2, 4), ("gateup", 28672, 4096, 3, 4), ("down", 4096, 14336, 2, 4),
                   ("head", 128256, 4096, 1, 4)],
     "qwen3-14b": [("qkv", 7168, 5120, 0, 4), ("o", 5120, 5120, 2, 4), ("gateup", 34816, 5120, 3, 4), ("down", 5120, 17408, 2, 4)],
+    # the fused projections through the fp32 accumulate epilogue (stream-K kernel) instead of their 16-bit epilogues
+    "llama3-8b-acc": [("gateup", 28672, 4096, 2, 4), ("head", 128256, 4096, 2, 4), ("gateup-tp2", 14336, 4096, 2, 4),
+                      ("gateup-tp4", 7168, 4096, 2, 4), ("gateup-tp8", 3584, 4096, 2, 4), ("head-tp8", 16032, 4096, 2, 4)],
+    "llama3-8b-tp2": [("qkv", 3072, 4096, 0, 4), ("o", 4096, 2048, 2, 4), ("gateup", 14336, 4096, 3, 4), ("down", 4096, 7168, 2, 4),
+                      ("head", 64128, 4096, 1, 4)],
+    "llama3-8b-tp4": [("qkv", 1536, 4096, 0, 4), ("o", 4096, 1024, 2, 4), ("gateup", 7168, 4096, 3, 4), ("down", 4096, 3584, 2, 4),
+                      ("head", 32064, 4096, 1, 4)],
     "llama3-8b-tp8": [("qkv", 768, 4096, 0, 4), ("o", 4096, 512, 2, 4), ("gateup", 3584, 4096, 3, 4), ("down", 4096, 1792, 2, 4),
                       ("head", 16032, 4096, 1, 4)],
     "llama3-70b-8bit-tp8": [("qkv", 1280, 8192, 0, 8), ("o", 8192, 1024, 2, 8), ("gateup", 7168, 8192, 3, 8), ("down", 8192, 3584, 2, 8)],
