@@ -271,8 +271,8 @@ class PeerExchange:
         if self._closed:
             return
         self._closed = True
-        from ._lib import lib
-        try:
+        try:                               # best effort: at interpreter shutdown the import machinery may already be gone
+            from ._lib import lib
             with torch.cuda.device(self.device):
                 torch.cuda.synchronize()
                 for p, b in enumerate(self._peer_base):
