@@ -39,7 +39,8 @@ constexpr int EPI_THREADS = EPI_WARPS * 32;
 constexpr int WARP_W = DQ_WARPS + EPI_WARPS;     // TMA producer: weights + scale/bias tiles (never waits for the previous grid)
 constexpr int WARP_X = WARP_W + 1;               // TMA producer: activation tiles (after griddepcontrol.wait)
 constexpr int WARP_MMA = WARP_X + 1;
-constexpr int TC_THREADS = (WARP_MMA + 1) * 32;
+constexpr int MMA_WARPS = 2;                      // one issuing warp per 128-row block of the pair (see umma_half_kblock_f16_ts)
+constexpr int TC_THREADS = (WARP_MMA + MMA_WARPS) * 32;
 constexpr int TMEM_COLS = 512;
 constexpr int MAX_TN = 128;
 constexpr int W_TILE_BYTES = 128 * 128;          // one weight block of one stage: 128 rows x 128 packed bytes
@@ -113,10 +114,10 @@ qmm_sk_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < S; ++s) { mbar_init(full_w(s), 1); mbar_init(empty_w(s), DQ_WARPS); }
-    for (int s = 0; s < p.x_slots; ++s) { mbar_init(full_x(s), 1); mbar_init(empty_x(s), 1); }
-    for (int s = 0; s < NSLOT; ++s) { mbar_init(full_a(s), 8); mbar_init(empty_a(s), 1); }
+    for (int s = 0; s < p.x_slots; ++s) { mbar_init(full_x(s), 1); mbar_init(empty_x(s), MMA_WARPS); }
+    for (int s = 0; s < NSLOT; ++s) { mbar_init(full_a(s), 8); mbar_init(empty_a(s), MMA_WARPS); }
     for (int s = 0; s < NSB; ++s) { mbar_init(sb_full(s), 1); mbar_init(sb_empty(s), DQ_WARPS); }
-    for (int d = 0; d < 2; ++d) { mbar_init(accum_full(d), 1); mbar_init(accum_empty(d), EPI_WARPS); }
+    for (int d = 0; d < 2; ++d) { mbar_init(accum_full(d), MMA_WARPS); mbar_init(accum_empty(d), EPI_WARPS); }
     fence_barrier_init();
     tma_prefetch_desc(&tm_w);
     tma_prefetch_desc(&tm_x);
@@ -183,8 +184,8 @@ qmm_sk_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
         __syncwarp();
       }
     }
-  } else if (warp == WARP_MMA) {
-    // ===================================== MMA issuer =======================================
+  } else if (warp >= WARP_MMA) {
+    // ===================================== MMA issuers (warp WARP_MMA + b: block b of the pair) =====================
     // instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32 (1<<4), a/b format (0 f16, 1 bf16) at
     // bits 7/10, K-major A and B, N>>3 at bit 17, M>>4 at bit 24
     const uint32_t fmt = std::is_same<T, __nv_bfloat16>::value ? 1u : 0u;
@@ -193,7 +194,8 @@ qmm_sk_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     uint32_t it = 0;
     const uint64_t xdesc0 = make_desc_sw128(x_ring);            // X slot 0, first 16 k; slot s adds s * (slot bytes >> 4)
     const uint32_t xdesc_step = x_slot_bytes >> 4;
-    const uint32_t a_base = tmem_base + A_COL0;
+    const int mw = warp - WARP_MMA;                    // block of the pair this warp issues for
+    const uint32_t a_base = tmem_base + A_COL0 + (uint32_t)(mw * 32);
     for (long long u = u_begin; u < u_end; ++seg) {
       const int s0 = (int)(u % p.num_st);
       const int ns = (int)min((long long)(p.num_st - s0), u_end - u);
@@ -202,7 +204,7 @@ qmm_sk_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
         mbar_wait(accum_empty(buf), (uint32_t)(((seg / NBUF) - 1) & 1));
         tc_fence_after();
       }
-      const uint32_t d0 = tmem_base + d_col(buf, 0), d1 = tmem_base + d_col(buf, 1);
+      const uint32_t dmine = tmem_base + d_col(buf, mw);
       const int nkb = ns * KPS;
       for (int j = 0; j < nkb; ++j, ++it) {
         const uint32_t slot = it & (NSLOT - 1), xs = it & x_mask;
@@ -210,7 +212,7 @@ qmm_sk_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
         mbar_wait(full_a(slot), (it >> 2) & 1u);
         tc_fence_after();
         if (elect_one()) {
-          umma_kblock_f16_ts(d0, d1, a_base + slot * 64, xdesc0 + (uint64_t)(xs * xdesc_step), idesc, j > 0 ? 1u : 0u);
+          umma_half_kblock_f16_ts(dmine, a_base + slot * 64, xdesc0 + (uint64_t)(xs * xdesc_step), idesc, j > 0 ? 1u : 0u);
           umma_commit(empty_a(slot));
           umma_commit(empty_x(xs));
           if (j == nkb - 1) umma_commit(accum_full(buf));

@@ -22,14 +22,14 @@
 //      j, j+S, ... of all S slots in CTA order and applies the fused epilogue to them.
 // Sums are therefore taken in a fixed order: results are bit-reproducible run to run.
 //
-// warp roles (736 threads):
+// warp roles (768 threads):
 //   warps 0..15  dequantisers: 4 groups of 4 warps, group g handles weight block g&1 on k-blocks of parity g>>1;
 //                a thread owns one weight row: LDS packed codes -> 16-bit q*s+b -> tcgen05.st into the A ring;
 //   warps 16..19 epilogue: TMEM -> registers -> global (thread = output column n: every warp store is one coalesced
 //                line per token), stream-K partial tiles and their final reduction;
 //   warp 20      TMA producer of weights and scale/bias tiles (independent of the previous kernel: starts at once);
 //   warp 21      TMA producer of X tiles (after griddepcontrol.wait);
-//   warp 22      TMEM owner + MMA issuer (elect.sync, operands in uniform registers).
+//   warps 22, 23 MMA issuers, one per 128-row block of the pair (elect.sync, operands in uniform registers); warp 22 owns TMEM.
 //
 // rings:  W   (packed weights, 2 x [128 rows x 128 B] per stage) in shared memory, SWIZZLE_128B, filled by TMA and
 //             handed back as soon as the dequant warps hold the codes in registers, so the HBM stream never waits
@@ -73,7 +73,8 @@ constexpr int EPI_THREADS = EPI_WARPS * 32;
 constexpr int WARP_W = DQ_WARPS + EPI_WARPS;     // TMA producer: weights + scale/bias tiles (never waits for the previous grid)
 constexpr int WARP_X = WARP_W + 1;               // TMA producer: activation tiles (after griddepcontrol.wait)
 constexpr int WARP_MMA = WARP_X + 1;
-constexpr int TC_THREADS = (WARP_MMA + 1) * 32;
+constexpr int MMA_WARPS = 2;                      // one issuing warp per 128-row block of the pair (see umma_half_kblock_f16_ts)
+constexpr int TC_THREADS = (WARP_MMA + MMA_WARPS) * 32;
 constexpr int TMEM_COLS = 512;
 constexpr int MAX_TN = 128;
 constexpr int NSLOT = 8;                         // upper bound of A ring slots (each: 2 blocks x 32 TMEM columns); a launch
@@ -284,10 +285,10 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < S; ++s) { mbar_init(full_w(s), 1); mbar_init(empty_w(s), DQ_WARPS); }
-    for (int s = 0; s < p.x_slots; ++s) { mbar_init(full_x(s), 1); mbar_init(empty_x(s), 1); }
-    for (int s = 0; s < p.a_slots; ++s) { mbar_init(full_a(s), 8); mbar_init(empty_a(s), 1); }
+    for (int s = 0; s < p.x_slots; ++s) { mbar_init(full_x(s), 1); mbar_init(empty_x(s), MMA_WARPS); }
+    for (int s = 0; s < p.a_slots; ++s) { mbar_init(full_a(s), 8); mbar_init(empty_a(s), MMA_WARPS); }
     for (int s = 0; s < NSB; ++s) { mbar_init(sb_full(s), 1); mbar_init(sb_empty(s), DQ_WARPS); }
-    for (int d = 0; d < 2; ++d) { mbar_init(accum_full(d), 1); mbar_init(accum_empty(d), EPI_WARPS); }
+    for (int d = 0; d < 2; ++d) { mbar_init(accum_full(d), MMA_WARPS); mbar_init(accum_empty(d), EPI_WARPS); }
     fence_barrier_init();
     tma_prefetch_desc(&tm_w);
     tma_prefetch_desc(&tm_x);
@@ -371,8 +372,8 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
      }
     }
     TFLUSH(3, 1, lane == 0);                         // 3 empty_x, 4 total
-  } else if (warp == WARP_MMA) {
-    // ===================================== MMA issuer =======================================
+  } else if (warp >= WARP_MMA) {
+    // ===================================== MMA issuers (warp WARP_MMA + b: block b of the pair) =====================
     // instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32 (1<<4), a/b format (0 f16, 1 bf16) at
     // bits 7/10, K-major A and B, N>>3 at bit 17, M>>4 at bit 24
     const uint32_t fmt = std::is_same<T, __nv_bfloat16>::value ? 1u : 0u;
@@ -382,7 +383,8 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     TDECL;
     const uint64_t xdesc0 = make_desc_sw128(x_ring);            // X slot 0, first 16 k; slot s adds s * (slot bytes >> 4)
     const uint32_t xdesc_step = x_slot_bytes >> 4;
-    const uint32_t a_base = tmem_base + A_COL0;
+    const int mw = warp - WARP_MMA;                    // block of the pair this warp issues for
+    const uint32_t a_base = tmem_base + A_COL0 + (uint32_t)(mw * 32);
     const uint32_t x_slots = (uint32_t)p.x_slots;
     for (int item = cta; item < p.items; item += G, ++seg) {
       const int ns = seg_of(p, item).ns;
@@ -391,7 +393,7 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
         TWAIT(2, accum_empty(buf), (uint32_t)(((seg / NBUF) - 1) & 1));
         tc_fence_after();
       }
-      const uint32_t d0 = tmem_base + d_col(buf, 0), d1 = tmem_base + d_col(buf, 1);
+      const uint32_t dmine = tmem_base + d_col(buf, mw);
       const int nkb = ns * KPS;
       for (int j = 0; j < nkb; ++j) {
         TWAIT(0, full_x(xs), xph);
@@ -399,7 +401,7 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
         tc_fence_after();
         if (elect_one()) {
           if (!(kDebug & 2))
-            umma_kblock_f16_ts(d0, d1, a_base + slot * 64, xdesc0 + (uint64_t)(xs * xdesc_step), idesc, j > 0 ? 1u : 0u);
+            umma_half_kblock_f16_ts(dmine, a_base + slot * 64, xdesc0 + (uint64_t)(xs * xdesc_step), idesc, j > 0 ? 1u : 0u);
           umma_commit(empty_a(slot));
           umma_commit(empty_x(xs));
           if (j == nkb - 1) umma_commit(accum_full(buf));
@@ -409,7 +411,7 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
         if (++xs == x_slots) { xs = 0; xph ^= 1u; }
       }
     }
-    TFLUSH(5, 3, lane == 0);                         // 5 full_x, 6 full_a, 7 accum_empty, 8 total
+    TFLUSH(5, 3, lane == 0 && mw == 0);              // 5 full_x, 6 full_a, 7 accum_empty, 8 total
   } else if (warp < DQ_WARPS) {
     // ===================================== dequantisers =====================================
     const int grp = warp >> 2;                         // 0..3

@@ -82,6 +82,10 @@ __device__ __forceinline__ void umma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, ui
 // were what bounded the kernel at ~3.7 TB/s), so the per-MMA operands are formed with the fewest adds possible:
 //   A slices at a, a+8, ..., a+56 TMEM columns (block 0: 0..24, block 1: 32..56), B descriptors at b, b+2, b+4, b+6
 //   (16-byte units: 32 bytes = 16 k per MMA).  acc = 0 clears D on the first slice of each block.
+// The two blocks' MMAs ALTERNATE: consecutive tcgen05.mma into the SAME accumulator are a dependent chain (one every
+// 64 cycles at M=128, K=16 whatever N <= 128), two independent accumulators interleaved retire one MMA every 32 cycles at
+// N=64 = the full rate of the pipe (scripts/probe_mma2.cu, profiles/r2_run22_probe_mma2.txt); four in a row per block, the
+// order used before, averaged 51.
 __device__ __forceinline__ void umma_kblock_f16_ts(uint32_t d0, uint32_t d1, uint32_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
   asm volatile(
       "{\n"
@@ -101,15 +105,41 @@ __device__ __forceinline__ void umma_kblock_f16_ts(uint32_t d0, uint32_t d1, uin
       "add.u64 b2, %3, 4;\n"
       "add.u64 b3, %3, 6;\n"
       "tcgen05.mma.cta_group::1.kind::f16 [%0], [%2], %3, %4, p;\n"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], [a1], b1, %4, pt;\n"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], [a2], b2, %4, pt;\n"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], [a3], b3, %4, pt;\n"
       "tcgen05.mma.cta_group::1.kind::f16 [%1], [a4], %3, %4, p;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [a1], b1, %4, pt;\n"
       "tcgen05.mma.cta_group::1.kind::f16 [%1], [a5], b1, %4, pt;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [a2], b2, %4, pt;\n"
       "tcgen05.mma.cta_group::1.kind::f16 [%1], [a6], b2, %4, pt;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [a3], b3, %4, pt;\n"
       "tcgen05.mma.cta_group::1.kind::f16 [%1], [a7], b3, %4, pt;\n"
       "}\n" ::"r"(d0),
       "r"(d1), "r"(a), "l"(b), "r"(idesc), "r"(acc)
+      : "memory");
+}
+// The four MMAs of ONE block of a k-block (A slices a, a+8, a+16, a+24; B descriptors b, b+2, b+4, b+6).  The GEMM kernels run
+// TWO issuing warps, one per 128-row block: a single thread issues one tcgen05.mma (M=128, K=16, N <= 64) every 51-64 cycles
+// whatever the order of its accumulators, two threads of different warps together retire one every 32 cycles = the full rate of
+// the pipe at N=64 (scripts/probe_mma2.cu, profiles/r2_run22_probe_mma2.txt).
+__device__ __forceinline__ void umma_half_kblock_f16_ts(uint32_t d, uint32_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p, pt;\n"
+      ".reg .b32 a1, a2, a3;\n"
+      ".reg .b64 b1, b2, b3;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "setp.eq.b32 pt, %3, %3;\n"
+      "add.u32 a1, %1, 8;\n"
+      "add.u32 a2, %1, 16;\n"
+      "add.u32 a3, %1, 24;\n"
+      "add.u64 b1, %2, 2;\n"
+      "add.u64 b2, %2, 4;\n"
+      "add.u64 b3, %2, 6;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [a1], b1, %3, pt;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [a2], b2, %3, pt;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [a3], b3, %3, pt;\n"
+      "}\n" ::"r"(d),
+      "r"(a), "l"(b), "r"(idesc), "r"(acc)
       : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
