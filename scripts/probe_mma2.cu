@@ -25,13 +25,13 @@ __device__ __forceinline__ void umma_f16_ts1(uint32_t d_tmem, uint32_t a_tmem, u
 }
 
 // issuers = 1 or 2 warps; each issues iters * 4 MMAs (K slices 0..3 of its A slot) into its own accumulator
-__global__ void __launch_bounds__(128, 1) probe(int N, int Mrows, int iters, int issuers, unsigned long long* out) {
+__global__ void __launch_bounds__(128, 1) probe(int N, int Mrows, int iters, int issuers, int commits, unsigned long long* out) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t bar0 = base, bar1 = base + 8, slot = base + 16;
+  const uint32_t bar0 = base, bar1 = base + 8, slot = base + 16, scratch = base + 64;   // scratch: 4 barriers per issuer, never waited on
   const uint32_t b_tile = base + 1024;                 // [256 x 64] 16-bit, SWIZZLE_128B: 32 KB
   const int warp = threadIdx.x >> 5;
-  if (threadIdx.x == 0) { mbar_init(bar0, 1); mbar_init(bar1, 1); fence_barrier_init(); }
+  if (threadIdx.x == 0) { mbar_init(bar0, 1); mbar_init(bar1, 1); for (int i = 0; i < 8; ++i) mbar_init(scratch + 8 * i, 1); fence_barrier_init(); }
   if (warp == 0) tmem_alloc(slot, 512);
   tc_fence_before();
   __syncthreads();
@@ -53,6 +53,7 @@ __global__ void __launch_bounds__(128, 1) probe(int N, int Mrows, int iters, int
     for (int i = 0; i < iters; ++i) {
 #pragma unroll
       for (int k4 = 0; k4 < 4; ++k4) umma_f16_ts1(d, a + 8 * k4, bd + 2 * k4, idesc, 1u);
+      for (int c = 0; c < commits; ++c) umma_commit(scratch + 8 * (4 * warp + c));
     }
     umma_commit(bar);
     mbar_wait(bar, ph);
@@ -77,11 +78,12 @@ int main() {
   const int smem = 1024 + 1024 + 32768;
   CK(cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   const int iters = 2000;
-  for (int Mrows : {128, 64}) {
-    for (int issuers : {1, 2}) {
-      printf("M=%d, %d issuing warp(s), A in TMEM, one accumulator per issuer\n", Mrows, issuers);
-      for (int N : {16, 64, 128, 192}) {
-        probe<<<sms, 128, smem>>>(N, Mrows, iters, issuers, out);
+  for (int Mrows : {128}) {
+    for (int issuers : {1, 2})
+    for (int commits : {0, 1, 2, 3}) {
+      printf("M=%d, %d issuing warp(s), A in TMEM, one accumulator per issuer, %d tcgen05.commit after every 4 MMAs\n", Mrows, issuers, commits);
+      for (int N : {16, 64}) {
+        probe<<<sms, 128, smem>>>(N, Mrows, iters, issuers, commits, out);
         CK(cudaDeviceSynchronize());
         double mx = 0;
         for (int i = 0; i < sms; ++i) mx = out[i] > mx ? (double)out[i] : mx;
