@@ -172,10 +172,14 @@ __device__ __forceinline__ float block_sum(float v, float* sh) {
   return r;
 }
 
-template <typename T>
-__global__ void __launch_bounds__(256)
+// NT = 128 is the "early" variant (B200P_RMS_EARLY): at most 32 registers per thread, so that a CTA fits next to a resident
+// tensor-path GEMM CTA (768 threads x 80 registers), launched with the PDL attribute, and it releases ITS dependents before
+// waiting for its own producer -- the GEMM that follows the norm is then scheduled while the GEMM before the norm drains.
+template <typename T, int NT>
+__global__ void __launch_bounds__(NT, NT == 128 ? 16 : 1)
 rmsnorm_kernel(const float* __restrict__ x, const T* __restrict__ w, T* __restrict__ y, int64_t H, float eps, int perm) {
   __shared__ float sh[33];
+  if constexpr (NT == 128) pdl_launch_dependents();
   pdl_wait();
   const float* xr = x + (int64_t)blockIdx.x * H;
   T* yr = y + (int64_t)blockIdx.x * H;
@@ -236,8 +240,17 @@ extern "C" int b200p_rmsnorm(const float* x, const void* w, void* y, int64_t M, 
   B200P_REQUIRE(aligned(x, 16) && aligned(y, 16) && H % 4 == 0, B200P_ERR_ALIGN,
                 "rmsnorm needs 16-byte aligned rows (H %% 4 == 0)");
   if (M == 0) return B200P_OK;
-  B200P_DISPATCH_DTYPE(dtype, T, (launch_pdl(rmsnorm_kernel<T>, (unsigned)M, 256, 0, (cudaStream_t)stream, 
-                                     x, (const T*)w, (T*)y, H, eps, perm)));
+  // auto: from 16 rows on the next kernel is a tile GEMM that profits (B=64 T=256: 2.91 -> 2.87 ms); below, the GEMV kernels
+  // do not, and the 128-thread CTA is the slower norm (B=1 T=8192: 2.38 -> 2.43 ms) -- profiles/r2_run29_*
+  static const int early_env = [] { const char* e = getenv("B200P_RMS_EARLY"); return e ? atoi(e) : -1; }();
+  const bool early = early_env >= 0 ? early_env != 0 : M >= 16;
+  if (early) {
+    B200P_DISPATCH_DTYPE(dtype, T, (launch_pdl_opt(true, rmsnorm_kernel<T, 128>, (unsigned)M, 128, 0, (cudaStream_t)stream,
+                                       x, (const T*)w, (T*)y, H, eps, perm)));
+  } else {
+    B200P_DISPATCH_DTYPE(dtype, T, (launch_pdl(rmsnorm_kernel<T, 256>, (unsigned)M, 256, 0, (cudaStream_t)stream,
+                                       x, (const T*)w, (T*)y, H, eps, perm)));
+  }
   B200P_LAUNCH_CHECK("rmsnorm_kernel");
   return B200P_OK;
 }
