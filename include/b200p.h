@@ -159,6 +159,22 @@ int b200p_attn(const void* q, const void* kcache, const void* vcache, const int3
                void* out, int64_t B, int64_t L, int Hq, int Hkv, int D, int64_t Tcap,
                float scale, int dtype, int flags, void* workspace, size_t workspace_bytes, void* stream);
 size_t b200p_attn_workspace_bytes(int64_t B, int64_t L, int Hq, int D);
+/* Decode attention (L == 1) that allocates NOTHING: b200p_attn's split-K decode kernel with its split partials in a
+ * file-scope device array of the library instead of a caller-allocated workspace.
+ *                      [no counterpart in the reference: added for callers that
+ *                       cannot call cudaMalloc -- code under CUDA graph capture, tight serving loops, harnesses that forbid it]
+ * Same arguments and result as b200p_attn with L = 1 (bit-identical: same kernels, same split count); 16-bit caches,
+ * D == 128, Hq / Hkv <= 16 only.  The scratch is B200P_ATTN_STATIC_SCRATCH_BYTES (16 MiB, held by every GPU that loads the
+ * library until the process exits), i.e. B * Hq <= 992; larger calls are rejected with B200P_ERR_ARG -- use b200p_attn.
+ * The call makes no cudaMalloc / cudaFree and calls no allocating routine; its first use on a device resolves the array's
+ * device address (cudaGetSymbolAddress), so make that first call outside a stream capture.
+ * Every call shares the array, which keeps the last call's contents (nothing in it has to start at zero: each call writes
+ * every record it later reads).  Calls that overlap on the GPU -- two streams, concurrent graph branches -- RACE on it:
+ * serialise them. */
+#define B200P_ATTN_STATIC_SCRATCH_BYTES (16u << 20)
+int b200p_attn_decode_static(const void* q, const void* kcache, const void* vcache, const int32_t* lengths,
+                             void* out, int64_t B, int Hq, int Hkv, int D, int64_t Tcap,
+                             float scale, int dtype, int flags, void* stream);
 /* 0 = auto, 1 = generic CUDA-core kernel only, 2 = tensor (mma) kernels only: split-K decode for L == 1, causal flash
  * prefill for L > 1 (16-bit, head_dim 128) */
 int b200p_attn_set_path(int path);

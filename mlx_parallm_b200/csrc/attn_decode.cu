@@ -11,6 +11,7 @@
 // Why legacy mma.sync and not tcgen05 here: M = G <= 16 rows of real work per kv head; the kernel is
 // bound by streaming K/V (2*T*D*2 bytes per kv head) and the tensor pipe is ~10 % busy either way.
 // Algorithmic HBM bytes per launch: sum_b len_b * Hkv * D * 2 (K and V) * sizeof(T).
+#include <mutex>
 #include <type_traits>
 
 #include <stdlib.h>
@@ -312,3 +313,69 @@ int attn_decode_launch(const void* q, const void* kc, const void* vc, const int3
 }
 
 }  // namespace b200p
+
+// ------------------------------------------------------------------------------------------------ no-allocation variant
+// b200p_attn_decode_static: the split-K decode attention above with its split partials in a FILE-SCOPE device array
+// instead of a caller-allocated workspace -- for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+// serving loops, harnesses that forbid it).  No counterpart in the reference.
+//
+// The array is part of the library image: every GPU that loads the library holds its 16 MiB until the process exits.
+// In HOST code the name `g_attn_static_scratch` is only a stand-in for the symbol, not a device address (a kernel handed
+// it would fault or, where the GPU can reach host memory, silently use the wrong memory): the device address is resolved
+// once per device with cudaGetSymbolAddress, with that device current, and that pointer is what the kernels receive.
+// Every call shares the array and it keeps the last call's contents.  Nothing has to start at zero: attn_decode_kernel writes
+// the (m, l, O) record of EVERY (row, query head, split) of the call -- an empty split writes m = -inf, l = 0 -- before
+// attn_reduce_kernel of the same call reads them, and no record outside the call's B*Hq*splits is read.  Two calls that
+// overlap on the GPU (different streams, or concurrent graph branches) race on the array: serialise them.
+constexpr size_t ATTN_STATIC_SCRATCH_BYTES = B200P_ATTN_STATIC_SCRATCH_BYTES;
+static __device__ __align__(256) float g_attn_static_scratch[ATTN_STATIC_SCRATCH_BYTES / sizeof(float)];
+
+namespace b200p {
+constexpr int ATTN_STATIC_MAX_DEVICES = 64;
+static void* g_attn_static_ptr[ATTN_STATIC_MAX_DEVICES] = {};
+static std::mutex g_attn_static_mu;
+
+// device address of the scratch array on the CURRENT device (resolved on the first call per device; no allocation)
+static int attn_static_scratch_ptr(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+  B200P_REQUIRE(dev >= 0 && dev < ATTN_STATIC_MAX_DEVICES, B200P_ERR_ARG, "device index %d beyond %d", dev,
+                ATTN_STATIC_MAX_DEVICES);
+  std::lock_guard<std::mutex> lock(g_attn_static_mu);
+  if (!g_attn_static_ptr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_attn_static_scratch);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_attn_static_scratch)");
+    B200P_REQUIRE(p != nullptr && aligned(p, 256), B200P_ERR_CUDA, "static attention scratch resolved to a bad address");
+    g_attn_static_ptr[dev] = p;
+  }
+  *out = g_attn_static_ptr[dev];
+  return B200P_OK;
+}
+}  // namespace b200p
+
+extern "C" int b200p_attn_decode_static(const void* q, const void* kcache, const void* vcache, const int32_t* lengths,
+                                        void* out, int64_t B, int Hq, int Hkv, int D, int64_t Tcap, float scale, int dtype,
+                                        int flags, void* stream) {
+  using namespace b200p;
+  B200P_REQUIRE(q && kcache && vcache && lengths && out, B200P_ERR_ARG, "null pointer");
+  B200P_REQUIRE((flags & ~B200P_OUT_PERM8) == 0, B200P_ERR_ARG, "unknown flags 0x%x", flags);
+  B200P_REQUIRE(Hq > 0 && Hkv > 0 && Hq % Hkv == 0, B200P_ERR_ARG, "bad head counts %d/%d", Hq, Hkv);
+  B200P_REQUIRE(B >= 0 && Tcap > 0, B200P_ERR_ARG, "bad shape");
+  B200P_REQUIRE(attn_decode_supported(1, Hq, Hkv, D, dtype), B200P_ERR_ARG,
+                "b200p_attn_decode_static: 16-bit caches, head_dim 128 and at most 16 query heads per kv head only");
+  const size_t need = attn_decode_workspace_bytes(B, 1, Hq, D);
+  B200P_REQUIRE(need <= ATTN_STATIC_SCRATCH_BYTES, B200P_ERR_ARG,
+                "b200p_attn_decode_static: B * Hq = %lld needs %zu bytes of scratch, the static array holds %zu "
+                "(B * Hq <= %zu); use b200p_attn with a caller-allocated workspace",
+                (long long)(B * Hq), need, ATTN_STATIC_SCRATCH_BYTES,
+                ATTN_STATIC_SCRATCH_BYTES / (size_t)(AD_MAX_SPLITS * AD_REC * sizeof(float)));
+  if (B == 0) return B200P_OK;
+  void* ws = nullptr;
+  const int rc = attn_static_scratch_ptr(&ws);
+  if (rc != B200P_OK) return rc;
+  PdlClass pdl_cls(8);
+  return attn_decode_launch(q, kcache, vcache, lengths, out, B, 1, Hq, Hkv, D, Tcap, scale, dtype,
+                            (flags & B200P_OUT_PERM8) ? 1 : 0, ws, ATTN_STATIC_SCRATCH_BYTES, (cudaStream_t)stream);
+}
