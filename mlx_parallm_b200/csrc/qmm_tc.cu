@@ -105,6 +105,11 @@ __device__ unsigned long long g_tc_timing[32];
     tacc[slot] += (unsigned long long)(clock64() - t0_);        \
   } while (0)
 #define TDECL unsigned long long tacc[4] = {0ull, 0ull, 0ull, 0ull}; const long long tstart_ = clock64()
+// section timers of the dequant warps (slots 16..19: LDS fetch, math, TMEM store + wait::st, fence + publish)
+#define TSEC_DECL unsigned long long tsec[4] = {0ull, 0ull, 0ull, 0ull}; long long tmark_ = 0
+#define TSEC_BEGIN() tmark_ = clock64()
+#define TSEC_END(i) do { const long long n_ = clock64(); tsec[i] += (unsigned long long)(n_ - tmark_); tmark_ = n_; } while (0)
+#define TSEC_FLUSH(cond) do { if (blockIdx.x == 0 && (cond)) for (int i_ = 0; i_ < 4; ++i_) g_tc_timing[16 + i_] = tsec[i_]; } while (0)
 #define TFLUSH(base, n, cond)                                                                                   \
   do {                                                                                                          \
     if (blockIdx.x == 0 && (cond)) {                                                                            \
@@ -116,6 +121,10 @@ __device__ unsigned long long g_tc_timing[32];
 #define TWAIT(slot, bar, par) mbar_wait(bar, par)
 #define TDECL
 #define TFLUSH(base, n, cond)
+#define TSEC_DECL
+#define TSEC_BEGIN()
+#define TSEC_END(i)
+#define TSEC_FLUSH(cond)
 #endif
 
 struct TcParams {
@@ -432,6 +441,7 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     uint32_t slot = (uint32_t)kpar, aph = 0;         // A ring slot of this thread's next k-block (it advances by 2) + phase
     uint4 s8 = make_uint4(0u, 0u, 0u, 0u), b8 = s8;
     TDECL;
+    TSEC_DECL;
 
     constexpr int CPK = PKB / 16;                    // 16-byte chunks of packed codes per k-block
     constexpr int KPT = KPS / 2;                     // k-blocks per thread per stage
@@ -440,6 +450,7 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     // producer: the HBM stream then only waits for LDS, not for the dequant math or the MMAs
     auto fetch_stage = [&]() {
       TWAIT(0, full_w(si), (uint32_t)ph);
+      TSEC_BEGIN();
       const uint32_t wsrc = w_ring + si * w_stage_bytes + w_row_off;
 #pragma unroll
       for (int j2 = 0; j2 < KPT; ++j2)
@@ -448,11 +459,13 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
           pk[j2 * CPK + c] = lds128(wsrc + ((((uint32_t)((kpar + 2 * j2) * CPK + c)) ^ w_xor) << 4));
       __syncwarp();
       if (lane == 0) mbar_arrive(empty_w(si));
+      TSEC_END(0);
       if (++si == S) { si = 0; ph ^= 1; }
     };
     // one k-block: 64 codes of row r -> 32 packed 16-bit pairs -> A ring slot
     auto kblock = [&](int j2, uint32_t s2, uint32_t b2) {
       uint32_t o[32];
+      TSEC_BEGIN();
       const uint32_t* pw = reinterpret_cast<const uint32_t*>(pk + j2 * CPK);
       if constexpr (FAST) {
         const SmallScale sc = small_scale_prep(s2, b2);
@@ -462,15 +475,19 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
 #pragma unroll
         for (int c = 0; c < 8; ++c) dequant8<T, BITS, XPERM>(pw + c * (BITS / 4), s2, b2, o + 4 * c);
       }
+      TSEC_END(1);
       TWAIT(2, empty_a(slot), aph ^ 1u);
+      TSEC_BEGIN();
       tc_fence_after();
       if (!(kDebug & 8)) {
         tmem_st32(a_dst + slot * 64, o);
         tmem_st_wait();
       }
+      TSEC_END(2);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(full_a(slot));
+      TSEC_END(3);
       slot += 2;
       if (slot >= a_slots) { slot -= a_slots; aph ^= 1u; }
     };
@@ -557,6 +574,7 @@ qmm_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
       }
     }
     TFLUSH(9, 3, threadIdx.x == 0);                  // 9 full_w, 10 sb_full, 11 empty_a, 12 total (dequant warp 0)
+    TSEC_FLUSH(threadIdx.x == 0);
     // ---- help the epilogue warp of this lane quarter drain the CTA's LAST whole tile (see tc_drain_tile)
     if (p.S == 1 && warp_active && cta < p.items && !(kDebug & 4)) {
       const int n_seg = (p.items - cta + G - 1) / G, seg = n_seg - 1, item = cta + seg * G;

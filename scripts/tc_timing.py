@@ -36,7 +36,9 @@ assert L.b200p_debug_tc_timing(buf) == 0
 v = list(buf)
 names = ["W producer: empty_w", "W producer: sb_empty", "W producer TOTAL", "X producer: empty_x", "X producer TOTAL",
          "MMA: full_x", "MMA: full_a", "MMA: accum_empty", "MMA TOTAL", "dequant w0: full_w", "dequant w0: sb_full",
-         "dequant w0: empty_a", "dequant w0 TOTAL", "epilogue: accum_full", "epilogue TOTAL (to end of tile epilogues)"]
+         "dequant w0: empty_a", "dequant w0 TOTAL", "epilogue: accum_full", "epilogue TOTAL (to end of tile epilogues)",
+         "(unused)", "dequant w0 section: LDS of the codes + slot release", "dequant w0 section: dequant math (+ clock reads)",
+         "dequant w0 section: tcgen05.st + wait::st", "dequant w0 section: fence + syncwarp + arrive"]
 print(f"M={M} N={N} K={K} epi={epi} small={small}: cycles in CTA 0")
 for n, c in zip(names, v):
     print(f"  {n:45s} {c:9d}")
