@@ -2,7 +2,11 @@
 // All HBM- or latency-bound byte work: one pass, 128-bit accesses, no tensor cores.
 #include <type_traits>
 
+#include <cooperative_groups.h>
+
 #include "common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace b200p {
 
@@ -227,6 +231,87 @@ rmsnorm_kernel(const float* __restrict__ x, const T* __restrict__ w, T* __restri
     yr[i] = Tr<T>::from_f(xr[i] * inv * Tr<T>::to_f(w[i]));
 }
 
+// "early" RMSNorm in ONE pass over the row: the row is split over a thread-block cluster of C = H / 2048 CTAs (2 at H = 4096,
+// 4 at 8192), every thread keeps its 16 elements in registers between the sum of squares and the output, and the C partial
+// sums meet through distributed shared memory (each CTA writes its sum into slot [rank] of every CTA, one barrier.cluster).
+// The generic kernel above reads the row twice, and with 32 registers per thread its second read is four dependent round
+// trips to L2 (a resident GEMM CTA leaves no L1).  Same launch contract as the NT = 128 variant: 128 threads x 32 registers,
+// PDL attribute, dependents released before its own wait.  The norm weights do not depend on the previous kernel and are
+// loaded before the wait.  The sum is taken in (warp, CTA rank) order: reproducible, not bit-identical to the generic kernel's.
+template <typename T>
+__global__ void __launch_bounds__(128, 16)
+rmsnorm_cluster_kernel(const float* __restrict__ x, const T* __restrict__ w, T* __restrict__ y, int64_t H, float eps, int perm) {
+  static_assert(sizeof(T) == 2, "16-bit outputs only");
+  constexpr int NG = 2;                            // groups of 8 consecutive elements per thread
+  __shared__ float s_warp[4];
+  __shared__ float s_cta[8];
+  cg::cluster_group cluster = cg::this_cluster();
+  const unsigned rank = cluster.block_rank(), C = cluster.num_blocks();
+  const int tid = threadIdx.x;
+  pdl_launch_dependents();
+  const int64_t row = blockIdx.x / C;
+  uint4 wv[NG];
+#pragma unroll
+  for (int j = 0; j < NG; ++j) wv[j] = reinterpret_cast<const uint4*>(w)[(j * C + rank) * 128 + tid];
+  pdl_wait();
+  const float4* xr = reinterpret_cast<const float4*>(x + row * H);
+  float4 a[NG], b[NG];
+#pragma unroll
+  for (int j = 0; j < NG; ++j) {
+    const int64_t g = (int64_t)(j * C + rank) * 128 + tid;
+    a[j] = xr[2 * g];
+    b[j] = xr[2 * g + 1];
+  }
+  float ss = 0.f;
+#pragma unroll
+  for (int j = 0; j < NG; ++j)
+    ss += a[j].x * a[j].x + a[j].y * a[j].y + a[j].z * a[j].z + a[j].w * a[j].w + b[j].x * b[j].x + b[j].y * b[j].y +
+          b[j].z * b[j].z + b[j].w * b[j].w;
+  ss = warp_sum(ss);
+  if ((tid & 31) == 0) s_warp[tid >> 5] = ss;
+  __syncthreads();
+  if (tid < (int)C) *cluster.map_shared_rank(&s_cta[rank], tid) = (s_warp[0] + s_warp[1]) + (s_warp[2] + s_warp[3]);
+  cluster.sync();
+  float tot = 0.f;
+  for (unsigned r = 0; r < C; ++r) tot += s_cta[r];
+  const float inv = 1.0f / sqrtf(tot / (float)H + eps);
+  uint4* yr = reinterpret_cast<uint4*>(y + row * H);
+#pragma unroll
+  for (int j = 0; j < NG; ++j) {
+    const T* wp = reinterpret_cast<const T*>(&wv[j]);
+    const float v[8] = {a[j].x, a[j].y, a[j].z, a[j].w, b[j].x, b[j].y, b[j].z, b[j].w};
+    __align__(16) T o[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const T r = Tr<T>::from_f(v[e] * inv * Tr<T>::to_f(wp[e]));
+      // PERM8: element e of the group sits at position [0,4,1,5,2,6,3,7]^-1 = perm8_pos(e) (compile-time after unrolling)
+      if (perm) o[perm8_pos(e)] = r; else o[e] = r;
+    }
+    yr[(int64_t)(j * C + rank) * 128 + tid] = *reinterpret_cast<uint4*>(o);
+  }
+}
+
+template <typename T>
+static cudaError_t launch_rmsnorm_cluster(int C, int64_t M, cudaStream_t st, const float* x, const void* w, void* y, int64_t H,
+                                          float eps, int perm) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(M * C));
+  cfg.blockDim = dim3(128);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)C;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 2;
+  return cudaLaunchKernelEx(&cfg, rmsnorm_cluster_kernel<T>, x, (const T*)w, (T*)y, H, eps, perm);
+}
+int sm_count();
+
 }  // namespace b200p
 
 extern "C" int b200p_rmsnorm(const float* x, const void* w, void* y, int64_t M, int64_t H, float eps,
@@ -244,6 +329,17 @@ extern "C" int b200p_rmsnorm(const float* x, const void* w, void* y, int64_t M, 
   // do not, and the 128-thread CTA is the slower norm (B=1 T=8192: 2.38 -> 2.43 ms) -- profiles/r2_run29_*
   static const int early_env = [] { const char* e = getenv("B200P_RMS_EARLY"); return e ? atoi(e) : -1; }();
   const bool early = early_env >= 0 ? early_env != 0 : M >= 16;
+  // one-pass cluster variant of the early norm: 16-bit rows of 2048 * C elements, C in {1, 2, 4, 8}, one CTA per SM at most
+  static const int cluster_env = [] { const char* e = getenv("B200P_RMS_CLUSTER"); return e ? atoi(e) : 1; }();
+  const int64_t C = H / 2048;
+  if (early && cluster_env && dtype != B200P_F32 && H % 2048 == 0 && (C == 1 || C == 2 || C == 4 || C == 8) &&
+      M * C <= sm_count() && aligned(w, 16)) {
+    cudaError_t e = dtype == B200P_F16
+        ? launch_rmsnorm_cluster<__half>((int)C, M, (cudaStream_t)stream, x, w, y, H, eps, perm)
+        : launch_rmsnorm_cluster<__nv_bfloat16>((int)C, M, (cudaStream_t)stream, x, w, y, H, eps, perm);
+    if (e != cudaSuccess) return cuda_fail(e, "rmsnorm_cluster_kernel");
+    return B200P_OK;
+  }
   if (early) {
     B200P_DISPATCH_DTYPE(dtype, T, (launch_pdl_opt(true, rmsnorm_kernel<T, 128>, (unsigned)M, 128, 0, (cudaStream_t)stream,
                                        x, (const T*)w, (T*)y, H, eps, perm)));

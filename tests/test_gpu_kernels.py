@@ -189,6 +189,29 @@ def test_rmsnorm(ops, dtype):
     assert rel_err(y.float().cpu().numpy(), exp) < {"float32": 1e-6, "float16": 1.1e-3, "bfloat16": 8.1e-3}[dtype]
 
 
+@pytest.mark.parametrize("dtype,M,H", [
+    ("float16", 8, 4096),       # below 16 rows: the 256-thread kernel
+    ("float16", 64, 4096),      # early one-pass kernel, cluster of 2 (Llama-3-8B decode at B=64)
+    ("bfloat16", 32, 8192),     # cluster of 4 (70B-class)
+    ("float16", 16, 2048),      # cluster of 1
+    ("bfloat16", 64, 5120),     # Qwen3-14B: 5120 is not a multiple of 2048 -> early two-pass kernel
+    ("float16", 100, 4096),     # 100 rows x 2 CTAs exceed the SMs -> early two-pass kernel
+])
+@pytest.mark.parametrize("perm", [False, True])
+def test_rmsnorm_variants_at_decode_sizes(ops, dtype, M, H, perm):
+    """Every RMSNorm variant the dispatcher can pick (csrc/elementwise.cu), PERM8 and plain, against the oracle."""
+    rng = np.random.default_rng(31)
+    x = rng.standard_normal((M, H)).astype(np.float32) * 3
+    x[1] *= 50.0                                    # rows of very different norms
+    w = ref.round_to(1 + 0.1 * rng.standard_normal(H), dtype)
+    y = ops.rmsnorm(torch.from_numpy(x).cuda(), t_(w, dtype), 1e-5, out_perm=perm).float().cpu().numpy()
+    if perm:                                        # undo [0,4,1,5,2,6,3,7] inside every aligned group of 8
+        y = y.reshape(M, H // 8, 8)[:, :, [0, 2, 4, 6, 1, 3, 5, 7]].reshape(M, H)
+    exp = ref.rms_norm(x, w, 1e-5, dtype)
+    for r in range(M):                              # per row: a row of small norm must not hide behind a large one
+        assert rel_err(y[r], exp[r]) < {"float16": 1.1e-3, "bfloat16": 8.1e-3}[dtype], r
+
+
 @pytest.mark.parametrize("dtype,D,qk_norm", [("float16", 128, False), ("bfloat16", 128, True), ("float32", 16, False), ("float16", 64, True)])
 def test_rope_kv_append(ops, dtype, D, qk_norm):
     rng = np.random.default_rng(4)
