@@ -107,8 +107,9 @@ size_t b200p_qmm_workspace_bytes(int64_t M, int64_t N, int64_t K);
 /* 1 if the tcgen05 tile path can run this call, else 0 */
 int b200p_qmm_tensor_supported(int64_t M, int64_t N, int64_t K, int group_size, int bits, int dtype,
                                int epilogue);
-/* force a path for tests/benchmarks: 0 = auto, 1 = CUDA-core GEMV only, 2 = tcgen05 tile kernel only, 3 = mma.sync
- * GEMV only (2 and 3: error if the call is unsupported on that path) */
+/* force a path for tests/benchmarks: 0 = auto, 1 = CUDA-core GEMV only, 2 = tcgen05 tile kernels only, 3 = mma.sync
+ * GEMV only, 4 = mma.sync small-matrix GEMM only (csrc/qmm_mma.cu: ADD_RESIDUAL, M <= 64, N % 128 == 0, K % 256 == 0)
+ * (2, 3 and 4: error if the call is unsupported on that path) */
 int b200p_qmm_set_path(int path);
 /* smallest M routed to the tensor path in auto mode (default 1: measured, scripts/qmm_sweep.py, profiles/r1_run11_qmm_sweep_gemv_vs_tensor.txt) */
 int b200p_qmm_set_min_tensor_m(int m);

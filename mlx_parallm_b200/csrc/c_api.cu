@@ -33,6 +33,9 @@ int qmm_sk_launch(const void* x, const uint32_t* w, const void* s, const void* b
                   int64_t K, int64_t ldx, int64_t ldy, int bits, int dtype, int flags, cudaStream_t st);
 void qmm_tc_set_min_m(int m);
 bool qmv_mma_supported(int64_t M, int64_t N, int64_t K, int gs, int bits, int dtype, int epi);
+bool qmm_mma_supported(int64_t M, int64_t N, int64_t K, int gs, int bits, int dtype, int epi, const void* y, int64_t ldy);
+int qmm_mma_launch(const void* x, const uint32_t* w, const void* s, const void* b, void* y, int64_t M, int64_t N, int64_t K,
+                   int64_t ldx, int64_t ldy, int dtype, int flags, cudaStream_t st);
 int qmv_mma_launch(const void* x, const uint32_t* w, const void* s, const void* b, void* y, int64_t M, int64_t N, int64_t K,
                    int64_t ldx, int64_t ldy, int dtype, int epi, int flags, cudaStream_t st);
 int attn_generic_launch(const void* q, const void* kc, const void* vc, const int32_t* lengths, void* out,
@@ -48,7 +51,14 @@ int attn_prefill_launch(const void* q, const void* kc, const void* vc, const int
                         int Hq, int Hkv, int D, int64_t Tcap, float scale, int dtype, int out_perm, cudaStream_t st);
 
 static const bool g_use_sk = [] { const char* e = getenv("B200P_QMM_SK"); return !e || atoi(e) != 0; }();
-static int g_qmm_path = 0;   // 0 auto, 1 CUDA-core gemv, 2 tcgen05 tiles, 3 mma.sync gemv
+static int g_qmm_path = 0;   // 0 auto, 1 CUDA-core gemv, 2 tcgen05 tiles, 3 mma.sync gemv, 4 mma.sync small-matrix GEMM
+// pipeline-free mma.sync GEMM (qmm_mma.cu) for the accumulate epilogue above the GEMV's rows: matrices up to this many weights
+// (q|k|v 25 M and o_proj 17 M of Llama-3-8B, every tensor-parallel shard; down_proj 59 M and gate|up stay on the tile kernels)
+static long long g_mma_max_weights = [] { const char* e = getenv("B200P_MMA_MAX_WEIGHTS"); return e ? atoll(e) : (1ll << 25); }();
+// ... and up to this many rows: measured against the tile kernels (profiles/r2_run35_small_gemm_paths.txt) it wins at 8 and 16
+// rows (q|k|v 6.2 vs 7.2 us, o_proj 4.3 vs 5.7, TP=8 shards 2.6-4.1 vs 3.8-5.3), ties at 32 and loses at 64, where it is bound
+// by the mma.sync rate (q|k|v 14.6 vs 8.9 us)
+static int g_mma_max_m = [] { const char* e = getenv("B200P_MMA_MAX_M"); return e ? atoi(e) : 16; }();
 // Auto rule for the mma.sync GEMV, from the measured three-way sweep (profiles/r1_run12_qmm_sweep_three_paths.txt, us per
 // launch in a CUDA graph): it wins where the tile kernel's fixed cost dominates -- M <= 4 and matrices up to ~32 M weights
 // (q|k|v 6.4 vs 8.4 us, o_proj 5.2 vs 6.5 us at M = 1) -- and loses on the big streams (gate|up 23.9 vs 22.4 us) and as M
@@ -118,7 +128,7 @@ extern "C" int b200p_qmm_set_min_tensor_m(int m) {
 }
 
 extern "C" int b200p_qmm_set_path(int path) {
-  B200P_REQUIRE(path >= 0 && path <= 3, B200P_ERR_ARG, "path must be 0..3");
+  B200P_REQUIRE(path >= 0 && path <= 4, B200P_ERR_ARG, "path must be 0..4");
   g_qmm_path = path;
   return B200P_OK;
 }
@@ -172,6 +182,10 @@ extern "C" int b200p_qmm(const void* x, const uint32_t* w, const void* scales, c
   if (mma_ok && (g_qmm_path == 3 || (g_qmm_path == 0 && M <= g_gemv_max_m &&
                                      N * K <= (M <= 2 ? 2 * g_gemv_max_weights : g_gemv_max_weights))))
     return qmv_mma_launch(x, w, scales, biases, y, M, N, K, ldx, ldy, dtype, epilogue, flags, st);
+  const bool gm_ok = qmm_mma_supported(M, N, K, group_size, bits, dtype, epilogue, y, ldy) && aligned(w, 32);
+  if (g_qmm_path == 4) B200P_REQUIRE(gm_ok, B200P_ERR_ARG, "mma.sync small-matrix GEMM forced but unsupported for this call");
+  if (gm_ok && (g_qmm_path == 4 || (g_qmm_path == 0 && M > g_gemv_max_m && M <= g_mma_max_m && N * K <= g_mma_max_weights)))
+    return qmm_mma_launch(x, w, scales, biases, y, M, N, K, ldx, ldy, dtype, flags, st);
   const bool tc_ok = qmm_tc_supported(M, N, K, group_size, bits, dtype, epilogue);
   if (g_qmm_path == 2) {
     B200P_REQUIRE(tc_ok, B200P_ERR_ARG, "tensor path forced but unsupported for this call");

@@ -26,6 +26,11 @@ SHAPES = {   # name, N, K, epilogue (0 store 16-bit, 1 store f32, 2 += f32, 3 si
     # the fused projections through the fp32 accumulate epilogue (stream-K kernel) instead of their 16-bit epilogues
     "llama3-8b-acc": [("gateup", 28672, 4096, 2, 4), ("head", 128256, 4096, 2, 4), ("gateup-tp2", 14336, 4096, 2, 4),
                       ("gateup-tp4", 7168, 4096, 2, 4), ("gateup-tp8", 3584, 4096, 2, 4), ("head-tp8", 16032, 4096, 2, 4)],
+    # accumulate-epilogue matrices of one GPU and of the TP=2 / TP=8 shards (the candidates of the mma.sync small-matrix GEMM)
+    "small-acc": [("qkv", 6144, 4096, 2, 4), ("o", 4096, 4096, 2, 4), ("down", 4096, 14336, 2, 4),
+                  ("qkv-tp2", 3072, 4096, 2, 4), ("o-tp2", 4096, 2048, 2, 4), ("down-tp2", 4096, 7168, 2, 4),
+                  ("qkv-tp8", 768, 4096, 2, 4), ("o-tp8", 4096, 512, 2, 4), ("gateup-tp8", 3584, 4096, 2, 4),
+                  ("down-tp8", 4096, 1792, 2, 4)],
     "llama3-8b-tp2": [("qkv", 3072, 4096, 0, 4), ("o", 4096, 2048, 2, 4), ("gateup", 14336, 4096, 3, 4), ("down", 4096, 7168, 2, 4),
                       ("head", 64128, 4096, 1, 4)],
     "llama3-8b-tp4": [("qkv", 1536, 4096, 0, 4), ("o", 4096, 1024, 2, 4), ("gateup", 7168, 4096, 3, 4), ("down", 4096, 3584, 2, 4),
@@ -39,8 +44,9 @@ try:
     peak = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")))["hbm_gbs"]
 except Exception:
     pass
-_lib.check(L.b200p_qmm_set_path(2))
-print(f"model {model}; us per launch (GB/s, fraction of {peak:.0f} GB/s): 3-op dequant | small-scale dequant")
+PATH = int(os.environ.get("QMM_BENCH_PATH", "2"))      # 2 tcgen05 tile kernels (default), 4 mma.sync small-matrix GEMM, 0 auto
+_lib.check(L.b200p_qmm_set_path(PATH))
+print(f"model {model}; path {PATH}; us per launch (GB/s, fraction of {peak:.0f} GB/s): 3-op dequant | small-scale dequant")
 for name, N, K, epi, bits in SHAPES:
     if only and name not in only:
         continue

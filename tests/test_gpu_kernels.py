@@ -540,7 +540,53 @@ def test_qmm_mma_gemv_agrees_with_the_other_paths_and_is_the_auto_choice(ops):
     a, _ = qmm_case(ops, 4, 512, 2048, 4, "float16", 1, seed=9, path=0)
     assert rel_err(m, t) < 1e-5 and rel_err(m, g) < 1e-3
     assert np.array_equal(a, m)                          # small matrix, M <= 4: auto == the mma.sync GEMV, bit for bit
-    assert _lib.lib().b200p_qmm_set_path(4) == -1
+    assert _lib.lib().b200p_qmm_set_path(5) == -1
+
+
+# ---------------------------------------------------------------- mma.sync small-matrix GEMM (csrc/qmm_mma.cu)
+@pytest.mark.parametrize("dtype,M,N,K", [
+    ("float16", 5, 128, 512),        # NT = 1, two steps, no K split
+    ("float16", 8, 256, 1024),
+    ("bfloat16", 16, 128, 2048),     # NT = 2
+    ("float16", 23, 384, 1024),      # NT = 4 with zero-filled token lines
+    ("float16", 64, 256, 2048),      # NT = 8, K split
+    ("bfloat16", 64, 128, 256),      # a single step
+    ("float16", 33, 1024, 4096),     # many row blocks x splits: partial sums meet through the bulk reduce-add
+])
+def test_qmm_mma_small_matrix_gemm_matches_oracle(ops, dtype, M, N, K):
+    from mlx_parallm_b200 import _lib
+    got, exp = qmm_case(ops, M, N, K, 4, dtype, _lib.EPI_ADD_RESIDUAL, seed=M + N, path=4, ragged_ld=(M == 23))
+    assert rel_err(got, exp) < {"float16": 1e-3, "bfloat16": 6e-3}[dtype]     # bound: rounding of the dequantised weights
+    auto, _ = qmm_case(ops, M, N, K, 4, dtype, _lib.EPI_ADD_RESIDUAL, seed=M + N, path=0)
+    assert rel_err(auto, got) < 1e-5                     # auto (this kernel up to 16 rows, stream-K tiles above): same dequantised
+                                                         # weights, fp32 sums in another order
+
+
+def test_qmm_mma_perm8_activations_and_unsupported_shapes(ops):
+    from mlx_parallm_b200 import _lib
+    from test_gpu_layouts import to_perm8
+    rng = np.random.default_rng(77)
+    M, N, K = 64, 256, 1024
+    wq = rng.integers(0, 2 ** 32, (N, K // 8), dtype=np.uint32)
+    s = ref.round_to(rng.uniform(0.5, 1.5, (N, K // 64)) * (2 / 15) / np.sqrt(K), "float16")
+    b = ref.round_to(-s * 7.5, "float16")
+    x = ref.round_to(rng.standard_normal((M, K)), "float16")
+    _lib.check(_lib.lib().b200p_qmm_set_path(4))
+    try:
+        nat = torch.zeros((M, N), dtype=torch.float32, device="cuda")
+        per = torch.zeros((M, N), dtype=torch.float32, device="cuda")
+        ops.qmm(t_(x, "float16"), w_(wq), t_(s, "float16"), t_(b, "float16"), 64, 4, _lib.EPI_ADD_RESIDUAL, out=nat)
+        ops.qmm(t_(to_perm8(x), "float16"), w_(wq), t_(s, "float16"), t_(b, "float16"), 64, 4, _lib.EPI_ADD_RESIDUAL, out=per,
+                x_perm=True)
+        assert rel_err(per.cpu().numpy(), nat.cpu().numpy()) < 1e-6
+        assert rel_err(nat.cpu().numpy(), ref.quantized_matmul(x, wq, s, b, 64, 4)) < 1e-3
+        with pytest.raises(_lib.B200PError):                  # N not a multiple of 128: forced path refuses, nothing is launched
+            ops.qmm(t_(x, "float16"), w_(wq[:96]), t_(s[:96], "float16"), t_(b[:96], "float16"), 64, 4, _lib.EPI_ADD_RESIDUAL,
+                    out=nat[:, :96].contiguous())
+        with pytest.raises(_lib.B200PError):                  # STORE epilogue: not this kernel's
+            ops.qmm(t_(x, "float16"), w_(wq), t_(s, "float16"), t_(b, "float16"), 64, 4, _lib.EPI_STORE_F32)
+    finally:
+        _lib.lib().b200p_qmm_set_path(0)
 
 
 # ---------------------------------------------------------------- split-K tensor decode attention
