@@ -325,15 +325,18 @@ extern "C" int b200p_rmsnorm(const float* x, const void* w, void* y, int64_t M, 
   B200P_REQUIRE(aligned(x, 16) && aligned(y, 16) && H % 4 == 0, B200P_ERR_ALIGN,
                 "rmsnorm needs 16-byte aligned rows (H %% 4 == 0)");
   if (M == 0) return B200P_OK;
-  // auto: from 16 rows on the next kernel is a tile GEMM that profits (B=64 T=256: 2.91 -> 2.87 ms); below, the GEMV kernels
-  // do not, and the 128-thread CTA is the slower norm (B=1 T=8192: 2.38 -> 2.43 ms) -- profiles/r2_run29_*
+  // Which norm.  The one-pass cluster form (16-bit rows of 2048 * C elements, C in {1, 2, 4, 8}, at most one CTA per SM) is an
+  // "early" kernel and wins at every row count (B=1 T=8192 2.29 -> 2.22 ms, B=8 3.46 -> 3.41, B=64 T=256 2.88 -> 2.86:
+  // profiles/r2_run33_*, r2_run37_*).  Where it does not apply, the two-pass early kernel pays from 16 rows on (the next kernel
+  // is then a tile GEMM that streams weights while it waits: B=64 T=256 2.91 -> 2.87 ms) and loses below (a 128-thread CTA is
+  // the slower norm and the GEMV after it gains nothing: B=1 T=8192 2.38 -> 2.43 ms, profiles/r2_run29_*).
   static const int early_env = [] { const char* e = getenv("B200P_RMS_EARLY"); return e ? atoi(e) : -1; }();
-  const bool early = early_env >= 0 ? early_env != 0 : M >= 16;
-  // one-pass cluster variant of the early norm: 16-bit rows of 2048 * C elements, C in {1, 2, 4, 8}, one CTA per SM at most
   static const int cluster_env = [] { const char* e = getenv("B200P_RMS_CLUSTER"); return e ? atoi(e) : 1; }();
   const int64_t C = H / 2048;
-  if (early && cluster_env && dtype != B200P_F32 && H % 2048 == 0 && (C == 1 || C == 2 || C == 4 || C == 8) &&
-      M * C <= sm_count() && aligned(w, 16)) {
+  const bool cluster_ok = cluster_env && dtype != B200P_F32 && H % 2048 == 0 && (C == 1 || C == 2 || C == 4 || C == 8) &&
+                          M * C <= sm_count() && aligned(w, 16);
+  const bool early = early_env >= 0 ? early_env != 0 : (M >= 16 || cluster_ok);
+  if (early && cluster_ok) {
     cudaError_t e = dtype == B200P_F16
         ? launch_rmsnorm_cluster<__half>((int)C, M, (cudaStream_t)stream, x, w, y, H, eps, perm)
         : launch_rmsnorm_cluster<__nv_bfloat16>((int)C, M, (cudaStream_t)stream, x, w, y, H, eps, perm);

@@ -190,7 +190,9 @@ def test_rmsnorm(ops, dtype):
 
 
 @pytest.mark.parametrize("dtype,M,H", [
-    ("float16", 8, 4096),       # below 16 rows: the 256-thread kernel
+    ("float16", 8, 4096),       # one-pass cluster kernel at a few rows
+    ("float16", 1, 4096),
+    ("bfloat16", 8, 5120),      # below 16 rows and no cluster form: the 256-thread kernel
     ("float16", 64, 4096),      # early one-pass kernel, cluster of 2 (Llama-3-8B decode at B=64)
     ("bfloat16", 32, 8192),     # cluster of 4 (70B-class)
     ("float16", 16, 2048),      # cluster of 1
@@ -202,7 +204,7 @@ def test_rmsnorm_variants_at_decode_sizes(ops, dtype, M, H, perm):
     """Every RMSNorm variant the dispatcher can pick (csrc/elementwise.cu), PERM8 and plain, against the oracle."""
     rng = np.random.default_rng(31)
     x = rng.standard_normal((M, H)).astype(np.float32) * 3
-    x[1] *= 50.0                                    # rows of very different norms
+    x[M // 2] *= 50.0                               # rows of very different norms
     w = ref.round_to(1 + 0.1 * rng.standard_normal(H), dtype)
     y = ops.rmsnorm(torch.from_numpy(x).cuda(), t_(w, dtype), 1e-5, out_perm=perm).float().cpu().numpy()
     if perm:                                        # undo [0,4,1,5,2,6,3,7] inside every aligned group of 8
