@@ -58,6 +58,7 @@ static long long g_mma_max_weights = [] { const char* e = getenv("B200P_MMA_MAX_
 // ... and up to this many rows: measured against the tile kernels (profiles/r2_run35_small_gemm_paths.txt) it wins at 8 and 16
 // rows (q|k|v 6.2 vs 7.2 us, o_proj 4.3 vs 5.7, TP=8 shards 2.6-4.1 vs 3.8-5.3), ties at 32 and loses at 64, where it is bound
 // by the mma.sync rate (q|k|v 14.6 vs 8.9 us)
+static int g_gemv_silu_max_m = [] { const char* e = getenv("B200P_GEMV_SILU_MAX_M"); return e ? atoi(e) : 0; }();
 static int g_mma_max_m = [] { const char* e = getenv("B200P_MMA_MAX_M"); return e ? atoi(e) : 16; }();
 // Auto rule for the mma.sync GEMV, from the measured three-way sweep (profiles/r1_run12_qmm_sweep_three_paths.txt, us per
 // launch in a CUDA graph): it wins where the tile kernel's fixed cost dominates -- M <= 4 and matrices up to ~32 M weights
@@ -174,12 +175,17 @@ extern "C" int b200p_qmm(const void* x, const uint32_t* w, const void* scales, c
   if (M == 0) return B200P_OK;
   PdlClass pdl_cls(64);
   cudaStream_t st = (cudaStream_t)stream;
-  const bool mma_ok = qmv_mma_supported(M, N, K, group_size, bits, dtype, epilogue) && aligned(y, 4) && aligned(w, 32) &&
-                      !(flags & B200P_Y_PERM8);
+  // (SILU_MUL through the GEMV: 16-bit output, PERM8 allowed; the other GEMV epilogues write fp32 in the natural order)
+  const bool mma_ok = qmv_mma_supported(M, N, K, group_size, bits, dtype, epilogue) && aligned(w, 32) &&
+                      (epilogue == B200P_EPI_SILU_MUL ? aligned(y, 2) : (aligned(y, 4) && !(flags & B200P_Y_PERM8)));
   if (g_qmm_path == 3) B200P_REQUIRE(mma_ok, B200P_ERR_ARG, "mma.sync GEMV forced but unsupported for this call");
   // up to two rows the GEMV also wins on matrices of twice that size (down_proj 4096 x 14336: 12.8 vs 14.1 us at M = 1,
   // profiles/r1_run34_gemv_splits.txt); gate|up (117 M weights) stays on the tile kernel
-  if (mma_ok && (g_qmm_path == 3 || (g_qmm_path == 0 && M <= g_gemv_max_m &&
+  // gate|up with the fused silu(gate) * up epilogue through the GEMV (rows paired gate / up, no K split): up to
+  // B200P_GEMV_SILU_MAX_M rows, any size; 0 = never (the default: see profiles/r2_run39_*)
+  if (mma_ok && epilogue == B200P_EPI_SILU_MUL && g_qmm_path == 0 && M <= g_gemv_silu_max_m)
+    return qmv_mma_launch(x, w, scales, biases, y, M, N, K, ldx, ldy, dtype, epilogue, flags, st);
+  if (mma_ok && (g_qmm_path == 3 || (g_qmm_path == 0 && epilogue != B200P_EPI_SILU_MUL && M <= g_gemv_max_m &&
                                      N * K <= (M <= 2 ? 2 * g_gemv_max_weights : g_gemv_max_weights))))
     return qmv_mma_launch(x, w, scales, biases, y, M, N, K, ldx, ldy, dtype, epilogue, flags, st);
   const bool gm_ok = qmm_mma_supported(M, N, K, group_size, bits, dtype, epilogue, y, ldy) && aligned(w, 32);

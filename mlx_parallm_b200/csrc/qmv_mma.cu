@@ -46,18 +46,23 @@ __device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], 
 constexpr int QM_WARPS = 4;
 constexpr int QM_STEP_K = 256;
 
-// NT: n-tiles of 8 tokens (M <= 8*NT).  ATOMIC: combine with red.add (ADD_RESIDUAL / split-K) else plain fp32 store.
-template <typename T, int NT, bool XPERM, bool ATOMIC>
+// NT: n-tiles of 8 tokens (M <= 8*NT).  MODE 0: plain fp32 store; 1: combine with red.add (ADD_RESIDUAL / split-K);
+// 2: SILU_MUL -- the warp's second row block is not "rows + 8" but the UP rows that match its 8 GATE rows (row n of gate_proj
+// is row N/2 + n of the fused matrix), so every lane holds the gate and the up sum of the same (row, token) and stores
+// silu(g) * u as one 16-bit value, in the PERM8 column order if y_perm; never K-split.
+template <typename T, int NT, bool XPERM, int MODE>
 __global__ void __launch_bounds__(QM_WARPS * 32)
 qmv_mma_kernel(const T* __restrict__ x, const uint32_t* __restrict__ w, const T* __restrict__ scales,
                const T* __restrict__ biases, float* __restrict__ y, int M, int64_t N, int64_t K, int64_t ldx, int64_t ldy,
-               int splits, int steps_per_split) {
+               int splits, int steps_per_split, int y_perm) {
+  constexpr bool ATOMIC = MODE == 1;
+  constexpr bool SILU = MODE == 2;
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const int64_t wid = (int64_t)blockIdx.x * QM_WARPS + (threadIdx.x >> 5);
   const int64_t rg = wid / splits;
   const int ks = (int)(wid - rg * splits);
-  if (rg * 16 >= N) return;
-  const int64_t r0 = rg * 16 + g, r1 = r0 + 8;
+  if (SILU ? rg * 8 >= N / 2 : rg * 16 >= N) return;
+  const int64_t r0 = SILU ? rg * 8 + g : rg * 16 + g, r1 = SILU ? N / 2 + r0 : r0 + 8;
   const int64_t wrow = K / 8;                 // uint32 words per weight row
   const int64_t ng = K / 64;
   const int64_t total_steps = K / QM_STEP_K;
@@ -146,6 +151,12 @@ qmv_mma_kernel(const T* __restrict__ x, const uint32_t* __restrict__ w, const T*
     for (int j = 0; j < 2; ++j) {
       const int tok = n * 8 + 2 * t + j;
       if (tok < M) {
+        if constexpr (SILU) {
+          const float gte = acc[n][j], up = acc[n][2 + j];
+          T* yt = reinterpret_cast<T*>(y) + (int64_t)tok * ldy;
+          yt[y_perm ? perm8_pos((int)r0) : (int)r0] = Tr<T>::from_f(gte / (1.0f + __expf(-gte)) * up);   // silu_tc of tc_ptx.cuh
+          continue;
+        }
         float* yr = y + (int64_t)tok * ldy;
         if (ATOMIC) {
           atomicAdd(yr + r0, acc[n][j]);
@@ -164,13 +175,15 @@ bool qmv_mma_supported(int64_t M, int64_t N, int64_t K, int gs, int bits, int dt
   if (dtype != B200P_F16 && dtype != B200P_BF16) return false;
   if (M < 1 || M > 16) return false;
   if (K % QM_STEP_K != 0 || N % 16 != 0) return false;
+  if (epi == B200P_EPI_SILU_MUL) return true;                        // N % 16 == 0 -> N / 2 gate rows in whole groups of 8
   return epi == B200P_EPI_STORE_F32 || epi == B200P_EPI_ADD_RESIDUAL;
 }
 
 template <typename T>
 static int launch_qmv_mma(const void* x, const uint32_t* w, const void* s, const void* b, void* y, int64_t M, int64_t N,
-                          int64_t K, int64_t ldx, int64_t ldy, int epi, bool xperm, cudaStream_t st) {
-  const int64_t row_groups = N / 16;
+                          int64_t K, int64_t ldx, int64_t ldy, int epi, bool xperm, bool yperm, cudaStream_t st) {
+  const bool silu = epi == B200P_EPI_SILU_MUL;
+  const int64_t row_groups = silu ? N / 2 / 8 : N / 16;          // SILU_MUL: a warp takes 8 gate rows and their 8 up rows
   const int64_t total_steps = K / QM_STEP_K;
   // Split-K so that every SM holds ~16 warps, but never a grid that spills a few CTAs into a second wave (4096 x 14336 at ten
   // splits was 640 CTAs on 592 slots: 1.08 waves, 30 % slower than 8 splits in one wave): among the split counts pick the
@@ -200,17 +213,17 @@ static int launch_qmv_mma(const void* x, const uint32_t* w, const void* s, const
   splits = (total_steps + sps - 1) / sps;
   const int64_t warps = row_groups * splits;
   dim3 grid((unsigned)((warps + QM_WARPS - 1) / QM_WARPS)), block(QM_WARPS * 32);
-  const bool atomic = epi == B200P_EPI_ADD_RESIDUAL;
-#define GO(NT_, XP_, AT_)                                                                                                \
-  launch_pdl(qmv_mma_kernel<T, NT_, XP_, AT_>, grid, block, 0, st, (const T*)x, w, (const T*)s, (const T*)b, (float*)y,   \
-             (int)M, N, K, ldx, ldy, (int)splits, (int)sps)
+  const int mode = silu ? 2 : (epi == B200P_EPI_ADD_RESIDUAL ? 1 : 0);
+#define GO(NT_, XP_, MD_)                                                                                                \
+  launch_pdl(qmv_mma_kernel<T, NT_, XP_, MD_>, grid, block, 0, st, (const T*)x, w, (const T*)s, (const T*)b, (float*)y,   \
+             (int)M, N, K, ldx, ldy, (int)splits, (int)sps, yperm ? 1 : 0)
+#define GO_MODE(NT_, XP_) do { if (mode == 2) GO(NT_, XP_, 2); else if (mode == 1) GO(NT_, XP_, 1); else GO(NT_, XP_, 0); } while (0)
   if (M <= 8) {
-    if (xperm) { if (atomic) GO(1, true, true); else GO(1, true, false); }
-    else { if (atomic) GO(1, false, true); else GO(1, false, false); }
+    if (xperm) GO_MODE(1, true); else GO_MODE(1, false);
   } else {
-    if (xperm) { if (atomic) GO(2, true, true); else GO(2, true, false); }
-    else { if (atomic) GO(2, false, true); else GO(2, false, false); }
+    if (xperm) GO_MODE(2, true); else GO_MODE(2, false);
   }
+#undef GO_MODE
 #undef GO
   B200P_LAUNCH_CHECK("qmv_mma_kernel");
   return B200P_OK;
@@ -218,10 +231,11 @@ static int launch_qmv_mma(const void* x, const uint32_t* w, const void* s, const
 
 int qmv_mma_launch(const void* x, const uint32_t* w, const void* s, const void* b, void* y, int64_t M, int64_t N, int64_t K,
                    int64_t ldx, int64_t ldy, int dtype, int epi, int flags, cudaStream_t st) {
-  B200P_REQUIRE(aligned(s, 2) && aligned(b, 2) && aligned(y, 4) && aligned(w, 32), B200P_ERR_ALIGN, "bad alignment (weights: 32 bytes)");
-  const bool xperm = (flags & B200P_X_PERM8) != 0;
-  if (dtype == B200P_F16) return launch_qmv_mma<__half>(x, w, s, b, y, M, N, K, ldx, ldy, epi, xperm, st);
-  return launch_qmv_mma<__nv_bfloat16>(x, w, s, b, y, M, N, K, ldx, ldy, epi, xperm, st);
+  B200P_REQUIRE(aligned(s, 2) && aligned(b, 2) && aligned(y, epi == B200P_EPI_SILU_MUL ? 2 : 4) && aligned(w, 32), B200P_ERR_ALIGN,
+                "bad alignment (weights: 32 bytes)");
+  const bool xperm = (flags & B200P_X_PERM8) != 0, yperm = (flags & B200P_Y_PERM8) != 0;
+  if (dtype == B200P_F16) return launch_qmv_mma<__half>(x, w, s, b, y, M, N, K, ldx, ldy, epi, xperm, yperm, st);
+  return launch_qmv_mma<__nv_bfloat16>(x, w, s, b, y, M, N, K, ldx, ldy, epi, xperm, yperm, st);
 }
 
 }  // namespace b200p

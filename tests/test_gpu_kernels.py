@@ -545,6 +545,17 @@ def test_qmm_mma_gemv_agrees_with_the_other_paths_and_is_the_auto_choice(ops):
     assert _lib.lib().b200p_qmm_set_path(5) == -1
 
 
+@pytest.mark.parametrize("dtype,M", [("float16", 1), ("bfloat16", 3), ("float16", 8), ("float16", 13)])
+def test_qmv_mma_silu_mul_pairs_gate_and_up_rows(ops, dtype, M):
+    """SILU_MUL through the mma.sync GEMV (forced path 3): a warp takes 8 gate rows and the 8 matching up rows."""
+    from mlx_parallm_b200 import _lib
+    got, exp = qmm_case(ops, M, 256, 512, 4, dtype, _lib.EPI_SILU_MUL, seed=40 + M, path=3)
+    assert got.shape == (M, 128)
+    assert rel_err(got, exp) < {"float16": 2e-3, "bfloat16": 1e-2}[dtype]
+    tile, _ = qmm_case(ops, M, 256, 512, 4, dtype, _lib.EPI_SILU_MUL, seed=40 + M, path=2)
+    assert rel_err(got, tile) < {"float16": 1.1e-3, "bfloat16": 8.1e-3}[dtype]      # one rounding of the same fp32 value
+
+
 # ---------------------------------------------------------------- mma.sync small-matrix GEMM (csrc/qmm_mma.cu)
 @pytest.mark.parametrize("dtype,M,N,K", [
     ("float16", 5, 128, 512),        # NT = 1, two steps, no K split
