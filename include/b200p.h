@@ -147,6 +147,12 @@ int b200p_silu_mul(float* gu, void* out, int64_t M, int64_t I, int64_t ldg, int6
  * is rounded to `dtype` first, as MLX's astype does).  16-bit types only. */
 int b200p_lora_add(const void* x, const void* At, const void* Bt, void* y, int64_t M, int64_t N, int64_t K, int64_t ldx,
                    int64_t ldy, int64_t col0, float scale, int dtype, int out_f32, void* stream);
+/* Rows that b200p_rope_kv_append could NOT append because lengths[b] + l reached Tcap (their K / V are dropped and the
+ * attention of that step reads a stale slot): *count = number of (token, V head) pairs since the last reset on the current
+ * device; reset != 0 clears it.  Synchronises `stream`; not capturable.  The Python surface (models/base.py) grows the cache
+ * before every step and checks this at generation boundaries; direct C-ABI callers should do the same.
+ *                      [no MLX counterpart: the reference's caches grow inside update_and_fetch, models/base.py:104-117] */
+int b200p_kv_overflow_count(unsigned int* count, int reset, void* stream);
 /* lengths[b] += delta (device side, keeps the decode graph replayable) */
 int b200p_advance_lengths(int32_t* lengths, int64_t B, int32_t delta, void* stream);
 

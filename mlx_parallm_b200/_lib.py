@@ -43,6 +43,7 @@ SIGNATURES = {
     "b200p_silu_mul": (_i32, [_vp, _vp, _i64, _i64, _i64, _i64, _i32, _i32, _vp]),
     "b200p_lora_add": (_i32, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i64, _i64, _f32, _i32, _i32, _vp]),
     "b200p_advance_lengths": (_i32, [_vp, _i64, _i32, _vp]),
+    "b200p_kv_overflow_count": (_i32, [C.POINTER(C.c_uint), _i32, _vp]),
     "b200p_attn": (_i32, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i32, _i32, _i32, _i64, _f32, _i32, _i32, _vp, _sz, _vp]),
     "b200p_attn_workspace_bytes": (_sz, [_i64, _i64, _i32, _i32]),
     "b200p_attn_decode_static": (_i32, [_vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i64, _f32, _i32, _i32, _vp]),

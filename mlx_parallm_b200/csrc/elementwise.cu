@@ -360,6 +360,12 @@ extern "C" int b200p_rmsnorm(const float* x, const void* w, void* y, int64_t M, 
 // ------------------------------------------------------------------------------------------------
 namespace b200p {
 
+// Rows whose position reached the cache capacity: their K / V are NOT written (there is no room) and the step's attention
+// would read a stale slot -- plausible but wrong tokens.  The Python surface grows the cache before every step and cannot get
+// here; a direct C-ABI caller can.  Every such (token, V head) bumps this per-device counter, read with
+// b200p_kv_overflow_count at generation boundaries.
+__device__ unsigned int g_kv_overflow = 0;
+
 // TIN = T: qkv is the projection's 16-bit output.  TIN = float: qkv is the fp32 split-K accumulation buffer of the
 // projection (b200p_qmm with ADD_RESIDUAL into a zeroed buffer): values are rounded to T first (the rounding the
 // reference's projection output has) and the buffer is re-zeroed behind the read, ready for the next step.
@@ -396,6 +402,7 @@ __global__ void rope_kv_append_kernel(TIN* __restrict__ qkv, T* __restrict__ q_o
   (void)F32IN;
   if (head >= Hq + Hkv) {  // V head: plain append
     int hv = head - Hq - Hkv;
+    if (pos_i >= Tcap && i == 0) atomicAdd(&g_kv_overflow, 1u);
     if (pos_i < Tcap && act) {
       T* dst = vc + (((int64_t)b * Hkv + hv) * Tcap + pos_i) * D;
       dst[i] = Tr<T>::from_f(x1);
@@ -475,7 +482,10 @@ rope_kv_append_d128_kernel(TIN* __restrict__ qkv, T* __restrict__ q_out, T* __re
     T* dst;
     float o1[2], o2[2];
     if (head >= Hq + Hkv) {      // V head: plain append
-      if (pos_i >= Tcap) return;
+      if (pos_i >= Tcap) {
+        if (lane == 0) atomicAdd(&g_kv_overflow, 1u);
+        return;
+      }
       dst = vc + (((int64_t)b * Hkv + (head - Hq - Hkv)) * Tcap + pos_i) * D;
       o1[0] = x1[0]; o1[1] = x1[1]; o2[0] = x2[0]; o2[1] = x2[1];
     } else {
@@ -621,5 +631,20 @@ extern "C" int b200p_advance_lengths(int32_t* lengths, int64_t B, int32_t delta,
   if (B == 0) return B200P_OK;
   launch_pdl(advance_lengths_kernel, (unsigned)((B + 255) / 256), 256, 0, (cudaStream_t)stream, lengths, B, delta);
   B200P_LAUNCH_CHECK("advance_lengths_kernel");
+  return B200P_OK;
+}
+
+extern "C" int b200p_kv_overflow_count(unsigned int* count, int reset, void* stream) {
+  B200P_REQUIRE(count, B200P_ERR_ARG, "null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e = cudaMemcpyFromSymbolAsync(count, b200p::g_kv_overflow, sizeof(unsigned int), 0, cudaMemcpyDeviceToHost, st);
+  if (e != cudaSuccess) return b200p::cuda_fail(e, "cudaMemcpyFromSymbolAsync(g_kv_overflow)");
+  if (reset) {
+    const unsigned int zero = 0;
+    e = cudaMemcpyToSymbolAsync(b200p::g_kv_overflow, &zero, sizeof(unsigned int), 0, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return b200p::cuda_fail(e, "cudaMemcpyToSymbolAsync(g_kv_overflow)");
+  }
+  e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) return b200p::cuda_fail(e, "cudaStreamSynchronize");
   return B200P_OK;
 }

@@ -188,6 +188,15 @@ def advance_lengths(lengths, delta: int):
     _call("b200p_advance_lengths", lambda: lib().b200p_advance_lengths(_p(lengths), lengths.numel(), int(delta), _stream()))
 
 
+def kv_overflow_count(reset: bool = False) -> int:
+    """Rows b200p_rope_kv_append had to drop since the last reset because their position reached the cache capacity
+    (include/b200p.h).  Synchronises the current stream: call it at generation boundaries, never under graph capture."""
+    import ctypes as C
+    n = C.c_uint(0)
+    _lib.check(lib().b200p_kv_overflow_count(C.byref(n), 1 if reset else 0, _stream()), "b200p_kv_overflow_count")
+    return int(n.value)
+
+
 def attn_workspace_bytes(B, L, Hq, D) -> int:
     return int(lib().b200p_attn_workspace_bytes(B, L, Hq, D))
 

@@ -318,6 +318,12 @@ def generate_step(
         if fx is not None and fx.status() != 0:
             raise RuntimeError("tensor-parallel exchange timed out waiting for a peer rank (status word "
                                f"{fx.status()}): results of this generation are invalid")
+        # same boundary, same reason: a row appended beyond its cache capacity is dropped by the kernel (it cannot happen
+        # through prepare_cache, which grows the buffers first -- this is the loud failure if that invariant ever breaks)
+        dropped = ops.kv_overflow_count(reset=True)
+        if dropped:
+            raise RuntimeError(f"KV cache overflow: {dropped} (token, head) appends were dropped by b200p_rope_kv_append; "
+                               "results of this generation are invalid")
 
     # prefill (eager, chunked) + first sample
     logits = model(y, cache=cache, last_only=True)[:, -1, :]

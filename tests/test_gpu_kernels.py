@@ -244,6 +244,27 @@ def test_rope_kv_append(ops, dtype, D, qk_norm):
         assert not kcn[b, :, s + L:].any() and not kcn[b, :, :s].any()      # nothing else touched
 
 
+@pytest.mark.parametrize("D", [128, 64])          # the head_dim-128 warp kernel and the generic one
+def test_rope_kv_append_counts_rows_beyond_capacity(ops, D):
+    """A row whose position reached Tcap cannot be appended: the kernel drops it and bumps the per-device counter that
+    b200p_kv_overflow_count reads (and the generation loop checks); rows with room are written as usual."""
+    B, L, Hq, Hkv, Tcap = 3, 1, 4, 2, 8
+    ops.kv_overflow_count(reset=True)
+    lengths = torch.tensor([3, 8, 9], dtype=torch.int32, device="cuda")       # row 0 fits, rows 1 and 2 are full
+    qkv = torch.randn((B * L, (Hq + 2 * Hkv) * D), device="cuda").to(torch.float16)
+    q_out = torch.zeros((B, L, Hq, D), dtype=torch.float16, device="cuda")
+    kc = torch.zeros((B, Hkv, Tcap, D), dtype=torch.float16, device="cuda")
+    vc = torch.zeros_like(kc)
+    ops.rope_kv_append(qkv, q_out, kc, vc, lengths, B, L, Hq, Hkv, D, 10000.0)
+    assert ops.kv_overflow_count() == 2 * Hkv                 # one count per dropped (token, V head)
+    assert ops.kv_overflow_count(reset=True) == 2 * Hkv       # reading does not clear; reset returns the old value
+    assert ops.kv_overflow_count() == 0
+    v_row0 = qkv[0].view(Hq + 2 * Hkv, D)[Hq + Hkv:]
+    assert torch.equal(vc[0, :, 3], v_row0) and not vc[1:].any() and not kc[1:].any()
+    ops.rope_kv_append(qkv[:1], q_out[:1], kc[:1], vc[:1], lengths[:1], 1, L, Hq, Hkv, D, 10000.0)
+    assert ops.kv_overflow_count() == 0                       # nothing dropped: the counter stays clear
+
+
 def attn_case(ops, B, L, Hq, Hkv, D, lengths, dtype, path, seed=5):
     from mlx_parallm_b200 import _lib
     rng = np.random.default_rng(seed)
