@@ -302,6 +302,29 @@ def time_prefill(model, cfg, B, Lp, reps=3, dist=None):
     return {"batch": B, "prompt_len": Lp, "ms": ms, "tok_s": B * Lp / ms * 1e3}
 
 
+def time_request(model, B=8, Lp=32, n_new=16, reps=2):
+    """Latency of ONE short request through the public API (utils.generate_step: prefill, decode-graph capture or reuse, a host
+    read of every token like the server's), wall clock: time to the first token and to the last of n_new.  The first
+    repetition pays the capture of the decode graph for this (batch, cache group); later ones show the steady state."""
+    import torch
+    from mlx_parallm_b200.utils import generate_step
+    g = torch.Generator(device="cpu").manual_seed(3)
+    prompt = torch.randint(0, model.args.vocab_size, (B, Lp), generator=g)
+    out = []
+    for rep in range(reps):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        ttft = None
+        for i, (tok, _) in zip(range(n_new), generate_step(prompt, model, temp=0.0)):
+            tok.tolist()
+            if ttft is None:
+                ttft = time.perf_counter() - t0
+        total = time.perf_counter() - t0
+        out.append({"ttft_ms": ttft * 1e3, "total_ms": total * 1e3})
+    return {"batch": B, "prompt_len": Lp, "new_tokens": n_new, "timing": "host wall clock, every token read on the host",
+            "first_request": out[0], "later_request": out[-1]}
+
+
 def tp_selfcheck(cfg_name, cfg, model, rank, world, local_rank, dist, B=8, L=32, steps=8):
     """Correctness of the sharded model carried by the multi-GPU line itself (outside the timed region): rank 0 also builds
     the UNSHARDED model from the same seed, every rank runs the same prefill + ``steps`` greedy steps through the sharded one,
@@ -504,6 +527,12 @@ def main():
                 prefill.append(time_prefill(model, cfg, pb, pl, reps=2, dist=dist))
             except Exception as ex:
                 prefill.append({"batch": pb, "prompt_len": pl, "error": str(ex)[:200]})
+    request = None
+    if world == 1 and not args.no_prefill:
+        try:
+            request = time_request(model)
+        except Exception as ex:
+            request = {"error": str(ex)[:200]}
     cb = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
@@ -532,7 +561,7 @@ def main():
                                     "step_frac_of_hbm_peak": main_res["step_frac_of_hbm_peak"],
                                     "step_frac_of_8TBs_nominal": main_res["step_gbs_per_gpu"] / 8000.0},
                 "kernels": {k: {"calls": v["calls_per_step"], "mean_us": round(v["mean_ms"] * 1e3, 2)} for k, v in main_res["kernels"].items()},
-                "clocks": clocks, "sweep": sweep, "prefill": prefill}
+                "clocks": clocks, "sweep": sweep, "prefill": prefill, "request_latency": request}
         if selfcheck is not None:
             line["tp_selfcheck"] = selfcheck
         if cb is not None:
