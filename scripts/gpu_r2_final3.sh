@@ -1,7 +1,8 @@
 #!/bin/bash
-# Round-2 evidence pass on one GPU (final build: two MMA issuers, early RMSNorm): smoke, the default bench command and the reference arm as the driver runs
+# Round-2 FINAL evidence pass on one GPU (final build): tests (timed), smoke, the default bench command and the reference arm as the driver runs
 # them, the ncu launch list of the same command, full captures of the dominant kernels.
 mkdir -p gpurun_out
+( time timeout 1500 python -m pytest tests -m gpu -q --timeout 600 -p no:cacheprovider 2>&1 | tail -4 ) > gpurun_out/r2_final_pytest.txt 2>&1; cat gpurun_out/r2_final_pytest.txt
 timeout 300 python __graft_entry__.py smoke 2>&1 | tail -2
 ( time timeout 900 python bench.py > gpurun_out/r2_final_bench.json 2> gpurun_out/r2_final_bench.err ) 2>&1 | tail -3; echo "bench exit $?"; wc -l gpurun_out/r2_final_bench.json
 ( time timeout 600 python bench.py --impl reference --steps 20 --warmup 3 > gpurun_out/r2_final_bench_reference.json 2> gpurun_out/r2_final_bench_reference.err ) 2>&1 | tail -3; head -c 600 gpurun_out/r2_final_bench_reference.json; echo
