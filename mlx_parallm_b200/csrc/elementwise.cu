@@ -291,6 +291,8 @@ rmsnorm_cluster_kernel(const float* __restrict__ x, const T* __restrict__ w, T* 
   }
 }
 
+bool pdl_enabled_gemm();      // the global PDL switch (b200p_set_pdl / B200P_PDL != 0): the early norms follow the GEMM launches
+
 template <typename T>
 static cudaError_t launch_rmsnorm_cluster(int C, int64_t M, cudaStream_t st, const float* x, const void* w, void* y, int64_t H,
                                           float eps, int perm) {
@@ -307,7 +309,7 @@ static cudaError_t launch_rmsnorm_cluster(int C, int64_t M, cudaStream_t st, con
   attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 2;
+  cfg.numAttrs = pdl_enabled_gemm() ? 2 : 1;       // without the attribute the griddepcontrol instructions are no-ops
   return cudaLaunchKernelEx(&cfg, rmsnorm_cluster_kernel<T>, x, (const T*)w, (T*)y, H, eps, perm);
 }
 int sm_count();
@@ -344,7 +346,7 @@ extern "C" int b200p_rmsnorm(const float* x, const void* w, void* y, int64_t M, 
     return B200P_OK;
   }
   if (early) {
-    B200P_DISPATCH_DTYPE(dtype, T, (launch_pdl_opt(true, rmsnorm_kernel<T, 128>, (unsigned)M, 128, 0, (cudaStream_t)stream,
+    B200P_DISPATCH_DTYPE(dtype, T, (launch_pdl_opt(b200p::pdl_enabled_gemm(), rmsnorm_kernel<T, 128>, (unsigned)M, 128, 0, (cudaStream_t)stream,
                                        x, (const T*)w, (T*)y, H, eps, perm)));
   } else {
     B200P_DISPATCH_DTYPE(dtype, T, (launch_pdl(rmsnorm_kernel<T, 256>, (unsigned)M, 256, 0, (cudaStream_t)stream,

@@ -37,6 +37,7 @@
 namespace b200p {
 
 int sm_count();
+bool pdl_enabled_gemm();
 
 constexpr int QG_WARPS = 8;
 constexpr int QG_ROWS = QG_WARPS * 16;            // weight rows per CTA
@@ -216,7 +217,7 @@ static int launch_qmm_mma_nt(const void* x, const uint32_t* w, const void* s, co
       if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(qmm_mma_kernel)");                                   \
       attr_set = true;                                                                                                     \
     }                                                                                                                      \
-    launch_pdl_opt(true, kern, grid, block, SMEM, st, (const T*)x, w, (const T*)s, (const T*)b, (float*)y, (int)M, N, K,   \
+    launch_pdl_opt(pdl_enabled_gemm(), kern, grid, block, SMEM, st, (const T*)x, w, (const T*)s, (const T*)b, (float*)y, (int)M, N, K,   \
                    ldx, ldy, (int)splits, (int)sps);                                                                       \
   } while (0)
   if (xperm) GO(true); else GO(false);
