@@ -57,3 +57,22 @@ def test_product_package_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 txt = open(os.path.join(dp, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", txt, flags=re.M), os.path.join(dp, f)
+
+
+def test_environment_switches_are_documented_and_exist():
+    """INTEGRATION.md's table of B200P_* environment switches against the sources: everything the library, the package, the
+    bench or the tests read is documented, and nothing documented has gone away."""
+    import glob
+    import re
+    root = ROOT if "ROOT" in globals() else os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    read = set()
+    for f in glob.glob(os.path.join(root, "mlx_parallm_b200", "csrc", "*.cu*")):
+        read |= set(re.findall(r'(?:getenv|env_int)\("(B200P_[A-Z0-9_]+)"', open(f).read()))
+    py = glob.glob(os.path.join(root, "mlx_parallm_b200", "**", "*.py"), recursive=True) + [os.path.join(root, "bench.py")] + \
+        glob.glob(os.path.join(root, "tests", "*.py"))
+    for f in py:
+        read |= set(re.findall(r'environ(?:\.get)?[\(\[]\s*"(B200P_[A-Z0-9_]+)"', open(f).read()))
+    table = open(os.path.join(root, "INTEGRATION.md")).read().split("## Environment switches", 1)[1]
+    documented = set(re.findall(r"`(B200P_[A-Z0-9_]+)`", "\n".join(l.split("|")[1] for l in table.splitlines() if l.startswith("| `B200P_"))))
+    assert read - documented == set(), f"read but not documented in INTEGRATION.md: {sorted(read - documented)}"
+    assert documented - read == set(), f"documented but never read: {sorted(documented - read)}"
