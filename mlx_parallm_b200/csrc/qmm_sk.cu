@@ -2,8 +2,9 @@
 //
 //   Y[tok, n] += sum_k X[tok, k] * (q[n,k] * s[n, k/64] + b[n, k/64])          Y float32
 //
-// Same main loop as qmm_tc.cu (swap-AB, weights dequantised straight into TMEM as the A operand, X tiles by TMA, 23 warps:
-// 16 dequantisers, 4 epilogue, 2 TMA producers, 1 MMA issuer).  What differs is the schedule and the way out:
+// Same main loop as qmm_tc.cu (swap-AB, weights dequantised straight into TMEM as the A operand, X tiles by TMA, 24 warps:
+// 16 dequantisers, 4 epilogue, 2 TMA producers, 2 MMA issuers -- one per 128-row block of the pair, see
+// umma_half_kblock_f16_ts in tc_ptx.cuh for why two).  What differs is the schedule and the way out:
 //   * persistent stream-K: the work of a launch is the linear sequence of units (output tile of 2 x 128 weight rows,
 //     K stage of 128 packed bytes per row); CTA c of G takes the contiguous range [c*U/G, (c+1)*U/G), so every SM streams
 //     the same number of weight bytes whatever N and K are -- o_proj / down_proj have 16 tiles for 148 SMs;
