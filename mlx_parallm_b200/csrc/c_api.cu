@@ -101,7 +101,8 @@ int sm_count() {
 
 using namespace b200p;
 
-extern "C" const char* b200p_version(void) { return "b200parallm 0.2 (sm_100a)";   // 0.2: round-2 ABI (PERM8 flags, stream-K / small-matrix GEMM paths, b200p_attn_decode_static, b200p_kv_overflow_count) }
+// 0.2: round-2 ABI (PERM8 flags, stream-K / small-matrix GEMM paths, b200p_attn_decode_static, b200p_kv_overflow_count)
+extern "C" const char* b200p_version(void) { return "b200parallm 0.2 (sm_100a)"; }
 extern "C" const char* b200p_last_error(void) { return g_err; }
 
 extern "C" int b200p_arch_check(void) {
